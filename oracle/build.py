@@ -1,0 +1,86 @@
+"""TEST INFRASTRUCTURE ONLY -- builds the two CPU checkers.
+
+  oracle/_build/libcsm_oracle.so   plain-C restatement (csm_oracle.c, nn_oracle.c)
+  oracle/_ref/libnautilus_ref.so   the UNMODIFIED reference sources, compiled where
+                                   they lie under /root/reference (only when that
+                                   tree is present, i.e. in the build container;
+                                   the GPU box uses the prebuilt file)
+
+Flags for the reference follow its Release build (CMakeLists.txt:11,16:
+-std=c++17 -O3 -DNDEBUG -fopenmp, no -march => no FMA contraction) plus
+-Dcimg_display=0 because there is no X11.  The reference's own build system
+(catkin/cmake + Eigen/glog/Ceres/ROS) cannot run here; its CSM and KD-tree
+translation units compile directly against oracle/shim/.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_ROOT = "/root/reference"
+BUILD_DIR = os.path.join(HERE, "_build")
+REF_DIR = os.path.join(HERE, "_ref")
+PORT_LIB = os.path.join(BUILD_DIR, "libcsm_oracle.so")
+REF_LIB = os.path.join(REF_DIR, "libnautilus_ref.so")
+
+
+def _newer(target: str, sources: list[str]) -> bool:
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources if os.path.exists(s))
+
+
+def _run(cmd: list[str]) -> None:
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+        raise RuntimeError("oracle build failed")
+
+
+def build_port(force: bool = False) -> str:
+    srcs = [os.path.join(HERE, f) for f in ("csm_oracle.c", "nn_oracle.c")]
+    srcs = [s for s in srcs if os.path.exists(s)]
+    if not force and _newer(PORT_LIB, srcs):
+        return PORT_LIB
+    os.makedirs(BUILD_DIR, exist_ok=True)
+    _run(["gcc", "-std=c11", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wall",
+          *srcs, "-o", PORT_LIB, "-lm"])
+    return PORT_LIB
+
+
+def build_ref(force: bool = False) -> str | None:
+    """Returns the path, or None when /root/reference is absent and nothing is prebuilt."""
+    csm_src = os.path.join(REF_ROOT, "third_party/csm/src/CorrelativeScanMatcher.cc")
+    kd_src = os.path.join(REF_ROOT, "src/util/kdtree.cc")
+    wrap = [os.path.join(HERE, f) for f in ("ref_wrap.cc", "ref_nn_wrap.cc")]
+    wrap = [s for s in wrap if os.path.exists(s)]
+    if not os.path.exists(csm_src):
+        return REF_LIB if os.path.exists(REF_LIB) else None
+    shim = [os.path.join(dp, f) for dp, _, fs in os.walk(os.path.join(HERE, "shim")) for f in fs]
+    if not force and _newer(REF_LIB, wrap + shim):
+        return REF_LIB
+    os.makedirs(REF_DIR, exist_ok=True)
+    srcs = wrap + [csm_src]
+    if os.path.exists(os.path.join(HERE, "ref_nn_wrap.cc")):
+        srcs.append(kd_src)
+    _run(["g++", "-std=c++17", "-O3", "-DNDEBUG", "-fopenmp", "-Dcimg_display=0",
+          "-fPIC", "-shared",
+          "-I" + os.path.join(HERE, "shim"),
+          "-I" + os.path.join(REF_ROOT, "third_party/csm/src"),
+          "-I" + os.path.join(REF_ROOT, "src"),
+          *srcs, "-o", REF_LIB])
+    return REF_LIB
+
+
+def build_all(force: bool = False) -> None:
+    build_port(force)
+    build_ref(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv)
+    print(PORT_LIB, os.path.exists(PORT_LIB))
+    print(REF_LIB, os.path.exists(REF_LIB))

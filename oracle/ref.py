@@ -1,0 +1,197 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes view of oracle/_ref/libnautilus_ref.so,
+the UNMODIFIED reference CSM compiled by oracle/build.py (see ref_wrap.cc).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this.  The product path
+(nautilus_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libnautilus_ref.so")
+
+_lib = None
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    L = C.CDLL(LIB_PATH)
+    d, f, vp, i64, u64 = C.c_double, C.c_float, C.c_void_p, C.c_int64, C.c_uint64
+    L.ref_table_new.restype = vp
+    L.ref_table_new.argtypes = [d, d]
+    L.ref_table_free.argtypes = [vp]
+    L.ref_table_width.restype = u64
+    L.ref_table_width.argtypes = [vp]
+    L.ref_table_height.restype = u64
+    L.ref_table_height.argtypes = [vp]
+    L.ref_table_set.argtypes = [vp, f, f, d]
+    L.ref_table_get.restype = d
+    L.ref_table_get.argtypes = [vp, f, f]
+    L.ref_table_is_inside.restype = C.c_int
+    L.ref_table_is_inside.argtypes = [vp, f, f]
+    L.ref_table_max_area.restype = d
+    L.ref_table_max_area.argtypes = [vp, d, d, d, d]
+    L.ref_table_abs_coords.restype = u64
+    L.ref_table_abs_coords.argtypes = [vp, d, d]
+    L.ref_table_values.argtypes = [vp, _f64p]
+    L.ref_table_load.argtypes = [vp, _f64p]
+    L.ref_table_blur.argtypes = [vp]
+    L.ref_table_normalize.argtypes = [vp]
+    L.ref_lowres_from_table.restype = vp
+    L.ref_lowres_from_table.argtypes = [d, d, d, d, vp]
+    L.ref_highres_table.restype = vp
+    L.ref_highres_table.argtypes = [d, d, d, d, _f32p, i64]
+    pd, pf = C.POINTER(d), C.POINTER(f)
+    L.ref_match.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, d, d, pd, pf, pf, pf]
+    L.ref_match_restricted.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, d, d, d,
+                                       pd, pf, pf, pf]
+    L.ref_uncertainty2.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, d, _f32p]
+    L.ref_uncertainty3.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, _f32p]
+    L.ref_match_batch.restype = d
+    L.ref_match_batch.argtypes = [d, d, d, d, _f32p, _i64p, _i32p, _i32p, _f64p, _f64p,
+                                  i64, C.c_int, _f64p, _f32p, _f32p, _f32p]
+    L.ref_build_tables_batch.restype = d
+    L.ref_build_tables_batch.argtypes = [d, d, d, d, _f32p, _i64p, i64, C.c_int, pd]
+    L.ref_max_threads.restype = C.c_int
+    _lib = L
+    return L
+
+
+class RefTable:
+    """struct LookupTable of the reference (CorrelativeScanMatcher.h:27-110)."""
+
+    def __init__(self, range_=None, resolution=None, handle=None):
+        self._L = lib()
+        self.h = handle if handle is not None else self._L.ref_table_new(range_, resolution)
+
+    def __del__(self):
+        try:
+            self._L.ref_table_free(self.h)
+        except Exception:
+            pass
+
+    @property
+    def width(self):
+        return int(self._L.ref_table_width(self.h))
+
+    @property
+    def height(self):
+        return int(self._L.ref_table_height(self.h))
+
+    def set(self, x, y, v):
+        self._L.ref_table_set(self.h, x, y, v)
+
+    def get(self, x, y):
+        return float(self._L.ref_table_get(self.h, x, y))
+
+    def is_inside(self, x, y):
+        return bool(self._L.ref_table_is_inside(self.h, x, y))
+
+    def max_area(self, sx, sy, ex, ey):
+        return float(self._L.ref_table_max_area(self.h, sx, sy, ex, ey))
+
+    def abs_coords(self, x, y):
+        return int(self._L.ref_table_abs_coords(self.h, x, y))
+
+    def values(self) -> np.ndarray:
+        out = np.empty((self.height, self.width), dtype=np.float64)
+        self._L.ref_table_values(self.h, out)
+        return out
+
+    def load(self, arr):
+        arr = np.ascontiguousarray(arr, dtype=np.float64)
+        assert arr.shape == (self.height, self.width)
+        self._L.ref_table_load(self.h, arr)
+
+    def blur(self):
+        self._L.ref_table_blur(self.h)
+
+    def normalize(self):
+        self._L.ref_table_normalize(self.h)
+
+
+class RefMatcher:
+    """class CorrelativeScanMatcher of the reference (CorrelativeScanMatcher.h:112-152)."""
+
+    def __init__(self, scanner_range, trans_range, low_res, high_res):
+        self._L = lib()
+        self.p = (float(scanner_range), float(trans_range), float(low_res), float(high_res))
+
+    def highres(self, cloud) -> RefTable:
+        cloud = np.ascontiguousarray(cloud, dtype=np.float32).reshape(-1, 2)
+        return RefTable(handle=self._L.ref_highres_table(*self.p, cloud, len(cloud)))
+
+    def lowres(self, hi: RefTable) -> RefTable:
+        return RefTable(handle=self._L.ref_lowres_from_table(*self.p, hi.h))
+
+    def match(self, a, b, rot_min=0.0, rot_max=2 * np.pi):
+        a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 2)
+        s, x, y, t = C.c_double(), C.c_float(), C.c_float(), C.c_float()
+        self._L.ref_match(*self.p, a, len(a), b, len(b), rot_min, rot_max,
+                          C.byref(s), C.byref(x), C.byref(y), C.byref(t))
+        return s.value, np.float32(x.value), np.float32(y.value), np.float32(t.value)
+
+    def match_restricted(self, a, b, rot_a, rot_b, restriction):
+        a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 2)
+        s, x, y, t = C.c_double(), C.c_float(), C.c_float(), C.c_float()
+        self._L.ref_match_restricted(*self.p, a, len(a), b, len(b), rot_a, rot_b,
+                                     restriction, C.byref(s), C.byref(x), C.byref(y),
+                                     C.byref(t))
+        return s.value, np.float32(x.value), np.float32(y.value), np.float32(t.value)
+
+    def uncertainty2(self, a, b, rotation):
+        a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 2)
+        out = np.zeros(4, dtype=np.float32)
+        self._L.ref_uncertainty2(*self.p, a, len(a), b, len(b), rotation, out)
+        return out.reshape(2, 2)
+
+    def uncertainty3(self, a, b):
+        a = np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b, dtype=np.float32).reshape(-1, 2)
+        out = np.zeros(9, dtype=np.float32)
+        self._L.ref_uncertainty3(*self.p, a, len(a), b, len(b), out)
+        return out.reshape(3, 3)
+
+    def match_batch(self, xy, offsets, pair_a, pair_b, rot_min, rot_max, threads=0):
+        n = len(pair_a)
+        score = np.zeros(n, np.float64)
+        x = np.zeros(n, np.float32)
+        y = np.zeros(n, np.float32)
+        th = np.zeros(n, np.float32)
+        secs = self._L.ref_match_batch(
+            *self.p, np.ascontiguousarray(xy, np.float32),
+            np.ascontiguousarray(offsets, np.int64),
+            np.ascontiguousarray(pair_a, np.int32), np.ascontiguousarray(pair_b, np.int32),
+            np.ascontiguousarray(rot_min, np.float64),
+            np.ascontiguousarray(rot_max, np.float64), n, threads, score, x, y, th)
+        return secs, score, x, y, th
+
+    def build_tables_batch(self, xy, offsets, threads=0):
+        cs = C.c_double()
+        secs = self._L.ref_build_tables_batch(
+            *self.p, np.ascontiguousarray(xy, np.float32),
+            np.ascontiguousarray(offsets, np.int64), len(offsets) - 1, threads,
+            C.byref(cs))
+        return secs, cs.value
+
+
+def max_threads() -> int:
+    return int(lib().ref_max_threads())
