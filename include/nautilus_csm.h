@@ -1,0 +1,151 @@
+/* nautilus_csm.h -- C ABI of libnautilus_csm_b200.so
+ *
+ * B200 (sm_100a) implementation of the correlative-scan-matching hot path of
+ * ut-amrl/nautilus.  The reference has no FFI layer for this path: its
+ * "operator API" is the C++ class in
+ *   third_party/csm/src/CorrelativeScanMatcher.h:27-152
+ * linked statically as libcsm (third_party/csm/CMakeLists.txt:32-39).  The
+ * entry points below are what a binding of that class has to reach; each one
+ * names the reference member it replaces.  A header-compatible C++ shim that
+ * forwards the reference class to these calls lives in
+ * nautilus_b200/cpp/CorrelativeScanMatcher.h, and INTEGRATION.md shows the
+ * reference-side change.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative NAUTILUS_E* code on
+ *     failure; nautilus_csm_last_error() gives the text (thread-local).
+ *     There is NO CPU fallback: without a usable CUDA device create() fails.
+ *   - point clouds are contiguous float (x, y) pairs, exactly the memory of a
+ *     std::vector<Eigen::Vector2f>; never retained after the call returns
+ *     unless uploaded with nautilus_csm_upload_scans.
+ *   - "a" is the query cloud, "b" the cloud that gets rasterised; the result
+ *     is the transform that moves a onto b (CorrelativeScanMatcher.cc:145-245).
+ *   - tables are double, x fastest: values[x + y * width]
+ *     (CImg<double>, CorrelativeScanMatcher.h:31-39).
+ *   - all pointers are HOST pointers unless a name ends in _dev.
+ */
+#ifndef NAUTILUS_CSM_H_
+#define NAUTILUS_CSM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NAUTILUS_OK 0
+#define NAUTILUS_EINVAL (-1)   /* bad argument */
+#define NAUTILUS_ECUDA (-2)    /* CUDA runtime error / no device */
+#define NAUTILUS_ENOMEM (-3)   /* device or host allocation failed */
+#define NAUTILUS_EEMPTY (-4)   /* empty query cloud or empty rotation window: the
+                                  reference never terminates on these inputs
+                                  (CorrelativeScanMatcher.cc:170-181) */
+#define NAUTILUS_ESTATE (-5)   /* call order violated (e.g. match before upload) */
+
+typedef struct NautilusCsm NautilusCsm;
+
+/* Constructor arguments of CorrelativeScanMatcher (CorrelativeScanMatcher.h:114-119)
+ * plus the knobs the reference hard-codes. */
+typedef struct NautilusCsmParams {
+  double scanner_range; /* range_       : table half extent, metres            */
+  double trans_range;   /* trans_range_ : translation search half extent       */
+  double low_res;       /* low_res_     : coarse cell size                     */
+  double high_res;      /* high_res_    : fine cell size                       */
+  double rot_step;      /* 0 => M_PI/180, the reference's constant (cc:92)     */
+  double blur_sigma;    /* 0 => 4, DEFAULT_GAUSSIAN_SIGMA (h:19)               */
+  int32_t device;       /* CUDA device ordinal                                 */
+  int32_t margin_cells; /* table crop margin in hi-res cells around the scan's
+                           occupied box.  <0 => never crop (every table is
+                           computed over the full grid, bit-identical to the
+                           reference); 0 => default (160: truncated tails are
+                           below 1e-20 of the table maximum)                   */
+  int32_t max_tables;   /* resident hi-res table slots per wave; 0 => auto     */
+  int32_t reserved;
+} NautilusCsmParams;
+
+/* Per-pair search statistics, counted by the same rule as the oracle:
+ * low-res candidates scored, hi-res candidates scored, windows popped. */
+typedef struct NautilusCsmStats {
+  int64_t n_low;
+  int64_t n_high;
+  int64_t n_pops;
+} NautilusCsmStats;
+
+/* Device-side timings of the last batch call, CUDA events on the handle's stream. */
+typedef struct NautilusCsmTimings {
+  float ms_total;    /* first launch to last launch of the call                */
+  float ms_tables;   /* rasterise + blur + normalise + pool                    */
+  float ms_low;      /* low-res exhaustive scoring                             */
+  float ms_refine;   /* memo reduction + best-first hi-res refinement          */
+  int32_t launches;  /* kernels launched by the call                           */
+  int32_t waves;     /* table waves the call was split into                    */
+} NautilusCsmTimings;
+
+const char* nautilus_csm_last_error(void);
+/* Library build tag, e.g. "nautilus_csm_b200 sm_100a". */
+const char* nautilus_csm_version(void);
+
+/* CorrelativeScanMatcher::CorrelativeScanMatcher (h:114-119). */
+int nautilus_csm_create(const NautilusCsmParams* params, NautilusCsm** out);
+void nautilus_csm_destroy(NautilusCsm* h);
+
+/* Run the handle's work on a caller-owned cudaStream_t (e.g. torch's current
+ * stream) instead of its own.  NULL restores the handle's stream. */
+int nautilus_csm_set_stream(NautilusCsm* h, void* cuda_stream);
+
+/* LookupTable::width of the hi- and low-res tables (h:32-35). */
+int nautilus_csm_table_dims(const NautilusCsm* h, uint64_t* w_high, uint64_t* w_low);
+
+/* LookupTable::convertX / AbsCoords (h:43-49,104-109) for a table of the given
+ * resolution; exposed so host code and tests can check the index maps. */
+int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v);
+
+/* --- scan residency -------------------------------------------------------
+ * Copies n_scans clouds to the device (one H2D); scan ids are 0..n_scans-1 and
+ * replace any previous set.  offsets has n_scans+1 entries, in points. */
+int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* offsets,
+                              int32_t n_scans);
+
+/* --- tables ---------------------------------------------------------------
+ * GetLookupTableHighRes (cc:50-53 -> GetLookupTable cc:21-30): rasterise,
+ * Van Vliet blur, normalise.  out_high: w_high^2 doubles; out_low (optional):
+ * w_low^2 doubles = GetLookupTableLowRes of the same table. */
+int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points,
+                               double* out_high, double* out_low);
+
+/* GetLookupTableLowRes(const LookupTable&) (cc:32-48) on a caller-made table of
+ * dimensions width x height and cell size `resolution`. out_low: w_low^2. */
+int nautilus_csm_lowres_from_table(NautilusCsm* h, const double* high, uint64_t width,
+                                   uint64_t height, double resolution, double* out_low);
+
+/* Builds (and discards) the tables of the given uploaded scans; the batch
+ * form of the two calls above, used for the table-build configuration.
+ * checksum (optional) receives the sum over all low-res tables. */
+int nautilus_csm_build_tables(NautilusCsm* h, const int32_t* scan_ids, int32_t n,
+                              double* checksum);
+
+/* --- matching -------------------------------------------------------------
+ * GetTransformation(a, b, rotation_min, rotation_max) (cc:145-245) for n_pairs
+ * independent pairs of uploaded scans.  Outputs have n_pairs entries; stats is
+ * optional.  Pairs may come in any order; they are grouped by target internally
+ * so each target's tables are built once per call. */
+int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
+                             const double* rot_min, const double* rot_max,
+                             int32_t n_pairs, double* score, float* x, float* y,
+                             float* theta, NautilusCsmStats* stats);
+
+/* Single pair from host clouds = batch of one (upload + tables + search). */
+int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b,
+                       int64_t nb, double rot_min, double rot_max, double* score,
+                       float* x, float* y, float* theta, NautilusCsmStats* stats);
+
+/* The rotation window of the 5-argument GetTransformation (cc:247-264). */
+void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,
+                                  double* rot_min, double* rot_max);
+
+int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NAUTILUS_CSM_H_ */

@@ -1,0 +1,797 @@
+// C ABI of libnautilus_csm_b200.so (include/nautilus_csm.h): handle, device
+// buffer ownership, host-built index lists, wave scheduling.  No CPU fallback:
+// every compute entry point launches the sm_100a kernels or fails.
+//
+// Host-built lists.  Every coordinate the reference derives from an
+// accumulating double, a float narrowing or a floor/round is one-dimensional
+// and tiny, so it is produced here with the reference's own expressions
+//  and uploaded: pooling windows, low-res translations
+// and their memo slots, hi-res window steps, rotation lists with libm
+// sinf/cosf.  The device only evaluates floor(x / res) on point + translation.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <numeric>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/nautilus_csm.h"
+#include "csm_kernels.h"
+
+using namespace csm;
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) {
+  g_error = msg;
+  return code;
+}
+
+#define CU_TRY(expr)                                                              \
+  do {                                                                            \
+    cudaError_t e_ = (expr);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      int code_ = (e_ == cudaErrorMemoryAllocation) ? NAUTILUS_ENOMEM : NAUTILUS_ECUDA; \
+      return fail(code_, std::string(#expr) + ": " + cudaGetErrorString(e_));     \
+    }                                                                             \
+  } while (0)
+
+// convertX / convertY on the host (CorrelativeScanMatcher.h:43-49)
+long long host_cell(float v, double res, uint64_t dim) {
+  const double c = (double)(dim / 2) + floor((double)v / res);
+  if (c < -4.0e18) return -4000000000000000000LL;
+  if (c > 4.0e18) return 4000000000000000000LL;
+  return (long long)c;
+}
+
+// CImg<T>::vanvliet coefficients (CImg.h:49267-49284) + Triggs matrix (49066-49081)
+void vanvliet_coeffs(double sigma, VanVliet* f) {
+  const double nnsigma = sigma < 0.5 ? 0.5 : sigma, m0 = 1.16680, m1 = 1.10783, m2 = 1.40586,
+               m1sq = m1 * m1, m2sq = m2 * m2,
+               q = (nnsigma < 3.556 ? -0.2568 + 0.5784 * nnsigma + 0.0561 * nnsigma * nnsigma
+                                    : 2.5091 + 0.9804 * (nnsigma - 3.556)),
+               qsq = q * q, scale = (m0 + q) * (m1sq + m2sq + 2 * m1 * q + qsq),
+               b1 = -q * (2 * m0 * m1 + m1sq + m2sq + (2 * m0 + 4 * m1) * q + 3 * qsq) / scale,
+               b2 = qsq * (m0 + 2 * m1 + 3 * q) / scale, b3 = -qsq * q / scale,
+               B = (m0 * (m1sq + m2sq)) / scale;
+  f->B = B; f->a1 = -b1; f->a2 = -b2; f->a3 = -b3;
+  const double a1 = f->a1, a2 = f->a2, a3 = f->a3,
+               scaleM = 1. / ((1. + a1 - a2 + a3) * (1. - a1 - a2 - a3) *
+                              (1. + a2 + (a1 - a3) * a3));
+  f->M[0] = scaleM * (-a3 * a1 + 1. - a3 * a3 - a2);
+  f->M[1] = scaleM * (a3 + a1) * (a2 + a3 * a1);
+  f->M[2] = scaleM * a3 * (a1 + a3 * a2);
+  f->M[3] = scaleM * (a1 + a3 * a2);
+  f->M[4] = -scaleM * (a2 - 1.) * (a2 + a3 * a1);
+  f->M[5] = -scaleM * a3 * (a3 * a1 + a3 * a3 + a2 - 1.);
+  f->M[6] = scaleM * (a3 * a1 + a2 + a1 * a1 - a2 * a2);
+  f->M[7] = scaleM * (a1 * a2 + a3 * a2 * a2 - a1 * a3 * a3 - a3 * a3 * a3 - a3 * a2 + a3);
+  f->M[8] = scaleM * a3 * (a1 + a3 * a2);
+}
+
+// Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
+struct PoolListHost {
+  std::vector<int> s, e, dst;
+  std::vector<unsigned char> win;
+  bool tiles = false;  // windows tile [0, dim) in order without gaps/overlap
+};
+
+PoolListHost make_pool_list(double range, double low_res, double hi_res, uint64_t hi_dim,
+                            uint64_t low_dim) {
+  PoolListHost pl;
+  for (double x = -range + CSM_EPSILON; x < range; x += low_res) {
+    // MaxArea(x, ., x + low_res, .): doubles narrowed to float by convertX
+    const uint64_t usx = (uint64_t)host_cell((float)x, hi_res, hi_dim);
+    const uint64_t uex = (uint64_t)host_cell((float)(x + low_res), hi_res, hi_dim);
+    const int x0 = (int)usx, x1 = (int)(uex - 1);  // get_crop(int, ...) narrowing
+    pl.s.push_back(std::min(x0, x1));
+    pl.e.push_back(std::max(x0, x1));
+    const long long d = host_cell((float)x, low_res, low_dim);  // SetPointValue(Vector2f(x, y))
+    pl.dst.push_back((d >= 0 && d < (long long)low_dim) ? (int)d : -1);
+    if (pl.s.size() > 10000000) break;  // degenerate parameters
+  }
+  const int n = (int)pl.s.size();
+  pl.win.assign(n, 0);
+  std::map<int, int> last;
+  for (int k = 0; k < n; ++k)
+    if (pl.dst[k] >= 0) last[pl.dst[k]] = k;
+  for (auto& kv : last) pl.win[kv.second] = 1;
+  bool tiles = n > 0 && pl.s[0] <= 0 && pl.e[n - 1] >= (int)hi_dim - 1;
+  for (int k = 0; tiles && k < n; ++k) {
+    if (pl.s[k] > pl.e[k]) tiles = false;
+    if (k + 1 < n && pl.e[k] + 1 != pl.s[k + 1]) tiles = false;
+  }
+  pl.tiles = tiles;
+  return pl;
+}
+
+struct DevPool {
+  PoolListDev d{nullptr, nullptr, nullptr, nullptr, 0};
+  void release() {
+    cudaFree(d.s); cudaFree(d.e); cudaFree(d.dst); cudaFree(d.win);
+    d = PoolListDev{nullptr, nullptr, nullptr, nullptr, 0};
+  }
+  int upload(const PoolListHost& h) {
+    release();
+    const int n = (int)h.s.size();
+    d.n = n;
+    if (n == 0) return NAUTILUS_OK;
+    CU_TRY(cudaMalloc(&d.s, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.e, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.dst, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.win, n));
+    CU_TRY(cudaMemcpy(d.s, h.s.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.e, h.e.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.dst, h.dst.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.win, h.win.data(), n, cudaMemcpyHostToDevice));
+    return NAUTILUS_OK;
+  }
+};
+
+// A set of clouds resident on the device.
+struct ScanSet {
+  float2* points = nullptr;
+  long long* offsets = nullptr;
+  std::vector<long long> host_offsets;
+  size_t cap_points = 0, cap_offsets = 0;
+  int n = 0;
+  void release() {
+    cudaFree(points); cudaFree(offsets);
+    points = nullptr; offsets = nullptr; cap_points = cap_offsets = 0; n = 0;
+  }
+};
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return NAUTILUS_OK;
+    cudaFree(p);
+    p = nullptr; cap = 0;
+    const size_t want = std::max(n, (size_t)16);
+    CU_TRY(cudaMalloc(&p, sizeof(T) * want));
+    cap = want;
+    return NAUTILUS_OK;
+  }
+  void release() { cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct NautilusCsm {
+  NautilusCsmParams params;
+  Geometry geo;
+  VanVliet vv;
+  double rot_step;
+  int device;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  int sm_count = 148;
+
+  // tables
+  PoolListHost pool_host;
+  DevPool pool_dev;
+  int n_slots = 0;
+  std::vector<TableSlot> slots_host;
+  DevBuf<TableSlot> slots_dev;
+  DevBuf<TableMeta> metas_dev;
+  double* slab_values = nullptr;
+  unsigned* slab_bitmap = nullptr;
+  unsigned char* slab_rowflag = nullptr;
+  double* slab_low = nullptr;
+  double* slab_lowlog = nullptr;
+  DevBuf<double> dense_scratch;
+  DevBuf<double> scalar_scratch;
+
+  // search grid
+  std::vector<float> t_low_host;
+  std::vector<int> slot_rank_host, n_h_host;
+  std::vector<float> t_high_host;
+  DevBuf<float> t_low_dev, t_high_dev;
+  DevBuf<int> slot_rank_dev, n_h_dev;
+  SearchGrid grid{};
+
+  // scans + per-batch buffers
+  ScanSet user_scans, tmp_scans;
+  DevBuf<int> table_scan_dev;
+  DevBuf<PairWork> pairs_dev;
+  DevBuf<Rotation> rots_dev;
+  DevBuf<PairResult> results_dev;
+  DevBuf<double> chunk_best_dev;
+  DevBuf<int> chunk_rot_dev;
+  std::vector<cudaEvent_t> events;
+  NautilusCsmTimings timings{};
+};
+
+namespace {
+
+void free_slots(NautilusCsm* h) {
+  cudaFree(h->slab_values); cudaFree(h->slab_bitmap); cudaFree(h->slab_rowflag);
+  cudaFree(h->slab_low); cudaFree(h->slab_lowlog);
+  h->slab_values = nullptr; h->slab_bitmap = nullptr; h->slab_rowflag = nullptr;
+  h->slab_low = nullptr; h->slab_lowlog = nullptr;
+  h->n_slots = 0;
+}
+
+size_t slot_bytes(const Geometry& g) {
+  const size_t w = g.w, wl = g.wl;
+  return sizeof(double) * ((w + 3) & ~(size_t)3) * w + sizeof(unsigned) * g.bm_stride * w + w +
+         sizeof(double) * (wl * wl + (wl + 1) * (wl + 1));
+}
+
+// Makes at least `want` table slots resident (bounded by params.max_tables and
+// by free device memory); returns the slot count through h->n_slots.
+int ensure_slots(NautilusCsm* h, int want) {
+  const Geometry& g = h->geo;
+  int cap = h->params.max_tables > 0 ? h->params.max_tables : 256;
+  size_t free_b = 0, total_b = 0;
+  CU_TRY(cudaMemGetInfo(&free_b, &total_b));
+  const size_t per = slot_bytes(g);
+  const size_t have = (size_t)h->n_slots * per;
+  const size_t budget = (free_b + have) / 2;  // leave half of what is free to the caller
+  cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)cap, budget / per));
+  want = std::max(1, std::min(want, cap));
+  if (want <= h->n_slots) return NAUTILUS_OK;
+  free_slots(h);
+  const size_t w = g.w, wl = g.wl, vstride = ((w + 3) & ~(size_t)3) * w;
+  CU_TRY(cudaMalloc(&h->slab_values, sizeof(double) * vstride * want));
+  CU_TRY(cudaMalloc(&h->slab_bitmap, sizeof(unsigned) * (size_t)g.bm_stride * w * want));
+  CU_TRY(cudaMalloc(&h->slab_rowflag, w * (size_t)want));
+  CU_TRY(cudaMalloc(&h->slab_low, sizeof(double) * wl * wl * want));
+  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 1) * (wl + 1) * want));
+  h->slots_host.resize(want);
+  for (int i = 0; i < want; ++i) {
+    TableSlot& s = h->slots_host[i];
+    s.values = h->slab_values + vstride * i;
+    s.bitmap = h->slab_bitmap + (size_t)g.bm_stride * w * i;
+    s.rowflag = h->slab_rowflag + w * (size_t)i;
+    s.low = h->slab_low + wl * wl * (size_t)i;
+    s.lowlog = h->slab_lowlog + (wl + 1) * (wl + 1) * (size_t)i;
+  }
+  int rc = h->slots_dev.reserve(want);
+  if (rc) return rc;
+  rc = h->metas_dev.reserve(want);
+  if (rc) return rc;
+  CU_TRY(cudaMemcpy(h->slots_dev.p, h->slots_host.data(), sizeof(TableSlot) * want,
+                    cudaMemcpyHostToDevice));
+  h->n_slots = want;
+  return NAUTILUS_OK;
+}
+
+// Low-res translation grid, memo slots and hi-res window steps.
+int build_search_grid(NautilusCsm* h) {
+  const double T = h->params.trans_range, rl = h->params.low_res, rh = h->params.high_res;
+  const uint64_t wl = (uint64_t)h->geo.wl;
+  std::vector<double> t_low_d;
+  for (double t = -T + CSM_EPSILON; t < T; t += rl) {  // cc:96-99
+    t_low_d.push_back(t);
+    if (t_low_d.size() > 100000) return fail(NAUTILUS_EINVAL, "translation grid too large");
+  }
+  const int n_t = (int)t_low_d.size();
+  if (n_t == 0) return fail(NAUTILUS_EINVAL, "empty translation grid (trans_range <= 0?)");
+  h->t_low_host.resize(n_t);
+  for (int i = 0; i < n_t; ++i) h->t_low_host[i] = (float)t_low_d[i];
+  // AbsCoords (h:104-109) of every (x_i, y_j); max_element visits slots in this order
+  std::vector<std::pair<unsigned long long, int>> order;
+  order.reserve((size_t)n_t * n_t);
+  for (int i = 0; i < n_t; ++i)
+    for (int j = 0; j < n_t; ++j) {
+      const size_t row = (size_t)(((double)(wl / 2) + round(t_low_d[j] / rl)) * (double)wl);
+      const size_t col = (size_t)((double)(wl / 2) + round(t_low_d[i] / rl));
+      order.emplace_back((unsigned long long)(row + col), i * n_t + j);
+    }
+  std::sort(order.begin(), order.end());
+  for (size_t k = 1; k < order.size(); ++k)
+    if (order[k].first == order[k - 1].first)
+      return fail(NAUTILUS_EINVAL,
+                  "two low-res translations share a memo slot (AbsCoords collision); "
+                  "unsupported parameter combination");
+  h->slot_rank_host.assign((size_t)n_t * n_t, 0);
+  for (size_t k = 0; k < order.size(); ++k) h->slot_rank_host[order[k].second] = (int)k;
+  // hi-res window opened at low index i (cc:195-202, 126-129)
+  std::vector<std::vector<float>> steps(n_t);
+  int nh_max = 1;
+  for (int i = 0; i < n_t; ++i) {
+    const float fx = h->t_low_host[i];
+    const double lo = std::max((double)fx, -T), hi = std::min(fx + rl, T);
+    for (double x = lo + CSM_EPSILON; x < hi; x += rh) {
+      steps[i].push_back((float)x);
+      if (steps[i].size() > 4096) return fail(NAUTILUS_EINVAL, "hi-res window too large");
+    }
+    nh_max = std::max(nh_max, (int)steps[i].size());
+  }
+  h->n_h_host.resize(n_t);
+  h->t_high_host.assign((size_t)n_t * nh_max, 0.f);
+  for (int i = 0; i < n_t; ++i) {
+    h->n_h_host[i] = (int)steps[i].size();
+    std::copy(steps[i].begin(), steps[i].end(), h->t_high_host.begin() + (size_t)i * nh_max);
+  }
+  int rc;
+  if ((rc = h->t_low_dev.reserve(n_t))) return rc;
+  if ((rc = h->t_high_dev.reserve((size_t)n_t * nh_max))) return rc;
+  if ((rc = h->slot_rank_dev.reserve((size_t)n_t * n_t))) return rc;
+  if ((rc = h->n_h_dev.reserve(n_t))) return rc;
+  CU_TRY(cudaMemcpy(h->t_low_dev.p, h->t_low_host.data(), sizeof(float) * n_t, cudaMemcpyHostToDevice));
+  CU_TRY(cudaMemcpy(h->t_high_dev.p, h->t_high_host.data(), sizeof(float) * n_t * nh_max,
+                    cudaMemcpyHostToDevice));
+  CU_TRY(cudaMemcpy(h->slot_rank_dev.p, h->slot_rank_host.data(), sizeof(int) * n_t * n_t,
+                    cudaMemcpyHostToDevice));
+  CU_TRY(cudaMemcpy(h->n_h_dev.p, h->n_h_host.data(), sizeof(int) * n_t, cudaMemcpyHostToDevice));
+  h->grid.n_t = n_t;
+  h->grid.t_low = h->t_low_dev.p;
+  h->grid.slot_rank = h->slot_rank_dev.p;
+  h->grid.n_h_max = nh_max;
+  h->grid.n_h = h->n_h_dev.p;
+  h->grid.t_high = h->t_high_dev.p;
+  h->grid.trans_low_x0 = 0.f;
+  return NAUTILUS_OK;
+}
+
+int upload_scan_set(NautilusCsm* h, ScanSet& ss, const float* xy, const int64_t* offsets,
+                    int32_t n_scans) {
+  if (n_scans < 0 || (n_scans > 0 && (!offsets))) return fail(NAUTILUS_EINVAL, "bad scan set");
+  const long long total = n_scans > 0 ? offsets[n_scans] : 0;
+  if (n_scans > 0 && offsets[0] != 0) return fail(NAUTILUS_EINVAL, "offsets[0] must be 0");
+  for (int i = 0; i < n_scans; ++i)
+    if (offsets[i + 1] < offsets[i]) return fail(NAUTILUS_EINVAL, "offsets must be non-decreasing");
+  if (total > 0 && !xy) return fail(NAUTILUS_EINVAL, "xy is null");
+  if ((size_t)total > ss.cap_points) {
+    cudaFree(ss.points); ss.points = nullptr; ss.cap_points = 0;
+    CU_TRY(cudaMalloc(&ss.points, sizeof(float2) * std::max<size_t>(total, 1024)));
+    ss.cap_points = std::max<size_t>(total, 1024);
+  }
+  if ((size_t)n_scans + 1 > ss.cap_offsets) {
+    cudaFree(ss.offsets); ss.offsets = nullptr; ss.cap_offsets = 0;
+    CU_TRY(cudaMalloc(&ss.offsets, sizeof(long long) * std::max<size_t>(n_scans + 1, 64)));
+    ss.cap_offsets = std::max<size_t>(n_scans + 1, 64);
+  }
+  ss.host_offsets.assign(n_scans + 1, 0);
+  for (int i = 0; i <= n_scans && n_scans > 0; ++i) ss.host_offsets[i] = offsets[i];
+  if (total > 0)
+    CU_TRY(cudaMemcpyAsync(ss.points, xy, sizeof(float2) * total, cudaMemcpyHostToDevice, h->stream));
+  CU_TRY(cudaMemcpyAsync(ss.offsets, ss.host_offsets.data(), sizeof(long long) * (n_scans + 1),
+                         cudaMemcpyHostToDevice, h->stream));
+  CU_TRY(cudaStreamSynchronize(h->stream));
+  ss.n = n_scans;
+  return NAUTILUS_OK;
+}
+
+cudaEvent_t get_event(NautilusCsm* h, size_t k) {
+  while (h->events.size() <= k) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    h->events.push_back(e);
+  }
+  return h->events[k];
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* nautilus_csm_last_error(void) { return g_error.c_str(); }
+const char* nautilus_csm_version(void) { return "nautilus_csm_b200 sm_100a r1"; }
+
+int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v) {
+  return host_cell(v, resolution, dim);
+}
+
+void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,
+                                  double* rot_min, double* rot_max) {
+  // math_util::AngleDiff / AngleMod (math_util.h:79-88), cc:252-257
+  const double two_pi = 2.0 * M_PI;
+  double d = rot_a - rot_b;
+  d -= two_pi * rint(d / two_pi);
+  double lo = d - restriction / 2;
+  lo -= two_pi * rint(lo / two_pi);
+  double hi = d + restriction / 2;
+  hi -= two_pi * rint(hi / two_pi);
+  if (hi < lo) hi += 2 * M_PI;
+  if (rot_min) *rot_min = lo;
+  if (rot_max) *rot_max = hi;
+}
+
+int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
+  if (!p || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  *out = nullptr;
+  if (!(p->scanner_range > 0) || !(p->low_res > 0) || !(p->high_res > 0) || !(p->trans_range > 0))
+    return fail(NAUTILUS_EINVAL, "ranges and resolutions must be positive");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return fail(NAUTILUS_ECUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
+  if (p->device < 0 || p->device >= n_dev) return fail(NAUTILUS_EINVAL, "bad device ordinal");
+  CU_TRY(cudaSetDevice(p->device));
+  cudaDeviceProp prop;
+  CU_TRY(cudaGetDeviceProperties(&prop, p->device));
+  if (prop.major < 10)
+    return fail(NAUTILUS_ECUDA, "device is not sm_100-class; this library is built for sm_100a only");
+  const double wd = floor((p->scanner_range * 2.0) / p->high_res);  // h:32-35
+  const double wld = floor((p->scanner_range * 2.0) / p->low_res);
+  if (wd < 1 || wd > 30000 || wld < 1 || wld > 65000)
+    return fail(NAUTILUS_EINVAL, "table dimensions out of the supported range");
+  NautilusCsm* h = new NautilusCsm();
+  h->params = *p;
+  h->device = p->device;
+  h->sm_count = prop.multiProcessorCount;
+  h->rot_step = p->rot_step > 0 ? p->rot_step : M_PI / 180;
+  h->geo.w = (int)wd;
+  h->geo.wl = (int)wld;
+  h->geo.res_h = p->high_res;
+  h->geo.res_l = p->low_res;
+  h->geo.bm_stride = (h->geo.w + 31) / 32;
+  h->geo.margin = p->margin_cells < 0 ? -1 : (p->margin_cells == 0 ? 160 : p->margin_cells);
+  // blur(sigma, sigma, 0, true, true): sigma is a float parameter there
+  const float sigma_f = (float)(p->blur_sigma > 0 ? p->blur_sigma : 4.0);
+  if (sigma_f < 0.5f) { delete h; return fail(NAUTILUS_EINVAL, "blur_sigma < 0.5 is a no-op in CImg; unsupported"); }
+  vanvliet_coeffs((double)sigma_f, &h->vv);
+  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete h;
+    return fail(NAUTILUS_ECUDA, "cudaStreamCreate failed");
+  }
+  h->stream = h->own_stream;
+  h->pool_host = make_pool_list(p->scanner_range, p->low_res, p->high_res, (uint64_t)h->geo.w,
+                                (uint64_t)h->geo.wl);
+  h->geo.n_pool = (int)h->pool_host.s.size();
+  int rc = h->pool_dev.upload(h->pool_host);
+  if (!rc) rc = build_search_grid(h);
+  if (rc) { nautilus_csm_destroy(h); return rc; }
+  *out = h;
+  return NAUTILUS_OK;
+}
+
+void nautilus_csm_destroy(NautilusCsm* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  free_slots(h);
+  h->pool_dev.release();
+  h->slots_dev.release(); h->metas_dev.release(); h->dense_scratch.release();
+  h->scalar_scratch.release();
+  h->t_low_dev.release(); h->t_high_dev.release(); h->slot_rank_dev.release(); h->n_h_dev.release();
+  h->user_scans.release(); h->tmp_scans.release();
+  h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();
+  h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
+  for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+int nautilus_csm_set_stream(NautilusCsm* h, void* cuda_stream) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_table_dims(const NautilusCsm* h, uint64_t* w_high, uint64_t* w_low) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  if (w_high) *w_high = (uint64_t)h->geo.w;
+  if (w_low) *w_low = (uint64_t)h->geo.wl;
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* offsets,
+                              int32_t n_scans) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  CU_TRY(cudaSetDevice(h->device));
+  return upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
+}
+
+int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out) {
+  if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  *out = h->timings;
+  return NAUTILUS_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int require_tiling(NautilusCsm* h) {
+  if (!h->pool_host.tiles)
+    return fail(NAUTILUS_EINVAL,
+                "low/high resolution pair whose pooling windows do not tile the grid is not "
+                "supported by the fused normalise+pool kernel");
+  return NAUTILUS_OK;
+}
+
+// Core of GetTransformation for a batch over one scan set.
+int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const int32_t* b_ids,
+                     const double* rot_min, const double* rot_max, int32_t n_pairs,
+                     double* score, float* x, float* y, float* theta, NautilusCsmStats* stats) {
+  if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
+  h->timings = NautilusCsmTimings{};
+  if (n_pairs == 0) return NAUTILUS_OK;
+  if (!a_ids || !b_ids || !rot_min || !rot_max || !score || !x || !y || !theta)
+    return fail(NAUTILUS_EINVAL, "null argument");
+  if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
+  int rc = require_tiling(h);
+  if (rc) return rc;
+  const int n_t = h->grid.n_t, n_tr = n_t * n_t;
+
+  // ---- rotation lists (cc:92-93: double accumulation, used as float), cached
+  // per distinct window; sinf/cosf from the host libm like Rotation2Df does.
+  std::map<std::pair<double, double>, std::pair<int, int>> rot_cache;
+  std::vector<Rotation> rots;
+  std::vector<PairWork> work(n_pairs);
+  int max_rot = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    if (a_ids[p] < 0 || a_ids[p] >= ss.n || b_ids[p] < 0 || b_ids[p] >= ss.n)
+      return fail(NAUTILUS_EINVAL, "scan id out of range");
+    if (ss.host_offsets[a_ids[p] + 1] == ss.host_offsets[a_ids[p]])
+      return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
+    auto key = std::make_pair(rot_min[p], rot_max[p]);
+    auto it = rot_cache.find(key);
+    if (it == rot_cache.end()) {
+      const int begin = (int)rots.size();
+      for (double r = rot_min[p]; r < rot_max[p]; r += h->rot_step) {
+        Rotation ro;
+        ro.theta = (float)r;
+        ro.c = cosf(ro.theta);
+        ro.s = sinf(ro.theta);
+        ro.pad = 0.f;
+        rots.push_back(ro);
+        if (rots.size() > 50000000) return fail(NAUTILUS_EINVAL, "rotation list too large");
+      }
+      it = rot_cache.emplace(key, std::make_pair(begin, (int)rots.size() - begin)).first;
+    }
+    if (it->second.second == 0)
+      return fail(NAUTILUS_EEMPTY, "empty rotation window: the reference does not terminate on it");
+    work[p].a_scan = a_ids[p];
+    work[p].rot_begin = it->second.first;
+    work[p].n_rot = it->second.second;
+    work[p].out_index = p;
+    work[p].pad = 0;
+    max_rot = std::max(max_rot, work[p].n_rot);
+  }
+
+  // ---- group by target: every target's tables are built once per call
+  std::vector<int> order(n_pairs);
+  std::iota(order.begin(), order.end(), 0);
+  std::stable_sort(order.begin(), order.end(), [&](int l, int r) { return b_ids[l] < b_ids[r]; });
+  std::vector<int> targets;       // distinct target scans in order
+  std::vector<int> first_pair;    // index into `sorted` of each target's first pair
+  std::vector<PairWork> sorted(n_pairs);
+  for (int k = 0; k < n_pairs; ++k) {
+    const int p = order[k];
+    if (k == 0 || b_ids[p] != targets.back()) {
+      targets.push_back(b_ids[p]);
+      first_pair.push_back(k);
+    }
+    sorted[k] = work[p];
+    sorted[k].table = (int)targets.size() - 1;  // made wave-relative below
+  }
+  first_pair.push_back(n_pairs);
+  const int n_targets = (int)targets.size();
+
+  rc = ensure_slots(h, n_targets);
+  if (rc) return rc;
+  const int n_slots = h->n_slots;
+  const int n_waves = (n_targets + n_slots - 1) / n_slots;
+  int max_wave_pairs = 0;
+  for (int w = 0; w < n_waves; ++w) {
+    const int t0 = w * n_slots, t1 = std::min(n_targets, t0 + n_slots);
+    for (int k = first_pair[t0]; k < first_pair[t1]; ++k) sorted[k].table -= t0;
+    max_wave_pairs = std::max(max_wave_pairs, first_pair[t1] - first_pair[t0]);
+  }
+
+  // ---- theta chunking: enough blocks to fill the SMs even for a small batch
+  const int target_blocks = h->sm_count * 8;
+  int chunks = std::max(1, std::min(max_rot, (target_blocks + max_wave_pairs - 1) / max_wave_pairs));
+  const int rot_per_chunk = (max_rot + chunks - 1) / chunks;
+  chunks = (max_rot + rot_per_chunk - 1) / rot_per_chunk;
+  SearchBuffers sb;
+  sb.chunks_per_pair = chunks;
+  sb.rot_per_chunk = rot_per_chunk;
+  if ((rc = h->chunk_best_dev.reserve((size_t)max_wave_pairs * chunks * n_tr))) return rc;
+  if ((rc = h->chunk_rot_dev.reserve((size_t)max_wave_pairs * chunks * n_tr))) return rc;
+  sb.chunk_best = h->chunk_best_dev.p;
+  sb.chunk_rot = h->chunk_rot_dev.p;
+
+  // point chunk of the low-res kernel: index lists + accumulators within ~96 KB
+  size_t max_pts = 0;
+  for (int p = 0; p < n_pairs; ++p)
+    max_pts = std::max<size_t>(max_pts, ss.host_offsets[a_ids[p] + 1] - ss.host_offsets[a_ids[p]]);
+  int point_chunk = (int)std::min<size_t>(max_pts, 2048);
+  while (point_chunk > 32 && low_score_smem_bytes(n_t, point_chunk) > 96 * 1024) point_chunk /= 2;
+  const size_t ls_smem = low_score_smem_bytes(n_t, point_chunk);
+  if (ls_smem > 200 * 1024) return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
+
+  if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
+  if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
+  if ((rc = h->rots_dev.reserve(rots.size()))) return rc;
+  if ((rc = h->results_dev.reserve(n_pairs))) return rc;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets.data(), sizeof(int) * n_targets,
+                         cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted.data(), sizeof(PairWork) * n_pairs,
+                         cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
+                         cudaMemcpyHostToDevice, st));
+
+  int launches = 0;
+  size_t ev = 0;
+  CU_TRY(cudaEventRecord(get_event(h, ev++), st));
+  for (int w = 0; w < n_waves; ++w) {
+    const int t0 = w * n_slots, t1 = std::min(n_targets, t0 + n_slots);
+    const int k0 = first_pair[t0], k1 = first_pair[t1];
+    launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
+                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, st, &launches);
+    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
+    launch_low_score(h->geo, h->grid, ss.points, ss.offsets, h->slots_dev.p, h->pairs_dev.p + k0,
+                     h->rots_dev.p, k1 - k0, sb, point_chunk, ls_smem, st);
+    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
+    launch_refine(h->geo, h->grid, h->params.trans_range, ss.points, ss.offsets, h->slots_dev.p,
+                  h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
+                  h->results_dev.p, st);
+    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
+    launches += 2;
+  }
+  CU_TRY(cudaGetLastError());
+  std::vector<PairResult> res(n_pairs);
+  CU_TRY(cudaMemcpyAsync(res.data(), h->results_dev.p, sizeof(PairResult) * n_pairs,
+                         cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+
+  h->timings.launches = launches;
+  h->timings.waves = n_waves;
+  for (int w = 0; w < n_waves; ++w) {
+    float a = 0, b = 0, c = 0;
+    cudaEventElapsedTime(&a, h->events[3 * w], h->events[3 * w + 1]);
+    cudaEventElapsedTime(&b, h->events[3 * w + 1], h->events[3 * w + 2]);
+    cudaEventElapsedTime(&c, h->events[3 * w + 2], h->events[3 * w + 3]);
+    h->timings.ms_tables += a; h->timings.ms_low += b; h->timings.ms_refine += c;
+  }
+  cudaEventElapsedTime(&h->timings.ms_total, h->events[0], h->events[3 * n_waves]);
+
+  int bad = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    score[p] = res[p].score; x[p] = res[p].x; y[p] = res[p].y; theta[p] = res[p].theta;
+    if (stats) { stats[p].n_low = res[p].n_low; stats[p].n_high = res[p].n_high; stats[p].n_pops = res[p].n_pops; }
+    bad |= res[p].pad;
+  }
+  if (bad) return fail(NAUTILUS_EEMPTY, "a pair had nothing to score");
+  return NAUTILUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
+                             const double* rot_min, const double* rot_max, int32_t n_pairs,
+                             double* score, float* x, float* y, float* theta,
+                             NautilusCsmStats* stats) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  CU_TRY(cudaSetDevice(h->device));
+  return match_batch_impl(h, h->user_scans, a_ids, b_ids, rot_min, rot_max, n_pairs, score, x, y,
+                          theta, stats);
+}
+
+int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,
+                       double rot_min, double rot_max, double* score, float* x, float* y,
+                       float* theta, NautilusCsmStats* stats) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  if (na < 0 || nb < 0) return fail(NAUTILUS_EINVAL, "negative point count");
+  if (na == 0) return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
+  CU_TRY(cudaSetDevice(h->device));
+  std::vector<float> xy((size_t)2 * (na + nb));
+  memcpy(xy.data(), a, sizeof(float) * 2 * na);
+  if (nb) memcpy(xy.data() + 2 * na, b, sizeof(float) * 2 * nb);
+  const int64_t offs[3] = {0, na, na + nb};
+  int rc = upload_scan_set(h, h->tmp_scans, xy.data(), offs, 2);
+  if (rc) return rc;
+  const int32_t ia = 0, ib = 1;
+  return match_batch_impl(h, h->tmp_scans, &ia, &ib, &rot_min, &rot_max, 1, score, x, y, theta,
+                          stats);
+}
+
+int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points, double* out_high,
+                               double* out_low) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  if (n_points < 0 || (n_points > 0 && !xy)) return fail(NAUTILUS_EINVAL, "bad cloud");
+  CU_TRY(cudaSetDevice(h->device));
+  int rc = require_tiling(h);
+  if (rc) return rc;
+  const int64_t offs[2] = {0, n_points};
+  if ((rc = upload_scan_set(h, h->tmp_scans, xy, offs, 1))) return rc;
+  if ((rc = ensure_slots(h, 1))) return rc;
+  if ((rc = h->table_scan_dev.reserve(1))) return rc;
+  const int zero = 0;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, &zero, sizeof(int), cudaMemcpyHostToDevice, st));
+  launch_table_wave(h->geo, h->vv, h->tmp_scans.points, h->tmp_scans.offsets, h->table_scan_dev.p,
+                    h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, 1, st, nullptr);
+  const size_t w = h->geo.w, wl = h->geo.wl;
+  if (out_high) {
+    if ((rc = h->dense_scratch.reserve(w * w))) return rc;
+    launch_expand(h->geo, h->slots_dev.p, h->metas_dev.p, 0, h->dense_scratch.p, st);
+    CU_TRY(cudaMemcpyAsync(out_high, h->dense_scratch.p, sizeof(double) * w * w,
+                           cudaMemcpyDeviceToHost, st));
+  }
+  if (out_low)
+    CU_TRY(cudaMemcpyAsync(out_low, h->slots_host[0].low, sizeof(double) * wl * wl,
+                           cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaStreamSynchronize(st));
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_lowres_from_table(NautilusCsm* h, const double* high, uint64_t width,
+                                   uint64_t height, double resolution, double* out_low) {
+  if (!h || !high || !out_low) return fail(NAUTILUS_EINVAL, "null argument");
+  if (width == 0 || height == 0)
+    return fail(NAUTILUS_EINVAL, "empty table (CImg::get_crop throws on an empty image)");
+  if (!(resolution > 0) || width > 30000 || height > 30000) return fail(NAUTILUS_EINVAL, "bad table");
+  CU_TRY(cudaSetDevice(h->device));
+  const NautilusCsmParams& p = h->params;
+  const size_t wl = h->geo.wl;
+  PoolListHost px = make_pool_list(p.scanner_range, p.low_res, resolution, width, wl);
+  PoolListHost py = make_pool_list(p.scanner_range, p.low_res, resolution, height, wl);
+  DevPool dx, dy;
+  int rc = dx.upload(px);
+  if (!rc) rc = dy.upload(py);
+  if (!rc) rc = h->dense_scratch.reserve(width * height + wl * wl);
+  if (rc) { dx.release(); dy.release(); return rc; }
+  cudaStream_t st = h->stream;
+  double* d_hi = h->dense_scratch.p;
+  double* d_low = d_hi + width * height;
+  cudaError_t e = cudaMemcpyAsync(d_hi, high, sizeof(double) * width * height, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_low, 0, sizeof(double) * wl * wl, st);
+  if (e == cudaSuccess) {
+    launch_pool_generic(d_hi, (int)width, (int)height, dx.d, dy.d, d_low, (int)wl, st);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out_low, d_low, sizeof(double) * wl * wl, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  dx.release(); dy.release();
+  if (e != cudaSuccess) return fail(NAUTILUS_ECUDA, cudaGetErrorString(e));
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_build_tables(NautilusCsm* h, const int32_t* scan_ids, int32_t n, double* checksum) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  if (n < 0 || (n > 0 && !scan_ids)) return fail(NAUTILUS_EINVAL, "bad scan id list");
+  CU_TRY(cudaSetDevice(h->device));
+  h->timings = NautilusCsmTimings{};
+  if (n == 0) { if (checksum) *checksum = 0; return NAUTILUS_OK; }
+  ScanSet& ss = h->user_scans;
+  for (int i = 0; i < n; ++i)
+    if (scan_ids[i] < 0 || scan_ids[i] >= ss.n) return fail(NAUTILUS_EINVAL, "scan id out of range");
+  int rc = require_tiling(h);
+  if (rc) return rc;
+  if ((rc = ensure_slots(h, n))) return rc;
+  if ((rc = h->table_scan_dev.reserve(n))) return rc;
+  if ((rc = h->scalar_scratch.reserve(1))) return rc;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, scan_ids, sizeof(int) * n, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemsetAsync(h->scalar_scratch.p, 0, sizeof(double), st));
+  int launches = 0, waves = 0;
+  CU_TRY(cudaEventRecord(get_event(h, 0), st));
+  for (int t0 = 0; t0 < n; t0 += h->n_slots, ++waves) {
+    const int cnt = std::min(n - t0, h->n_slots);
+    launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
+                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, cnt, st, &launches);
+    if (checksum) { launch_low_checksum(h->geo, h->slots_dev.p, cnt, h->scalar_scratch.p, st); ++launches; }
+  }
+  CU_TRY(cudaEventRecord(get_event(h, 1), st));
+  CU_TRY(cudaGetLastError());
+  double cs = 0;
+  CU_TRY(cudaMemcpyAsync(&cs, h->scalar_scratch.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  if (checksum) *checksum = cs;
+  cudaEventElapsedTime(&h->timings.ms_total, h->events[0], h->events[1]);
+  h->timings.ms_tables = h->timings.ms_total;
+  h->timings.launches = launches;
+  h->timings.waves = waves;
+  return NAUTILUS_OK;
+}
+
+}  // extern "C"

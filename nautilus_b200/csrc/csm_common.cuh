@@ -1,0 +1,114 @@
+// Shared device-side definitions for the CSM kernels (sm_100a).
+//
+// Everything numeric in here follows the reference arithmetic restated in
+// SURVEY.md Appendix A; the whole library is compiled with --fmad=false so no
+// multiply-add is contracted, matching the reference build (no -march flag =>
+// no FMA, /root/reference/CMakeLists.txt:11,16).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define CSM_MIN_VALUE_FOR_LOOKUP 1E-10  // CorrelativeScanMatcher.h:20
+#define CSM_EPSILON 1e-6                // CorrelativeScanMatcher.cc:19
+
+namespace csm {
+
+// Van Vliet-Young order-0 coefficients + Triggs-Sdika matrix
+// (CImg.h:49267-49284, 49066-49081); filled on the host.
+struct VanVliet {
+  double B, a1, a2, a3;
+  double M[9];
+};
+
+// Per table-slot metadata, written by the raster kernel.
+struct TableMeta {
+  // occupied box of the scan, in hi-res cells, inclusive; cx1 < cx0 => no point
+  int cx0, cx1, cy0, cy1;
+  // active rectangle the blurred table is computed on (inclusive); the cells
+  // outside it hold values below 1e-20 of the maximum and read as 0
+  int ax0, ax1, ay0, ay1;
+  int stride;    // row stride of the slot's value buffer, in doubles
+  int cropped;   // 1 when the active rectangle is not the whole grid
+  int n_inside;  // points that fell inside the grid
+  int pad;
+  unsigned long long max_key;  // order-preserving keys of the raw max / min
+  unsigned long long min_key;
+};
+
+// One resident table slot.
+struct TableSlot {
+  double* values;      // active rectangle, row-major, stride meta.stride
+  unsigned* bitmap;    // occupied-box bitmap, bm_stride words per row
+  unsigned char* rowflag;  // 1 per occupied-box row that has a point
+  double* low;         // wl*wl low-res values (max-pool of the normalised table)
+  double* lowlog;      // (wl+1)*(wl+1) log(max(low,1e-10)); last row/col = floor
+};
+
+// Grid geometry shared by all kernels.
+struct Geometry {
+  int w;          // hi-res table width = height  (LookupTable ctor, h:32-35)
+  int wl;         // low-res width
+  double res_h;   // high_res_
+  double res_l;   // low_res_
+  int bm_stride;  // bitmap words per row = ceil(w/32)
+  int margin;     // crop margin in cells; <0 => never crop
+  int n_pool;     // number of pooling windows per axis (loop trips of cc:37)
+};
+
+// convertX/convertY (CorrelativeScanMatcher.h:43-49): dim/2 + floor(x/res) in
+// double.  IEEE division (div.rn.f64) => identical to the host result.
+__device__ __forceinline__ long long cell_of(float v, double res, int dim) {
+  const double q = floor(__ddiv_rn((double)v, res));
+  const double c = (double)(dim / 2) + q;
+  if (c < -4.0e18) return -4000000000000000000LL;
+  if (c > 4.0e18) return 4000000000000000000LL;
+  return (long long)c;
+}
+
+// Order-preserving map double -> uint64 (for atomicMax / atomicMin).
+__device__ __forceinline__ unsigned long long order_key(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b & 0x8000000000000000ULL) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __host__ __forceinline__ double key_to_double(unsigned long long k) {
+  unsigned long long b = (k & 0x8000000000000000ULL) ? (k & 0x7FFFFFFFFFFFFFFFULL) : ~k;
+#ifdef __CUDA_ARCH__
+  return __longlong_as_double((long long)b);
+#else
+  double d;
+  memcpy(&d, &b, sizeof(d));
+  return d;
+#endif
+}
+
+// One step of the order-0 recursion, accumulation order of CImg.h:49103-49105:
+// ((x + v1*a1) + v2*a2) + v3*a3, every product and sum rounded separately.
+__device__ __forceinline__ double vv_step(double x, double v1, double v2, double v3,
+                                          double a1, double a2, double a3) {
+  double v0 = __dadd_rn(x, __dmul_rn(v1, a1));
+  v0 = __dadd_rn(v0, __dmul_rn(v2, a2));
+  v0 = __dadd_rn(v0, __dmul_rn(v3, a3));
+  return v0;
+}
+
+// Triggs boundary of CImg.h:49092-49099.  in: v1..v3 = last three causal
+// outputs, iplus = last input sample.  out: w0..w2.
+__device__ __forceinline__ void vv_triggs(const VanVliet& f, double iplus, double v1,
+                                          double v2, double v3, double& w0, double& w1,
+                                          double& w2) {
+  const double sum = __dmul_rn(f.B, f.B);
+  const double den = __dsub_rn(__dsub_rn(__dsub_rn(1.0, f.a1), f.a2), f.a3);
+  const double uplus = __ddiv_rn(iplus, den);
+  const double vplus = __ddiv_rn(uplus, den);
+  const double unp = __dsub_rn(v1, uplus), unp1 = __dsub_rn(v2, uplus),
+               unp2 = __dsub_rn(v3, uplus);
+  const double* M = f.M;
+  w0 = __dmul_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(M[0], unp), __dmul_rn(M[1], unp1)),
+                                     __dmul_rn(M[2], unp2)), vplus), sum);
+  w1 = __dmul_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(M[3], unp), __dmul_rn(M[4], unp1)),
+                                     __dmul_rn(M[5], unp2)), vplus), sum);
+  w2 = __dmul_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(M[6], unp), __dmul_rn(M[7], unp1)),
+                                     __dmul_rn(M[8], unp2)), vplus), sum);
+}
+
+}  // namespace csm

@@ -1,0 +1,85 @@
+// Host-side launch interface of the CSM kernels (implemented in csm_tables.cu
+// and csm_search.cu, driven by csm_capi.cu).
+#pragma once
+#include "csm_common.cuh"
+
+namespace csm {
+
+// 1-D pooling window list of GetLookupTableLowRes (CorrelativeScanMatcher.cc:37-45),
+// device arrays of n entries: hi-res cell window [s, e] (inclusive, after
+// get_crop's swap, may reach outside the grid), destination low-res cell (or
+// -1 when SetPointValue would drop it) and "last writer of its destination".
+struct PoolListDev {
+  int* s;
+  int* e;
+  int* dst;
+  unsigned char* win;
+  int n;
+};
+
+void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
+                       const long long* offsets, const int* scan_ids, TableSlot* slots,
+                       TableMeta* metas, const PoolListDev& pool, int n_tables,
+                       cudaStream_t stream, int* launches);
+void launch_pool_generic(const double* hi, int w, int h, const PoolListDev& px,
+                         const PoolListDev& py, double* low, int wl, cudaStream_t stream);
+void launch_expand(const Geometry& g, const TableSlot* slots, const TableMeta* metas, int t,
+                   double* dense, cudaStream_t stream);
+void launch_low_checksum(const Geometry& g, const TableSlot* slots, int n_tables, double* out,
+                         cudaStream_t stream);
+
+// ---- search ----------------------------------------------------------------
+
+// Search-grid description shared by every pair of a batch; all lists are built
+// on the host with the reference's accumulating-double loops.
+struct SearchGrid {
+  int n_t;               // low-res translations per axis (cc:96-99 trip count)
+  const float* t_low;    // [n_t] (float)x_trans of the low-res grid
+  const int* slot_rank;  // [n_t*n_t] index i*n_t+j -> rank of AbsCoords(x_i,y_j) among slots
+  int n_h_max;           // max hi-res steps per window axis
+  const int* n_h;        // [n_t] hi-res steps of the window opened at low index i
+  const float* t_high;   // [n_t*n_h_max] (float)x_trans of the hi-res steps (cc:126-129)
+  float trans_low_x0;    // unused placeholder for alignment
+};
+
+// Per-pair work item.
+struct PairWork {
+  int a_scan;      // query scan id
+  int table;       // table slot (in the current wave) of the target scan
+  int rot_begin;   // first entry of this pair's rotation list
+  int n_rot;       // rotations in [rot_min, rot_max) (cc:92 trip count)
+  int out_index;   // position in the caller's output arrays
+  int pad;
+};
+
+struct PairResult {
+  double score;
+  float x, y, theta;
+  int pad;
+  long long n_low, n_high, n_pops;
+};
+
+// Rotation list entry: angle as stored ((float)rotation), cosf/sinf from libm.
+struct Rotation {
+  float theta, c, s, pad;
+};
+
+struct SearchBuffers {
+  double* chunk_best;   // [n_pairs][n_chunks_max][n_t*n_t] best score per theta chunk
+  int* chunk_rot;       // same shape: rotation index (within the pair) of that best
+  int chunks_per_pair;  // theta chunks per pair (uniform upper bound)
+  int rot_per_chunk;
+};
+
+void launch_low_score(const Geometry& g, const SearchGrid& sg, const float2* points,
+                      const long long* offsets, const TableSlot* slots, const PairWork* pairs,
+                      const Rotation* rots, int n_pairs, const SearchBuffers& sb,
+                      int point_chunk, size_t smem_bytes, cudaStream_t stream);
+void launch_refine(const Geometry& g, const SearchGrid& sg, double trans_range,
+                   const float2* points, const long long* offsets, const TableSlot* slots,
+                   const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                   int n_pairs, const SearchBuffers& sb, PairResult* results,
+                   cudaStream_t stream);
+size_t low_score_smem_bytes(int n_t, int point_chunk);
+
+}  // namespace csm

@@ -1,0 +1,468 @@
+// Lookup-table construction on sm_100a: rasterise -> Van Vliet IIR blur (x then
+// y) -> normalise -> variable-window max-pool.  Replaces
+//   CorrelativeScanMatcher::GetLookupTable       (CorrelativeScanMatcher.cc:21-30)
+//   LookupTable::GaussianBlur / normalize        (CorrelativeScanMatcher.h:79-87)
+//   CImg::vanvliet / _cimg_recursive_apply       (CImg.h:49248-49314, 49062-49115)
+//   CImg::normalize                              (CImg.h:39499-39517)
+//   CorrelativeScanMatcher::GetLookupTableLowRes (CorrelativeScanMatcher.cc:32-48)
+//
+// Layout.  A scan lights at most ~1e3 of the 4e6 cells and the filter's impulse
+// response falls by 0.716 per cell, so the table is only computed on the
+// "active rectangle" = occupied box of the scan grown by `margin` cells and
+// clipped to the grid (TableMeta).  Inside it the recursion is the reference's,
+// operation for operation; where the rectangle edge coincides with the grid
+// edge the Neumann seed / Triggs boundary are applied exactly, and with
+// margin < 0 the rectangle is the whole grid and the table is bit-identical.
+// The rectangle is stored row-major (x fastest) in the slot's value buffer.
+//
+// All kernels take a wave of tables: blockIdx.y = table slot in the wave.
+#include "csm_common.cuh"
+#include "csm_kernels.h"
+
+namespace csm {
+
+// ---------------------------------------------------------------------------
+// K1  rasterise: cell coordinates, occupied box, active rectangle, bitmap.
+// One block per table.  The "image" the x-pass filters is never materialised:
+// a bit per cell of the occupied box is enough (SetPointValue(p, 1) is
+// idempotent and order-free, CorrelativeScanMatcher.cc:23-25).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) raster_kernel(
+    Geometry g, const float2* __restrict__ points, const long long* __restrict__ offsets,
+    const int* __restrict__ scan_ids, TableSlot* __restrict__ slots,
+    TableMeta* __restrict__ metas) {
+  const int t = blockIdx.x;
+  const int scan = scan_ids[t];
+  const long long p0 = offsets[scan], p1 = offsets[scan + 1];
+  const TableSlot slot = slots[t];
+  __shared__ int s_red[4][8];
+  __shared__ int s_box[5];
+
+  int lo_x = INT_MAX, hi_x = INT_MIN, lo_y = INT_MAX, hi_y = INT_MIN, cnt = 0;
+  for (long long i = p0 + threadIdx.x; i < p1; i += blockDim.x) {
+    const float2 p = points[i];
+    const long long cx = cell_of(p.x, g.res_h, g.w), cy = cell_of(p.y, g.res_h, g.w);
+    if (cx >= 0 && cx < g.w && cy >= 0 && cy < g.w) {
+      lo_x = min(lo_x, (int)cx); hi_x = max(hi_x, (int)cx);
+      lo_y = min(lo_y, (int)cy); hi_y = max(hi_y, (int)cy);
+      ++cnt;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo_x = min(lo_x, __shfl_xor_sync(0xffffffffu, lo_x, o));
+    hi_x = max(hi_x, __shfl_xor_sync(0xffffffffu, hi_x, o));
+    lo_y = min(lo_y, __shfl_xor_sync(0xffffffffu, lo_y, o));
+    hi_y = max(hi_y, __shfl_xor_sync(0xffffffffu, hi_y, o));
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __shared__ int s_cnt[8];
+  if (lane == 0) {
+    s_red[0][warp] = lo_x; s_red[1][warp] = hi_x;
+    s_red[2][warp] = lo_y; s_red[3][warp] = hi_y; s_cnt[warp] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int n = 0;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) {
+      lo_x = min(lo_x, s_red[0][k]); hi_x = max(hi_x, s_red[1][k]);
+      lo_y = min(lo_y, s_red[2][k]); hi_y = max(hi_y, s_red[3][k]);
+      n += s_cnt[k];
+    }
+    TableMeta m;
+    m.n_inside = n;
+    m.pad = 0;
+    if (n == 0) {  // no point inside the grid: the table is all zeros
+      m.cx0 = 0; m.cx1 = -1; m.cy0 = 0; m.cy1 = -1;
+      m.ax0 = 0; m.ax1 = -1; m.ay0 = 0; m.ay1 = -1;
+      m.stride = 0; m.cropped = 1;
+    } else {
+      m.cx0 = lo_x; m.cx1 = hi_x; m.cy0 = lo_y; m.cy1 = hi_y;
+      if (g.margin < 0) {
+        m.ax0 = 0; m.ax1 = g.w - 1; m.ay0 = 0; m.ay1 = g.w - 1;
+      } else {
+        m.ax0 = max(0, lo_x - g.margin); m.ax1 = min(g.w - 1, hi_x + g.margin);
+        m.ay0 = max(0, lo_y - g.margin); m.ay1 = min(g.w - 1, hi_y + g.margin);
+      }
+      m.cropped = !(m.ax0 == 0 && m.ay0 == 0 && m.ax1 == g.w - 1 && m.ay1 == g.w - 1);
+      m.stride = (m.ax1 - m.ax0 + 1 + 3) & ~3;
+    }
+    m.max_key = 0ULL;            // below every key
+    m.min_key = ~0ULL;           // above every key
+    metas[t] = m;
+    s_box[0] = m.cx0; s_box[1] = m.cx1; s_box[2] = m.cy0; s_box[3] = m.cy1; s_box[4] = n;
+  }
+  __syncthreads();
+  const int cx0 = s_box[0], cx1 = s_box[1], cy0 = s_box[2], cy1 = s_box[3];
+
+  // low-res tables start as "all zero" / "all floor"; the pool kernel fills
+  // the cells its windows reach.
+  const double floor_log = log(CSM_MIN_VALUE_FOR_LOOKUP);
+  for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
+  for (int i = threadIdx.x; i < (g.wl + 1) * (g.wl + 1); i += blockDim.x)
+    slot.lowlog[i] = floor_log;
+  if (s_box[4] == 0) return;
+
+  const int rows = cy1 - cy0 + 1, words = ((cx1 - cx0) >> 5) + 1;
+  for (int i = threadIdx.x; i < rows * words; i += blockDim.x)
+    slot.bitmap[(size_t)(i / words) * g.bm_stride + (i % words)] = 0u;
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) slot.rowflag[i] = 0;
+  __syncthreads();
+  for (long long i = p0 + threadIdx.x; i < p1; i += blockDim.x) {
+    const float2 p = points[i];
+    const long long cx = cell_of(p.x, g.res_h, g.w), cy = cell_of(p.y, g.res_h, g.w);
+    if (cx >= 0 && cx < g.w && cy >= 0 && cy < g.w) {
+      const int bx = (int)cx - cx0, by = (int)cy - cy0;
+      atomicOr(&slot.bitmap[(size_t)by * g.bm_stride + (bx >> 5)], 1u << (bx & 31));
+      slot.rowflag[by] = 1;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K2a  x-pass of CImg::blur -> vanvliet(sigma, 0, 'x') (CImg.h:49286-49291).
+// One warp per 32 rows of the occupied box, lane = row.  Rows without a point
+// stay identically zero in the reference and are skipped (the y-pass reads
+// them as zero).  The causal pass starts at the box's first column: every
+// sample left of it is an exact zero in the reference too.  Lanes run their
+// serial recursions 32 columns at a time into a shared-memory tile which the
+// warp then writes out row-contiguously (256 B per row segment).
+// ---------------------------------------------------------------------------
+constexpr int XP_WARPS = 4;
+
+__global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
+    Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas) {
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int group = blockIdx.x * XP_WARPS + warp;
+  const int rows = m.cy1 - m.cy0 + 1;
+  if (group * 32 >= rows) return;
+  const TableSlot slot = slots[t];
+  const int row_local = group * 32 + lane;
+  const bool has_row = row_local < rows && slot.rowflag[row_local] != 0;
+  const unsigned mask = __ballot_sync(0xffffffffu, has_row);
+  if (mask == 0u) return;
+
+  __shared__ double s_tile[XP_WARPS][32][33];
+  double (*tile)[33] = s_tile[warp];
+  double* base = slot.values + (size_t)(m.cy0 + group * 32 - m.ay0) * m.stride;  // row rr adds rr*stride
+  const unsigned* bm = slot.bitmap + (size_t)row_local * g.bm_stride;
+  const int words = ((m.cx1 - m.cx0) >> 5) + 1;
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
+  const double sum = __dmul_rn(f.B, f.B);
+
+  // Neumann seed val[1..3] = data[0] / B (CImg.h:49088-49090): data[0] is
+  // column 0 of the grid, which only a box starting at column 0 can light.
+  double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+  if (m.cx0 == 0 && has_row && (bm[0] & 1u)) v1 = v2 = v3 = __ddiv_rn(1.0, f.B);
+  // iplus = data[N-1] before the causal pass (CImg.h:49085)
+  double iplus = 0.0;
+  if (m.cx1 == g.w - 1 && has_row) {
+    const int b = g.w - 1 - m.cx0;
+    if ((bm[b >> 5] >> (b & 31)) & 1u) iplus = 1.0;
+  }
+
+  // ---- causal pass, columns cx0 .. ax1
+  const int n_fwd = m.ax1 - m.cx0 + 1;
+  for (int c0 = 0; c0 < n_fwd; c0 += 32) {
+    const int nk = min(32, n_fwd - c0);
+    const unsigned word = (has_row && (c0 >> 5) < words) ? bm[c0 >> 5] : 0u;
+#pragma unroll 4
+    for (int k = 0; k < nk; ++k) {
+      const double x = ((word >> k) & 1u) ? 1.0 : 0.0;
+      const double v0 = vv_step(x, v1, v2, v3, a1, a2, a3);
+      tile[lane][k] = v0;
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+    __syncwarp();
+    if (lane < nk) {
+      double* dst = base + (m.cx0 + c0 - m.ax0) + lane;
+      for (int rr = 0; rr < 32; ++rr)
+        if ((mask >> rr) & 1u) dst[(size_t)rr * m.stride] = tile[rr][lane];
+    }
+    __syncwarp();
+  }
+
+  // ---- boundary: Triggs at the grid edge (exact), zero state at a crop edge
+  const bool at_edge = (m.ax1 == g.w - 1);
+  double w0 = 0.0;
+  if (at_edge) {
+    double w1, w2;
+    vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+    v1 = w0; v2 = w1; v3 = w2;  // after the shift of CImg.h:49100
+  } else {
+    v1 = v2 = v3 = 0.0;
+  }
+
+  // ---- anti-causal pass, columns ax1 .. ax0, chunks aligned to cx0
+  // floor division for possibly negative chunk indices
+  const int rel_hi = m.ax1 - m.cx0;            // >= 0
+  const int rel_lo = m.ax0 - m.cx0;            // <= 0
+  const int ch_hi = rel_hi >> 5;
+  const int ch_lo = (rel_lo >= 0) ? (rel_lo >> 5) : -((-rel_lo + 31) >> 5);
+  for (int ch = ch_hi; ch >= ch_lo; --ch) {
+    const int r0 = ch * 32;                     // relative column of tile column 0
+    const int k_lo = max(0, rel_lo - r0), k_hi = min(31, rel_hi - r0);
+    // load the causal outputs (zero left of the box)
+    {
+      const int rel = r0 + lane;
+      const bool in = (lane >= k_lo && lane <= k_hi);
+      const double* src = base + (m.cx0 + rel - m.ax0);
+      for (int rr = 0; rr < 32; ++rr) {
+        double v = 0.0;
+        if (in && rel >= 0 && ((mask >> rr) & 1u)) v = src[(size_t)rr * m.stride];
+        tile[rr][lane] = v;
+      }
+    }
+    __syncwarp();
+    for (int k = k_hi; k >= k_lo; --k) {
+      if (at_edge && r0 + k == rel_hi) {  // data[N-1] = val[0] of the Triggs step
+        tile[lane][k] = w0;
+        continue;
+      }
+      const double v0 = vv_step(__dmul_rn(tile[lane][k], sum), v1, v2, v3, a1, a2, a3);
+      tile[lane][k] = v0;
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+    __syncwarp();
+    if (lane >= k_lo && lane <= k_hi) {
+      double* dst = base + (m.cx0 + r0 + lane - m.ax0);
+      for (int rr = 0; rr < 32; ++rr)
+        if ((mask >> rr) & 1u) dst[(size_t)rr * m.stride] = tile[rr][lane];
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K2b  y-pass of CImg::blur -> vanvliet(sigma, 0, 'y') (CImg.h:49292-49297),
+// fused with the max/min reduction CImg::normalize needs (CImg.h:39505).
+// One thread per column of the active rectangle; consecutive threads touch
+// consecutive addresses on every row.  The causal pass starts at the occupied
+// box's first row (exact zeros above it), runs to the rectangle's last row;
+// the anti-causal pass walks back to the rectangle's first row.
+// ---------------------------------------------------------------------------
+constexpr int YP_THREADS = 128;
+
+__global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
+    Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
+    TableMeta* __restrict__ metas) {
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int aw = m.ax1 - m.ax0 + 1;
+  if ((int)(blockIdx.x * YP_THREADS) >= aw) return;
+  const int col = blockIdx.x * YP_THREADS + threadIdx.x;
+  const bool live = col < aw;
+  const TableSlot slot = slots[t];
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
+  const double sum = __dmul_rn(f.B, f.B);
+  double* colp = slot.values + (live ? col : 0);
+  const unsigned char* flag = slot.rowflag;
+  const size_t stride = (size_t)m.stride;
+
+  double vmax = -INFINITY, vmin = INFINITY;
+  if (live) {
+    // Neumann seed: data[0] = x-pass output on grid row 0 (zero unless the box
+    // starts there and that row has a point).
+    double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+    if (m.cy0 == 0 && flag[0]) {
+      const double x0 = colp[(size_t)(0 - m.ay0) * stride];
+      v1 = v2 = v3 = __ddiv_rn(x0, f.B);
+    }
+    double iplus = 0.0;  // x-pass output on the grid's last row
+    if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
+      iplus = colp[(size_t)(g.w - 1 - m.ay0) * stride];
+
+    // causal pass: rows cy0 .. ay1
+    for (int r = m.cy0; r <= m.ay1; ++r) {
+      double* p = colp + (size_t)(r - m.ay0) * stride;
+      const double x = (r <= m.cy1 && flag[r - m.cy0]) ? *p : 0.0;
+      const double v0 = vv_step(x, v1, v2, v3, a1, a2, a3);
+      *p = v0;
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+    int r = m.ay1;
+    if (m.ay1 == g.w - 1) {  // Triggs boundary at the grid edge
+      double w0, w1, w2;
+      vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+      colp[(size_t)(r - m.ay0) * stride] = w0;
+      vmax = fmax(vmax, w0); vmin = fmin(vmin, w0);
+      v1 = w0; v2 = w1; v3 = w2;
+      --r;
+    } else {
+      v1 = v2 = v3 = 0.0;
+    }
+    // anti-causal pass down to the rectangle's first row
+    for (; r >= m.ay0; --r) {
+      double* p = colp + (size_t)(r - m.ay0) * stride;
+      const double y = (r >= m.cy0) ? *p : 0.0;
+      const double v0 = vv_step(__dmul_rn(y, sum), v1, v2, v3, a1, a2, a3);
+      *p = v0;
+      vmax = fmax(vmax, v0); vmin = fmin(vmin, v0);
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+  }
+  if ((threadIdx.x & 31) == 0 && vmax >= vmin) {
+    atomicMax(&metas[t].max_key, order_key(vmax));
+    atomicMin(&metas[t].min_key, order_key(vmin));
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K3+K4  normalise (CImg::normalize(0,1), CImg.h:39499-39517) fused with
+// GetLookupTableLowRes (CorrelativeScanMatcher.cc:32-48).
+//
+// The reference walks x,y over the low grid with an accumulating double and
+// pools hi-res cells [cX(x), cX(x+low_res)-1]: windows of 9-11 cells that tile
+// the axis (the end of window k is the start of window k+1 because the loop's
+// next x IS x+low_res).  The 1-D window list is built on the host with the
+// reference's own expressions (PoolList); blockIdx.x = window index along y.
+// Each block normalises the rows of its window in place, keeps the per-column
+// maxima in shared memory, then reduces them per x-window.  Normalisation is
+// monotone, so max(normalise(v)) == normalise(max(v)) bit for bit.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double normalise_value(double v, double mn, double range) {
+  // (v - m) / (M - m) * (1 - 0) + 0 ; the last two operations are exact no-ops
+  return __ddiv_rn(__dsub_rn(v, mn), range);
+}
+
+__global__ void __launch_bounds__(256) normalize_pool_kernel(
+    Geometry g, const TableSlot* __restrict__ slots, const TableMeta* __restrict__ metas,
+    const int* __restrict__ pool_s, const int* __restrict__ pool_e,
+    const int* __restrict__ pool_dst, const unsigned char* __restrict__ pool_win) {
+  extern __shared__ double s_colmax[];
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int ky = blockIdx.x;
+  const int rs = max(pool_s[ky], m.ay0), re = min(pool_e[ky], m.ay1);
+  if (rs > re) return;
+  const TableSlot slot = slots[t];
+  const double M = key_to_double(m.max_key);
+  const double mn = m.cropped ? 0.0 : key_to_double(m.min_key);
+  const bool constant = (M == mn);  // CImg fills with min_value (0) in that case
+  const double range = __dsub_rn(M, mn);
+  const int aw = m.ax1 - m.ax0 + 1;
+  for (int c = threadIdx.x; c < aw; c += blockDim.x) {
+    double cm = -INFINITY;
+    double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
+    for (int r = rs; r <= re; ++r, p += m.stride) {
+      const double nv = constant ? 0.0 : normalise_value(*p, mn, range);
+      *p = nv;
+      cm = fmax(cm, nv);
+    }
+    s_colmax[c] = cm;
+  }
+  __syncthreads();
+  const int dy = pool_dst[ky];
+  if (!pool_win[ky] || dy < 0) return;
+  for (int kx = threadIdx.x; kx < g.n_pool; kx += blockDim.x) {
+    const int dx = pool_dst[kx];
+    if (!pool_win[kx] || dx < 0) continue;
+    const int cs = max(pool_s[kx], m.ax0), ce = min(pool_e[kx], m.ax1);
+    if (cs > ce) continue;
+    double mx = 0.0;  // cells outside the grid (Dirichlet) / outside the rectangle
+    for (int c = cs; c <= ce; ++c) mx = fmax(mx, s_colmax[c - m.ax0]);
+    slot.low[(size_t)dy * g.wl + dx] = mx;
+    slot.lowlog[(size_t)dy * (g.wl + 1) + dx] =
+        log(mx <= CSM_MIN_VALUE_FOR_LOOKUP ? CSM_MIN_VALUE_FOR_LOOKUP : mx);
+  }
+}
+
+// Generic GetLookupTableLowRes for caller-made tables (any width/height/values,
+// no normalisation): one thread per (kx, ky) window pair, CImg::get_crop
+// semantics (zero fill outside the image takes part in the max).  Launched in
+// loop order position so that "later window overwrites earlier" is resolved by
+// the host-computed winner flags.
+__global__ void pool_generic_kernel(const double* __restrict__ hi, int w, int h,
+                                    const int* __restrict__ xs, const int* __restrict__ xe,
+                                    const int* __restrict__ xdst,
+                                    const unsigned char* __restrict__ xwin, int nx,
+                                    const int* __restrict__ ys, const int* __restrict__ ye,
+                                    const int* __restrict__ ydst,
+                                    const unsigned char* __restrict__ ywin, int ny,
+                                    double* __restrict__ low, int wl) {
+  const int kx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ky = blockIdx.y;
+  if (kx >= nx || ky >= ny) return;
+  if (!xwin[kx] || !ywin[ky] || xdst[kx] < 0 || ydst[ky] < 0) return;
+  const int x0 = xs[kx], x1 = xe[kx], y0 = ys[ky], y1 = ye[ky];
+  const bool outside = x0 < 0 || y0 < 0 || x1 >= w || y1 >= h;
+  double mx = outside ? 0.0 : -INFINITY;
+  for (int y = max(y0, 0); y <= min(y1, h - 1); ++y)
+    for (int x = max(x0, 0); x <= min(x1, w - 1); ++x)
+      mx = fmax(mx, hi[(size_t)y * w + x]);
+  low[(size_t)ydst[ky] * wl + xdst[kx]] = mx;
+}
+
+// Expands a slot's active rectangle into a dense w*w table (zeros outside).
+__global__ void expand_kernel(Geometry g, const TableSlot* __restrict__ slots,
+                              const TableMeta* __restrict__ metas, int t,
+                              double* __restrict__ dense) {
+  const TableMeta m = metas[t];
+  const TableSlot slot = slots[t];
+  const size_t n = (size_t)g.w * g.w;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % g.w), y = (int)(i / g.w);
+    double v = 0.0;
+    if (x >= m.ax0 && x <= m.ax1 && y >= m.ay0 && y <= m.ay1)
+      v = slot.values[(size_t)(y - m.ay0) * m.stride + (x - m.ax0)];
+    dense[i] = v;
+  }
+}
+
+// Sum of the low-res tables of a wave (checksum for the table-build benchmark).
+__global__ void low_checksum_kernel(Geometry g, const TableSlot* __restrict__ slots,
+                                    int n_tables, double* __restrict__ out) {
+  const int t = blockIdx.x;
+  if (t >= n_tables) return;
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) acc += slots[t].low[i];
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
+}
+
+// ---- launchers --------------------------------------------------------------
+void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
+                       const long long* offsets, const int* scan_ids, TableSlot* slots,
+                       TableMeta* metas, const PoolListDev& pool, int n_tables,
+                       cudaStream_t stream, int* launches) {
+  if (n_tables <= 0) return;
+  raster_kernel<<<n_tables, 256, 0, stream>>>(g, points, offsets, scan_ids, slots, metas);
+  dim3 gx((g.w + XP_WARPS * 32 - 1) / (XP_WARPS * 32), n_tables);
+  xpass_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+  dim3 gy((g.w + YP_THREADS - 1) / YP_THREADS, n_tables);
+  ypass_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  dim3 gn(g.n_pool, n_tables);
+  normalize_pool_kernel<<<gn, 256, sizeof(double) * g.w, stream>>>(
+      g, slots, metas, pool.s, pool.e, pool.dst, pool.win);
+  if (launches) *launches += 4;
+}
+
+void launch_pool_generic(const double* hi, int w, int h, const PoolListDev& px,
+                         const PoolListDev& py, double* low, int wl, cudaStream_t stream) {
+  dim3 grid((px.n + 127) / 128, py.n);
+  pool_generic_kernel<<<grid, 128, 0, stream>>>(hi, w, h, px.s, px.e, px.dst, px.win, px.n,
+                                                py.s, py.e, py.dst, py.win, py.n, low, wl);
+}
+
+void launch_expand(const Geometry& g, const TableSlot* slots, const TableMeta* metas, int t,
+                   double* dense, cudaStream_t stream) {
+  expand_kernel<<<592, 256, 0, stream>>>(g, slots, metas, t, dense);
+}
+
+void launch_low_checksum(const Geometry& g, const TableSlot* slots, int n_tables, double* out,
+                         cudaStream_t stream) {
+  low_checksum_kernel<<<n_tables, 256, 0, stream>>>(g, slots, n_tables, out);
+}
+
+}  // namespace csm
