@@ -1,0 +1,126 @@
+"""ctypes binding of libnautilus_csm_b200.so (include/nautilus_csm.h).
+
+The library is the product; this module only loads it.  There is no CPU
+fallback: if the shared library is missing, or no B200 is visible, calls fail
+loudly (RuntimeError / CsmError).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_DIR = os.path.join(_HERE, "lib")
+LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
+SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu"]
+HEADERS = ["csm_common.cuh", "csm_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
+
+NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+              "--fmad=false", "-Xcompiler", "-fPIC", "-shared"]
+
+
+class CsmError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"nautilus_csm error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("scanner_range", C.c_double), ("trans_range", C.c_double),
+                ("low_res", C.c_double), ("high_res", C.c_double),
+                ("rot_step", C.c_double), ("blur_sigma", C.c_double),
+                ("device", C.c_int32), ("margin_cells", C.c_int32),
+                ("max_tables", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_low", C.c_int64), ("n_high", C.c_int64), ("n_pops", C.c_int64)]
+
+
+class Timings(C.Structure):
+    _fields_ = [("ms_total", C.c_float), ("ms_tables", C.c_float), ("ms_low", C.c_float),
+                ("ms_refine", C.c_float), ("launches", C.c_int32), ("waves", C.c_int32)]
+
+
+EXPORTS = [
+    "nautilus_csm_last_error", "nautilus_csm_version", "nautilus_csm_create",
+    "nautilus_csm_destroy", "nautilus_csm_set_stream", "nautilus_csm_table_dims",
+    "nautilus_csm_cell", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
+    "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
+    "nautilus_csm_match_batch", "nautilus_csm_match", "nautilus_csm_rotation_window",
+    "nautilus_csm_last_timings",
+]
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS]
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile the CUDA library for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    if not force and not needs_build():
+        return LIB_PATH
+    os.makedirs(LIB_DIR, exist_ok=True)
+    cmd = ["nvcc", *NVCC_FLAGS, *[os.path.join(CSRC, s) for s in SOURCES], "-o", LIB_PATH]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                           "g.build()'` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, d, f = C.c_void_p, C.c_double, C.c_float
+    i32, i64, u64 = C.c_int32, C.c_int64, C.c_uint64
+    L.nautilus_csm_last_error.restype = C.c_char_p
+    L.nautilus_csm_version.restype = C.c_char_p
+    L.nautilus_csm_create.argtypes = [C.POINTER(Params), C.POINTER(vp)]
+    L.nautilus_csm_destroy.argtypes = [vp]
+    L.nautilus_csm_destroy.restype = None
+    L.nautilus_csm_set_stream.argtypes = [vp, vp]
+    L.nautilus_csm_table_dims.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
+    L.nautilus_csm_cell.restype = i64
+    L.nautilus_csm_cell.argtypes = [d, u64, f]
+    L.nautilus_csm_upload_scans.argtypes = [vp, vp, vp, i32]
+    L.nautilus_csm_highres_table.argtypes = [vp, vp, i64, vp, vp]
+    L.nautilus_csm_lowres_from_table.argtypes = [vp, vp, u64, u64, d, vp]
+    L.nautilus_csm_build_tables.argtypes = [vp, vp, i32, C.POINTER(d)]
+    L.nautilus_csm_match_batch.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    L.nautilus_csm_match.argtypes = [vp, vp, i64, vp, i64, d, d, C.POINTER(d), C.POINTER(f),
+                                     C.POINTER(f), C.POINTER(f), C.POINTER(Stats)]
+    L.nautilus_csm_rotation_window.restype = None
+    L.nautilus_csm_rotation_window.argtypes = [d, d, d, C.POINTER(d), C.POINTER(d)]
+    L.nautilus_csm_last_timings.argtypes = [vp, C.POINTER(Timings)]
+    _lib = L
+    return L
+
+
+def check(rc: int):
+    if rc != 0:
+        raise CsmError(rc, lib().nautilus_csm_last_error().decode())
+
+
+def ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)

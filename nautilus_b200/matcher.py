@@ -1,0 +1,191 @@
+"""Host-side mirror of the reference's CSM interface over the C ABI.
+
+Names, argument meaning and error behaviour follow
+/root/reference/third_party/csm/src/CorrelativeScanMatcher.h:27-152 so that the
+parity tests read like the reference's own tests
+(third_party/csm/test/correlative_scan_matcher_tests.cc).  All compute goes
+through libnautilus_csm_b200.so; nothing here falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+from ._lib import CsmError, Params, Stats, Timings, check, ptr
+
+MIN_VALUE_FOR_LOOKUP = 1e-10  # CorrelativeScanMatcher.h:20
+
+
+def _cloud(a) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a.reshape(-1, 2)
+
+
+class LookupTable:
+    """struct LookupTable (CorrelativeScanMatcher.h:27-110): a host copy of a table
+    with the reference's world<->cell maps.  Index math is the library's
+    (nautilus_csm_cell), values are a numpy array [height, width] (x fastest)."""
+
+    def __init__(self, range_: float, resolution: float, values: np.ndarray | None = None):
+        self.resolution = float(resolution)
+        dim = int(math.floor((range_ * 2.0) / resolution))  # h:32-35
+        self.width = self.height = dim
+        if values is None:
+            values = np.zeros((dim, dim), dtype=np.float64)
+        self.values = np.ascontiguousarray(values, dtype=np.float64).reshape(self.height, self.width)
+
+    def convertX(self, x) -> int:
+        return int(_lib.lib().nautilus_csm_cell(self.resolution, self.width, np.float32(x)))
+
+    def convertY(self, y) -> int:
+        return int(_lib.lib().nautilus_csm_cell(self.resolution, self.height, np.float32(y)))
+
+    def IsInside(self, point) -> bool:
+        x, y = self.convertX(point[0]), self.convertY(point[1])
+        return 0 <= x < self.width and 0 <= y < self.height
+
+    def GetPointValue(self, point) -> float:
+        x, y = self.convertX(point[0]), self.convertY(point[1])
+        if not (0 <= x < self.width and 0 <= y < self.height) or \
+                self.values[y, x] <= MIN_VALUE_FOR_LOOKUP:
+            return MIN_VALUE_FOR_LOOKUP
+        return float(self.values[y, x])
+
+    def SetPointValue(self, point, value: float) -> None:
+        x, y = self.convertX(point[0]), self.convertY(point[1])
+        if 0 <= x < self.width and 0 <= y < self.height:
+            self.values[y, x] = value
+
+    def GetDebugImage(self) -> np.ndarray:
+        return self.values
+
+    def AbsCoords(self, x: float, y: float) -> int:
+        row = int((self.height // 2 + _round_half_away(y / self.resolution)) * self.width)
+        col = int(self.width // 2 + _round_half_away(x / self.resolution))
+        return row + col
+
+
+def _round_half_away(v: float) -> float:
+    return math.copysign(math.floor(abs(v) + 0.5), v)  # C round()
+
+
+class CorrelativeScanMatcher:
+    """class CorrelativeScanMatcher (CorrelativeScanMatcher.h:112-152) on one B200.
+
+    Extra keyword arguments expose what the reference hard-codes: rot_step
+    (M_PI/180, cc:92), device, margin_cells (see include/nautilus_csm.h)."""
+
+    def __init__(self, scanner_range: float, trans_range: float, low_res: float,
+                 high_res: float, *, rot_step: float = 0.0, device: int = 0,
+                 margin_cells: int = 0, max_tables: int = 0, blur_sigma: float = 0.0):
+        self._L = _lib.lib()
+        self.range_, self.trans_range_ = float(scanner_range), float(trans_range)
+        self.low_res_, self.high_res_ = float(low_res), float(high_res)
+        p = Params(scanner_range, trans_range, low_res, high_res, rot_step, blur_sigma,
+                   device, margin_cells, max_tables, 0)
+        h = C.c_void_p()
+        check(self._L.nautilus_csm_create(C.byref(p), C.byref(h)))
+        self._h = h
+        wh, wl = C.c_uint64(), C.c_uint64()
+        check(self._L.nautilus_csm_table_dims(self._h, C.byref(wh), C.byref(wl)))
+        self.w_high, self.w_low = int(wh.value), int(wl.value)
+        self.n_scans = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.nautilus_csm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream_ptr: int | None):
+        check(self._L.nautilus_csm_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)))
+
+    # ---- tables ------------------------------------------------------------
+    def GetLookupTableHighRes(self, pointcloud) -> LookupTable:
+        pc = _cloud(pointcloud)
+        out = np.empty((self.w_high, self.w_high), dtype=np.float64)
+        check(self._L.nautilus_csm_highres_table(self._h, ptr(pc), len(pc), ptr(out), None))
+        return LookupTable(self.range_, self.high_res_, out)
+
+    def GetLookupTables(self, pointcloud) -> tuple[LookupTable, LookupTable]:
+        """Hi- and low-res tables of one cloud in one device pass."""
+        pc = _cloud(pointcloud)
+        hi = np.empty((self.w_high, self.w_high), dtype=np.float64)
+        lo = np.empty((self.w_low, self.w_low), dtype=np.float64)
+        check(self._L.nautilus_csm_highres_table(self._h, ptr(pc), len(pc), ptr(hi), ptr(lo)))
+        return (LookupTable(self.range_, self.high_res_, hi),
+                LookupTable(self.range_, self.low_res_, lo))
+
+    def GetLookupTableLowRes(self, high_res_table: LookupTable) -> LookupTable:
+        hv = np.ascontiguousarray(high_res_table.values, dtype=np.float64)
+        out = np.empty((self.w_low, self.w_low), dtype=np.float64)
+        check(self._L.nautilus_csm_lowres_from_table(
+            self._h, ptr(hv), high_res_table.width, high_res_table.height,
+            high_res_table.resolution, ptr(out)))
+        return LookupTable(self.range_, self.low_res_, out)
+
+    # ---- matching ----------------------------------------------------------
+    def GetTransformation(self, pointcloud_a, pointcloud_b, rotation_min: float = 0.0,
+                          rotation_max: float = 2 * math.pi, *, with_stats: bool = False):
+        """-> (prob, ((x, y), theta)) like the reference's pair<double, pair<Vector2f, float>>."""
+        a, b = _cloud(pointcloud_a), _cloud(pointcloud_b)
+        s, x, y, t = C.c_double(), C.c_float(), C.c_float(), C.c_float()
+        st = Stats()
+        check(self._L.nautilus_csm_match(self._h, ptr(a), len(a), ptr(b), len(b), rotation_min,
+                                         rotation_max, C.byref(s), C.byref(x), C.byref(y),
+                                         C.byref(t), C.byref(st)))
+        r = (s.value, ((np.float32(x.value), np.float32(y.value)), np.float32(t.value)))
+        return (r, (st.n_low, st.n_high, st.n_pops)) if with_stats else r
+
+    def GetTransformationRestricted(self, pointcloud_a, pointcloud_b, rotation_a: float,
+                                    rotation_b: float, rotation_restriction: float, **kw):
+        """The 5-argument overload (cc:247-264)."""
+        lo, hi = self.rotation_window(rotation_a, rotation_b, rotation_restriction)
+        return self.GetTransformation(pointcloud_a, pointcloud_b, lo, hi, **kw)
+
+    def rotation_window(self, rotation_a, rotation_b, rotation_restriction):
+        lo, hi = C.c_double(), C.c_double()
+        self._L.nautilus_csm_rotation_window(rotation_a, rotation_b, rotation_restriction,
+                                             C.byref(lo), C.byref(hi))
+        return lo.value, hi.value
+
+    # ---- batch API (new; what a batched SolveAutoLC would call) -------------
+    def upload_scans(self, xy, offsets) -> None:
+        xy = _cloud(xy)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        check(self._L.nautilus_csm_upload_scans(self._h, ptr(xy), ptr(offsets), len(offsets) - 1))
+        self.n_scans = len(offsets) - 1
+
+    def match_batch(self, a_ids, b_ids, rot_min, rot_max, *, with_stats: bool = False):
+        a_ids = np.ascontiguousarray(a_ids, dtype=np.int32)
+        b_ids = np.ascontiguousarray(b_ids, dtype=np.int32)
+        n = len(a_ids)
+        rot_min = np.ascontiguousarray(np.broadcast_to(np.asarray(rot_min, np.float64), (n,)))
+        rot_max = np.ascontiguousarray(np.broadcast_to(np.asarray(rot_max, np.float64), (n,)))
+        score = np.empty(n, np.float64)
+        x, y, th = (np.empty(n, np.float32) for _ in range(3))
+        stats = np.zeros((n, 3), np.int64) if with_stats else None
+        check(self._L.nautilus_csm_match_batch(
+            self._h, ptr(a_ids), ptr(b_ids), ptr(rot_min), ptr(rot_max), n, ptr(score), ptr(x),
+            ptr(y), ptr(th), ptr(stats) if with_stats else None))
+        return (score, x, y, th, stats) if with_stats else (score, x, y, th)
+
+    def build_tables(self, scan_ids, *, checksum: bool = True) -> float:
+        ids = np.ascontiguousarray(scan_ids, dtype=np.int32)
+        cs = C.c_double()
+        check(self._L.nautilus_csm_build_tables(self._h, ptr(ids), len(ids),
+                                                C.byref(cs) if checksum else None))
+        return cs.value
+
+    def last_timings(self) -> dict:
+        t = Timings()
+        check(self._L.nautilus_csm_last_timings(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timings._fields_}
