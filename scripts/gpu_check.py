@@ -20,13 +20,13 @@ def rel_err(got, want):
 def main():
     n_pairs = int(sys.argv[1]) if len(sys.argv) > 1 else 6
     pm = port.PortMatcher(30, 2, 0.3, 0.03)
-    a, b, _ = synth.make_pair(0)
-    ph = pm.highres(b)
+    a0, b0, _ = synth.make_pair(0)
+    ph = pm.highres(b0)
     pl = pm.lowres(ph)
     for margin in (-1, 0):
         m = CorrelativeScanMatcher(30, 2, 0.3, 0.03, margin_cells=margin)
         t0 = time.time()
-        hi, lo = m.GetLookupTables(b)
+        hi, lo = m.GetLookupTables(b0)
         dt = time.time() - t0
         eh, el = rel_err(hi.values, ph.values), rel_err(lo.values, pl.values)
         print(f"margin={margin}: hi bit-exact={np.array_equal(hi.values, ph.values)} "

@@ -1,0 +1,166 @@
+"""CPU tests: the oracle port (oracle/csm_oracle.c) against
+  (1) the reference's own 11 unit tests
+      (third_party/csm/test/correlative_scan_matcher_tests.cc:12-106),
+  (2) fixtures generated from the unmodified reference (tests/golden),
+  (3) the unmodified reference itself when oracle/_ref is present.
+Bit-exact throughout: integer/index work and fp64 tables with identical
+operation order."""
+import numpy as np
+import pytest
+
+from nautilus_b200 import synth
+from oracle import port
+
+
+def T(range_, res):
+    return port.PortTable(range_, res)
+
+
+# ---- (1) the reference's unit tests, restated one to one ---------------------
+def test_set_single_point():
+    t = T(4, 1)
+    t.set(0, 0, 0.5)
+    assert t.get(0, 0) == 0.5
+    assert t.get(.5, .5) == 0.5
+    assert t.get(-.5, -.5) < 0.5
+
+
+def test_overwrite_point():
+    t = T(4, 1)
+    t.set(3.9, 3.9, 0.01)
+    assert t.get(3.9, 3.9) == 0.01
+    t.set(-3.9, -3.9, 0.02)
+    assert t.get(-3.9, -3.9) == 0.02
+
+
+def test_nearby_points():
+    t = T(4, 1)
+    t.set(-3.9, -3.9, 0.01)
+    t.set(-3.0, -3.0, 0.275)
+    assert t.get(-3.51, -3.51) == 0.01
+    assert t.get(-3.49, -3.49) == 0.01
+    assert t.get(-2.99, -2.99) == 0.275
+
+
+def test_boundary_edge():
+    t = T(4, 1)
+    t.set(-4, -4, 0.23)
+    assert t.get(-4, -4) == 0.23
+    assert t.get(-4, -3.99) == 0.23
+    t.set(4, -4, 0.24)
+    assert t.get(3.99, -4) < 0.24
+    t.set(3.99, -4, 0.24)
+    assert t.get(3.99, -3.99) == 0.24
+
+
+def test_max_area():
+    t = T(4, 1)
+    for (x, y, v) in [(-3.5, -3, 0.2), (-3, 3, 0.1), (2, -4, 0.4), (2, 2, 0.5), (4, 0, 0.6)]:
+        t.set(x, y, v)
+    assert t.max_area(-4, -3, 3, 1) == 0.2
+
+
+def test_out_of_bounds():
+    t = T(4, 1)
+    t.set(-4, -5, 0.5)
+    assert t.max_area(-4, -4, 4, 4) < 0.5
+
+
+def test_create_low_res_simple():
+    t = T(4, 1)
+    t.set(0, 0, 1)
+    low = port.PortMatcher(4, 4, 1, 1).lowres(t)
+    assert low.get(0, 0) == 1
+
+
+def test_create_low_res():
+    t = T(4, 0.5)
+    t.set(0, 0.1, 0.5)
+    t.set(0, 0.7, 0.56)
+    low = port.PortMatcher(4, 4, 1, 0.5).lowres(t)
+    assert low.get(0, 0) == 0.56
+
+
+def test_low_res_inexpressible_resolution():
+    t = T(0.3, 0.03)
+    t.set(0, 0, 0.5)
+    t.set(0, 0.031, 0.56)
+    low = port.PortMatcher(0.3, 0.3, 0.3, 0.03).lowres(t)
+    assert (low.width, low.height) == (2, 2)
+    assert low.get(0, 0) == 0.56
+
+
+def test_low_res_inexpressible_resolution_second():
+    t = T(0.3, 0.03)
+    t.set(0, 0, 0.5)
+    t.set(0, -0.031, 0.56)
+    t.set(-0.061, -0.031, 0.56)
+    t.set(-0.031, -0.031, 0.75)
+    low = port.PortMatcher(0.3, 0.3, 0.3, 0.03).lowres(t)
+    assert (low.width, low.height) == (2, 2)
+    assert low.get(0, 0) == 0.5
+    assert low.get(-0.03, -0.03) == 0.75
+    assert low.get(-0.03, 0.03) == 1e-10
+    assert low.get(0.0, -0.03) == 0.56
+
+
+# ---- (2) fixtures from the unmodified reference ------------------------------
+def test_tables_match_golden(golden):
+    pm = port.PortMatcher(*golden["small_params"])
+    for k in range(4):
+        hi = pm.highres(golden[f"small_cloud_{k}"])
+        assert np.array_equal(hi.values, golden[f"small_hi_{k}"]), k
+        lo = pm.lowres(hi)
+        assert np.array_equal(lo.values, golden[f"small_lo_{k}"]), k
+
+
+def test_matches_match_golden(golden):
+    pm = port.PortMatcher(*golden["small_params"])
+    for k, row in enumerate(golden["small_match"]):
+        a, b = golden[f"small_a_{k}"], golden[f"small_b_{k}"]
+        r1 = pm.match(a, b, -0.5, 0.5)
+        r2 = pm.match(a, b)
+        got = [r1[0], r1[1], r1[2], r1[3], r2[0], r2[1], r2[2], r2[3]]
+        assert np.array_equal(np.asarray(got, np.float64), row), (k, got, row)
+
+
+def test_std_matches_match_golden(golden):
+    pm = port.PortMatcher(*golden["std_params"])
+    for k, row in enumerate(golden["std_match"]):
+        r = pm.match(golden[f"std_a_{k}"], golden[f"std_b_{k}"], -0.5, 0.5)
+        assert np.array_equal(np.asarray(r, np.float64), row), (k, r, row)
+
+
+def test_restricted_window_golden(golden):
+    pm = port.PortMatcher(*golden["small_params"])
+    a, b = golden["small_a_0"], golden["small_b_0"]
+    for ra, rb, rr, s, x, y, th in golden["small_restricted"]:
+        lo, hi = pm.rotation_window(ra, rb, rr)
+        r = pm.match(a, b, lo, hi)
+        assert np.array_equal(np.asarray(r, np.float64), [s, x, y, th])
+
+
+# ---- (3) live against the unmodified reference -------------------------------
+def test_port_equals_reference_live(ref_lib):
+    rm = ref_lib.RefMatcher(30, 2, 0.3, 0.03)
+    pm = port.PortMatcher(30, 2, 0.3, 0.03)
+    a, b, _ = synth.make_pair(11, n_beams=270)
+    rh = rm.highres(b)
+    ph = pm.highres(b)
+    assert np.array_equal(rh.values(), ph.values)
+    assert np.array_equal(rm.lowres(rh).values(), pm.lowres(ph).values)
+    assert rm.match(a, b, -0.5, 0.5) == pm.match(a, b, -0.5, 0.5)
+
+
+def test_port_edge_inputs(ref_lib):
+    """Empty target, points outside the grid, duplicated clouds (ties)."""
+    rm = ref_lib.RefMatcher(4, 1, 0.5, 0.05)
+    pm = port.PortMatcher(4, 1, 0.5, 0.05)
+    a = np.asarray([[0.5, 0.5], [1.0, -1.0], [-2.0, 0.3]], np.float32)
+    empty = np.zeros((0, 2), np.float32)
+    assert rm.match(a, empty, -0.1, 0.1) == pm.match(a, empty, -0.1, 0.1)
+    far = np.asarray([[10.0, 0.0], [0.0, -9.0], [0.2, 0.1]], np.float32)
+    assert rm.match(a, far, -0.1, 0.1) == pm.match(a, far, -0.1, 0.1)
+    assert rm.match(a, a, -0.2, 0.2) == pm.match(a, a, -0.2, 0.2)
+    with pytest.raises(ValueError):
+        pm.match(empty, a, -0.1, 0.1)
