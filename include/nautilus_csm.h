@@ -134,6 +134,12 @@ int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t
                              int32_t n_pairs, double* score, float* x, float* y,
                              float* theta, NautilusCsmStats* stats);
 
+/* Device-side copy of the last batch's results for a collective that follows on
+ * the same stream (multi-GPU gather): n_pairs records of 48 bytes in caller
+ * order, each { double score; float x, y, theta; int32 status; int64 n_low,
+ * n_high, n_pops; }.  dst_dev is a DEVICE pointer; the copy is stream-ordered. */
+int nautilus_csm_copy_results_dev(NautilusCsm* h, void* dst_dev, int32_t n_pairs);
+
 /* Single pair from host clouds = batch of one (upload + tables + search). */
 int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b,
                        int64_t nb, double rot_min, double rot_max, double* score,

@@ -51,7 +51,7 @@ EXPORTS = [
     "nautilus_csm_destroy", "nautilus_csm_set_stream", "nautilus_csm_table_dims",
     "nautilus_csm_cell", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
     "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
-    "nautilus_csm_match_batch", "nautilus_csm_match", "nautilus_csm_rotation_window",
+    "nautilus_csm_match_batch", "nautilus_csm_copy_results_dev", "nautilus_csm_match", "nautilus_csm_rotation_window",
     "nautilus_csm_last_timings",
 ]
 
@@ -108,6 +108,7 @@ def lib():
     L.nautilus_csm_lowres_from_table.argtypes = [vp, vp, u64, u64, d, vp]
     L.nautilus_csm_build_tables.argtypes = [vp, vp, i32, C.POINTER(d)]
     L.nautilus_csm_match_batch.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    L.nautilus_csm_copy_results_dev.argtypes = [vp, vp, i32]
     L.nautilus_csm_match.argtypes = [vp, vp, i64, vp, i64, d, d, C.POINTER(d), C.POINTER(f),
                                      C.POINTER(f), C.POINTER(f), C.POINTER(Stats)]
     L.nautilus_csm_rotation_window.restype = None

@@ -197,6 +197,8 @@ struct NautilusCsm {
   DevBuf<float> t_low_dev, t_high_dev;
   DevBuf<int> slot_rank_dev, n_h_dev;
   SearchGrid grid{};
+  int grid_rc = 0;          // build_search_grid result; matching needs 0
+  std::string grid_error;
 
   // scans + per-batch buffers
   ScanSet user_scans, tmp_scans;
@@ -208,6 +210,7 @@ struct NautilusCsm {
   DevBuf<int> chunk_rot_dev;
   std::vector<cudaEvent_t> events;
   NautilusCsmTimings timings{};
+  int last_n_pairs = 0;
 };
 
 namespace {
@@ -441,8 +444,16 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
                                 (uint64_t)h->geo.wl);
   h->geo.n_pool = (int)h->pool_host.s.size();
   int rc = h->pool_dev.upload(h->pool_host);
-  if (!rc) rc = build_search_grid(h);
   if (rc) { nautilus_csm_destroy(h); return rc; }
+  // A translation grid the memo cannot index (e.g. trans_range > scanner_range)
+  // only disables matching; the table entry points stay usable.
+  h->grid_rc = build_search_grid(h);
+  if (h->grid_rc == NAUTILUS_ENOMEM || h->grid_rc == NAUTILUS_ECUDA) {
+    rc = h->grid_rc;
+    nautilus_csm_destroy(h);
+    return rc;
+  }
+  if (h->grid_rc) h->grid_error = g_error;
   *out = h;
   return NAUTILUS_OK;
 }
@@ -512,6 +523,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if (!a_ids || !b_ids || !rot_min || !rot_max || !score || !x || !y || !theta)
     return fail(NAUTILUS_EINVAL, "null argument");
   if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
+  if (h->grid_rc) return fail(h->grid_rc, h->grid_error);
   int rc = require_tiling(h);
   if (rc) return rc;
   const int n_t = h->grid.n_t, n_tr = n_t * n_t;
@@ -651,6 +663,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   }
   cudaEventElapsedTime(&h->timings.ms_total, h->events[0], h->events[3 * n_waves]);
 
+  h->last_n_pairs = n_pairs;
   int bad = 0;
   for (int p = 0; p < n_pairs; ++p) {
     score[p] = res[p].score; x[p] = res[p].x; y[p] = res[p].y; theta[p] = res[p].theta;
@@ -673,6 +686,16 @@ int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t
   CU_TRY(cudaSetDevice(h->device));
   return match_batch_impl(h, h->user_scans, a_ids, b_ids, rot_min, rot_max, n_pairs, score, x, y,
                           theta, stats);
+}
+
+int nautilus_csm_copy_results_dev(NautilusCsm* h, void* dst_dev, int32_t n_pairs) {
+  if (!h || !dst_dev) return fail(NAUTILUS_EINVAL, "null argument");
+  if (n_pairs < 0 || n_pairs > h->last_n_pairs)
+    return fail(NAUTILUS_ESTATE, "no batch result of that size is resident");
+  CU_TRY(cudaSetDevice(h->device));
+  CU_TRY(cudaMemcpyAsync(dst_dev, h->results_dev.p, sizeof(PairResult) * (size_t)n_pairs,
+                         cudaMemcpyDeviceToDevice, h->stream));
+  return NAUTILUS_OK;
 }
 
 int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,

@@ -178,6 +178,12 @@ class CorrelativeScanMatcher:
             ptr(y), ptr(th), ptr(stats) if with_stats else None))
         return (score, x, y, th, stats) if with_stats else (score, x, y, th)
 
+    RESULT_BYTES = 48  # record size of nautilus_csm_copy_results_dev
+
+    def copy_results_dev(self, dst_dev_ptr: int, n_pairs: int) -> None:
+        """Stream-ordered device copy of the last batch's result records."""
+        check(self._L.nautilus_csm_copy_results_dev(self._h, C.c_void_p(dst_dev_ptr), n_pairs))
+
     def build_tables(self, scan_ids, *, checksum: bool = True) -> float:
         ids = np.ascontiguousarray(scan_ids, dtype=np.int32)
         cs = C.c_double()
