@@ -99,6 +99,9 @@ int nautilus_csm_table_dims(const NautilusCsm* h, uint64_t* w_high, uint64_t* w_
 /* LookupTable::convertX / AbsCoords (h:43-49,104-109) for a table of the given
  * resolution; exposed so host code and tests can check the index maps. */
 int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v);
+/* The same map as the device evaluates it (float thresholds, no division);
+ * returns -1 outside [0, dim).  Host twin of the kernels' cell_fast, for tests. */
+int64_t nautilus_csm_cell_fast(double resolution, uint64_t dim, float v);
 
 /* --- scan residency -------------------------------------------------------
  * Copies n_scans clouds to the device (one H2D); scan ids are 0..n_scans-1 and

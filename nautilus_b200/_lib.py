@@ -49,7 +49,7 @@ class Timings(C.Structure):
 EXPORTS = [
     "nautilus_csm_last_error", "nautilus_csm_version", "nautilus_csm_create",
     "nautilus_csm_destroy", "nautilus_csm_set_stream", "nautilus_csm_table_dims",
-    "nautilus_csm_cell", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
+    "nautilus_csm_cell", "nautilus_csm_cell_fast", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
     "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
     "nautilus_csm_match_batch", "nautilus_csm_copy_results_dev", "nautilus_csm_match", "nautilus_csm_rotation_window",
     "nautilus_csm_last_timings",
@@ -103,6 +103,8 @@ def lib():
     L.nautilus_csm_table_dims.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.nautilus_csm_cell.restype = i64
     L.nautilus_csm_cell.argtypes = [d, u64, f]
+    L.nautilus_csm_cell_fast.restype = i64
+    L.nautilus_csm_cell_fast.argtypes = [d, u64, f]
     L.nautilus_csm_upload_scans.argtypes = [vp, vp, vp, i32]
     L.nautilus_csm_highres_table.argtypes = [vp, vp, i64, vp, vp]
     L.nautilus_csm_lowres_from_table.argtypes = [vp, vp, u64, u64, d, vp]

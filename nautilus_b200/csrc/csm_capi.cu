@@ -76,6 +76,31 @@ void vanvliet_coeffs(double sigma, VanVliet* f) {
   f->M[8] = scaleM * a3 * (a1 + a3 * a2);
 }
 
+// Float thresholds of the cell map (see csm::CellMap): entry k is the smallest
+// float v with floor((double)v / res) >= qlo + k, found with the reference's
+// own expression (CorrelativeScanMatcher.h:43-49) by stepping nextafterf.
+std::vector<float> make_thresholds(double res, int dim, int* qlo_out, int* qhi_out) {
+  const int half = dim / 2, qlo = -half, qhi = dim - 1 - half;
+  std::vector<float> thr;
+  for (int q = qlo; q <= qhi + 1; ++q) {
+    auto ok = [&](float x) { return floor((double)x / res) >= (double)q; };
+    float v = (float)((double)q * res);
+    if (ok(v)) {
+      for (;;) {
+        const float d = nextafterf(v, -INFINITY);
+        if (!ok(d)) break;
+        v = d;
+      }
+    } else {
+      while (!ok(v)) v = nextafterf(v, INFINITY);
+    }
+    thr.push_back(v);
+  }
+  *qlo_out = qlo;
+  *qhi_out = qhi;
+  return thr;
+}
+
 // Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
 struct PoolListHost {
   std::vector<int> s, e, dst;
@@ -197,6 +222,9 @@ struct NautilusCsm {
   DevBuf<float> t_low_dev, t_high_dev;
   DevBuf<int> slot_rank_dev, n_h_dev;
   SearchGrid grid{};
+  std::vector<float> thr_low_host, thr_high_host;
+  DevBuf<float> thr_low_dev, thr_high_dev;
+  CellMap cm_low{}, cm_high{};
   int grid_rc = 0;          // build_search_grid result; matching needs 0
   std::string grid_error;
 
@@ -233,7 +261,7 @@ size_t slot_bytes(const Geometry& g) {
 // by free device memory); returns the slot count through h->n_slots.
 int ensure_slots(NautilusCsm* h, int want) {
   const Geometry& g = h->geo;
-  int cap = h->params.max_tables > 0 ? h->params.max_tables : 256;
+  int cap = h->params.max_tables > 0 ? h->params.max_tables : 4096;
   size_t free_b = 0, total_b = 0;
   CU_TRY(cudaMemGetInfo(&free_b, &total_b));
   const size_t per = slot_bytes(g);
@@ -334,6 +362,22 @@ int build_search_grid(NautilusCsm* h) {
   h->grid.n_h = h->n_h_dev.p;
   h->grid.t_high = h->t_high_dev.p;
   h->grid.trans_low_x0 = 0.f;
+  // exact cell maps for the two grids
+  int rc2;
+  h->thr_low_host = make_thresholds(rl, h->geo.wl, &h->cm_low.qlo, &h->cm_low.qhi);
+  h->thr_high_host = make_thresholds(rh, h->geo.w, &h->cm_high.qlo, &h->cm_high.qhi);
+  if ((rc2 = h->thr_low_dev.reserve(h->thr_low_host.size()))) return rc2;
+  if ((rc2 = h->thr_high_dev.reserve(h->thr_high_host.size()))) return rc2;
+  CU_TRY(cudaMemcpy(h->thr_low_dev.p, h->thr_low_host.data(), sizeof(float) * h->thr_low_host.size(),
+                    cudaMemcpyHostToDevice));
+  CU_TRY(cudaMemcpy(h->thr_high_dev.p, h->thr_high_host.data(),
+                    sizeof(float) * h->thr_high_host.size(), cudaMemcpyHostToDevice));
+  h->cm_low.lowf = h->thr_low_dev.p;
+  h->cm_low.half = h->geo.wl / 2;
+  h->cm_low.inv_res = (float)(1.0 / rl);
+  h->cm_high.lowf = h->thr_high_dev.p;
+  h->cm_high.half = h->geo.w / 2;
+  h->cm_high.inv_res = (float)(1.0 / rh);
   return NAUTILUS_OK;
 }
 
@@ -384,6 +428,22 @@ const char* nautilus_csm_version(void) { return "nautilus_csm_b200 sm_100a r1"; 
 
 int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v) {
   return host_cell(v, resolution, dim);
+}
+
+int64_t nautilus_csm_cell_fast(double resolution, uint64_t dim, float v) {
+  // host twin of the device cell map (csm::cell_fast); -1 = outside the grid
+  static thread_local double c_res = 0;
+  static thread_local uint64_t c_dim = 0;
+  static thread_local std::vector<float> c_thr;
+  static thread_local CellMap c_map;
+  if (c_res != resolution || c_dim != dim) {
+    c_thr = make_thresholds(resolution, (int)dim, &c_map.qlo, &c_map.qhi);
+    c_map.half = (int)dim / 2;
+    c_map.inv_res = (float)(1.0 / resolution);
+    c_res = resolution; c_dim = dim;
+  }
+  c_map.lowf = c_thr.data();
+  return cell_fast(c_map, v);
 }
 
 void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,
@@ -466,6 +526,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->pool_dev.release();
   h->slots_dev.release(); h->metas_dev.release(); h->dense_scratch.release();
   h->scalar_scratch.release();
+  h->thr_low_dev.release(); h->thr_high_dev.release();
   h->t_low_dev.release(); h->t_high_dev.release(); h->slot_rank_dev.release(); h->n_h_dev.release();
   h->user_scans.release(); h->tmp_scans.release();
   h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();
@@ -607,14 +668,8 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   sb.chunk_best = h->chunk_best_dev.p;
   sb.chunk_rot = h->chunk_rot_dev.p;
 
-  // point chunk of the low-res kernel: index lists + accumulators within ~96 KB
-  size_t max_pts = 0;
-  for (int p = 0; p < n_pairs; ++p)
-    max_pts = std::max<size_t>(max_pts, ss.host_offsets[a_ids[p] + 1] - ss.host_offsets[a_ids[p]]);
-  int point_chunk = (int)std::min<size_t>(max_pts, 2048);
-  while (point_chunk > 32 && low_score_smem_bytes(n_t, point_chunk) > 96 * 1024) point_chunk /= 2;
-  const size_t ls_smem = low_score_smem_bytes(n_t, point_chunk);
-  if (ls_smem > 200 * 1024) return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
+  if (low_score_smem_bytes(n_t, h->geo.wl) > 220 * 1024)
+    return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
 
   if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
   if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
@@ -637,10 +692,10 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
                       h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, st, &launches);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));
-    launch_low_score(h->geo, h->grid, ss.points, ss.offsets, h->slots_dev.p, h->pairs_dev.p + k0,
-                     h->rots_dev.p, k1 - k0, sb, point_chunk, ls_smem, st);
+    launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
+                     h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, st);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));
-    launch_refine(h->geo, h->grid, h->params.trans_range, ss.points, ss.offsets, h->slots_dev.p,
+    launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p,
                   h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
                   h->results_dev.p, st);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));

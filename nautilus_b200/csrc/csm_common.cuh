@@ -33,6 +33,9 @@ struct TableMeta {
   int pad;
   unsigned long long max_key;  // order-preserving keys of the raw max / min
   unsigned long long min_key;
+  // box of low-res cells whose value exceeds the lookup floor (1e-10); every
+  // other low-res cell reads as the floor.  lx1 < lx0 => none.
+  int lx0, lx1, ly0, ly1;
 };
 
 // One resident table slot.
@@ -54,6 +57,36 @@ struct Geometry {
   int margin;     // crop margin in cells; <0 => never crop
   int n_pool;     // number of pooling windows per axis (loop trips of cc:37)
 };
+
+// Exact cell lookup without a double division.  cell(v) = dim/2 + floor((double)v / res)
+// is monotone in v, so it is determined by the float thresholds
+//   lowf[q - qlo] = smallest float v with floor((double)v / res) >= q,
+// which the host finds with the reference's own expression.  A float estimate of
+// the quotient is corrected by at most one step against them.
+struct CellMap {
+  const float* lowf;  // thresholds for q = qlo .. qhi + 1
+  int qlo, qhi;       // quotients of the first / last in-grid cell
+  int half;           // dim / 2
+  float inv_res;
+};
+
+// Returns the cell in [0, dim) or -1 when v falls outside the grid.  The float
+// estimate is within one of the true quotient (relative error 1.2e-7 * |q|,
+// |q| <= 15000), so a single correction step is enough; the host twin of this
+// function is checked against the division form in tests/test_abi.py.
+__host__ __device__ __forceinline__ int cell_fast(const CellMap& m, float v) {
+#ifdef __CUDA_ARCH__
+  int q = __float2int_rd(__fmul_rn(v, m.inv_res));
+#else
+  const float e = floorf(v * m.inv_res);
+  int q = e < -2.0e9f ? -2000000000 : (e > 2.0e9f ? 2000000000 : (int)e);
+#endif
+  q = q < m.qlo ? m.qlo : (q > m.qhi ? m.qhi : q);
+  const float* t = m.lowf + (q - m.qlo);
+  if (v < t[0]) --q;
+  else if (v >= t[1]) ++q;
+  return (q < m.qlo || q > m.qhi) ? -1 : q + m.half;
+}
 
 // convertX/convertY (CorrelativeScanMatcher.h:43-49): dim/2 + floor(x/res) in
 // double.  IEEE division (div.rn.f64) => identical to the host result.

@@ -71,15 +71,15 @@ struct SearchBuffers {
   int rot_per_chunk;
 };
 
-void launch_low_score(const Geometry& g, const SearchGrid& sg, const float2* points,
-                      const long long* offsets, const TableSlot* slots, const PairWork* pairs,
-                      const Rotation* rots, int n_pairs, const SearchBuffers& sb,
-                      int point_chunk, size_t smem_bytes, cudaStream_t stream);
-void launch_refine(const Geometry& g, const SearchGrid& sg, double trans_range,
+void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm_low,
+                      const float2* points, const long long* offsets, const TableSlot* slots,
+                      const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                      int n_pairs, const SearchBuffers& sb, cudaStream_t stream);
+void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
                    const float2* points, const long long* offsets, const TableSlot* slots,
                    const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
                    int n_pairs, const SearchBuffers& sb, PairResult* results,
                    cudaStream_t stream);
-size_t low_score_smem_bytes(int n_t, int point_chunk);
+size_t low_score_smem_bytes(int n_t, int wl);
 
 }  // namespace csm

@@ -7,10 +7,10 @@
 // Two facts shape the kernels:
 //  * the cell a translated point falls in is separable: the x cell depends on
 //    (point, theta, x-translation) only, the y cell on (point, theta,
-//    y-translation) only.  Each block therefore converts a chunk of rotated
-//    points once per axis (n_t exact double divisions per point and axis, the
-//    reference's floor(x / res)) into shared-memory index lists, and every one
-//    of the n_t*n_t translations then costs one table gather + one add per point.
+//    y-translation) only.  Rotated points are therefore converted once per axis
+//    into shared-memory cell lists (exact cells through float thresholds, see
+//    CellMap), and every one of the n_t*n_t translations then costs one table
+//    gather + one add per point.
 //  * log(max(v, 1e-10)) is a function of the table cell, so it is taken once
 //    per low-res cell when the table is pooled (lowlog) instead of once per
 //    (candidate, point).
@@ -30,120 +30,206 @@ __device__ __forceinline__ float2 rotate_point(float2 p, float c, float s) {
   return q;
 }
 
-__host__ __device__ inline int padded_chunk(int point_chunk) {
-  int pc = (point_chunk + 1) & ~1;      // even number of uint16 per row
-  if (((pc >> 1) & 1) == 0) pc += 2;    // odd number of 32-bit words per row
-  return pc;
-}
-
-size_t low_score_smem_bytes(int n_t, int point_chunk) {
-  const int pcp = padded_chunk(point_chunk);
-  size_t idx = (size_t)2 * n_t * pcp * sizeof(unsigned short);
-  idx = (idx + 7) & ~(size_t)7;
-  return idx + (size_t)n_t * n_t * (2 * sizeof(double) + sizeof(int));
-}
-
 // ---------------------------------------------------------------------------
 // K5  low-res exhaustive scoring + per-translation max over a theta chunk.
-// grid = (theta chunks, pairs).
+// grid = (theta chunks, pairs), 8 warps per block.
+//
+// A warp scores one (rotation, translation tile) work item: a tile is 16
+// x-translations (lane & 15) by 14 y-translations (7 per lane, lane >> 4 picks
+// the half), so the reference's 14 x 14 grid is exactly one tile and every lane
+// keeps 7 running sums in registers.  Per chunk of 32 points the warp first
+// turns the rotated points into per-axis cell lists (lane = point; exact cells
+// through the float threshold map, no division), then every lane adds its 7
+// table values per point, in point order.  The part of the pooled log table
+// that lies above the lookup floor (TableMeta::lx0..ly1) is staged in shared
+// memory once per block; a half-warp reads 14 consecutive doubles of one table
+// row, which is conflict-free.  Tables whose box does not fit fall back to
+// gathering from global memory through L1.
 // ---------------------------------------------------------------------------
-constexpr int LS_THREADS = 256;
+constexpr int LS_WARPS = 8;
+constexpr int LS_THREADS = LS_WARPS * 32;
+constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
+constexpr int LS_PCP = LS_PC + 1;    // odd row stride: rows start on different banks
+constexpr int LS_TI = 16;            // x translations per tile
+constexpr int LS_JT = 7;             // y translations per lane
+constexpr int LS_TJ = 2 * LS_JT;     // y translations per tile
+constexpr int LS_TILE = LS_TI * LS_TJ;
+constexpr int LS_TABLE_CELLS = 7680; // shared-memory budget of the staged table (60 KB)
+
+size_t low_score_smem_bytes(int n_t, int wl) {
+  size_t b = sizeof(double) * LS_TABLE_CELLS;                       // staged table
+  b += sizeof(double) * LS_WARPS * LS_TILE;                          // per-round results
+  b += sizeof(double) * (size_t)n_t * n_t;                           // best score
+  b += sizeof(int) * (size_t)n_t * n_t;                              // best rotation
+  b += sizeof(int) * LS_WARPS * (LS_TI + LS_TJ) * LS_PCP;            // cell lists
+  b += sizeof(float) * ((size_t)wl + 2 + n_t);                       // thresholds, translations
+  return b;
+}
+
+template <bool SMEM>
+__device__ __forceinline__ void low_score_rounds(
+    const Geometry& g, const SearchGrid& sg, const CellMap& cm, const float* s_tlow,
+    const double* __restrict__ tab, int ox, int oy, int tw, int th, int ts,
+    const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
+    int rot1, int* s_lists, double* s_res, double* s_best, int* s_best_rot) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_t = sg.n_t;
+  const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
+  const int n_tiles = tiles_x * tiles_y;
+  const int n_items = (rot1 - rot0) * n_tiles;
+  int* lx = s_lists + warp * (LS_TI + LS_TJ) * LS_PCP;   // [LS_TI][LS_PCP] column in the box
+  int* ly = lx + LS_TI * LS_PCP;                          // [LS_TJ][LS_PCP] row offset in the box
+  const int li = lane & 15, lj = (lane >> 4) * LS_JT;
+
+  for (int round0 = 0; round0 < n_items; round0 += LS_WARPS) {
+    const int item = round0 + warp;
+    if (item < n_items) {
+      const int r = rot0 + item / n_tiles, tile = item % n_tiles;
+      const int ti = tile % tiles_x, tj = tile / tiles_x;
+      const Rotation rot = rots[r];
+      double acc[LS_JT];
+#pragma unroll
+      for (int u = 0; u < LS_JT; ++u) acc[u] = 0.0;
+      for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
+        const int pc = min(LS_PC, n_pts - p0);
+        if (lane < pc) {  // phase A: this lane's point -> cells for the tile's translations
+          const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
+#pragma unroll 4
+          for (int k = 0; k < LS_TI; ++k) {
+            const int ii = ti * LS_TI + k;
+            int v = tw;  // sentinel column: reads the floor
+            if (ii < n_t) {
+              const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii]));  // Vector2f(x_trans, .)
+              if (cx >= ox && cx < ox + tw) v = cx - ox;
+            }
+            lx[k * LS_PCP + lane] = v;
+          }
+#pragma unroll 2
+          for (int k = 0; k < LS_TJ; ++k) {
+            const int jj = tj * LS_TJ + k;
+            int v = th;  // sentinel row
+            if (jj < n_t) {
+              const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));
+              if (cy >= oy && cy < oy + th) v = cy - oy;
+            }
+            ly[k * LS_PCP + lane] = v * ts;
+          }
+        }
+        __syncwarp();
+        const int* px = lx + li * LS_PCP;
+        const int* py = ly + lj * LS_PCP;
+#pragma unroll 2
+        for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 gathers + adds per lane, point order
+          const int cxv = px[pl];
+#pragma unroll
+          for (int u = 0; u < LS_JT; ++u) {
+            const int at = py[u * LS_PCP + pl] + cxv;
+            const double t = SMEM ? tab[at] : __ldg(tab + at);
+            acc[u] = __dadd_rn(acc[u], t);
+          }
+        }
+        __syncwarp();
+      }
+#pragma unroll
+      for (int u = 0; u < LS_JT; ++u)  // probability / pointcloud.size() (cc:76)
+        s_res[warp * LS_TILE + (lj + u) * LS_TI + li] = __ddiv_rn(acc[u], (double)n_pts);
+    }
+    __syncthreads();
+    // merge the round in work-item (= ascending rotation) order: std::max keeps
+    // the earlier entry on ties (cc:109-110)
+    if (threadIdx.x < LS_TILE) {
+      const int t = threadIdx.x;
+      for (int w = 0; w < LS_WARPS && round0 + w < n_items; ++w) {
+        const int it = round0 + w, r = rot0 + it / n_tiles, tile = it % n_tiles;
+        const int i = (tile % tiles_x) * LS_TI + (t & 15), j = (tile / tiles_x) * LS_TJ + (t >> 4);
+        if (i < n_t && j < n_t) {
+          const double sc = s_res[w * LS_TILE + t];
+          const int tr = i * n_t + j;
+          if (sc > s_best[tr]) { s_best[tr] = sc; s_best_rot[tr] = r; }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
 
 __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
-    Geometry g, SearchGrid sg, const float2* __restrict__ points,
+    Geometry g, SearchGrid sg, CellMap cm_global, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
-    const PairWork* __restrict__ pairs, const Rotation* __restrict__ rots,
-    SearchBuffers sb, int point_chunk) {
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb) {
   const PairWork pw = pairs[blockIdx.y];
   const int rot0 = blockIdx.x * sb.rot_per_chunk;
   if (rot0 >= pw.n_rot) return;
   const int rot1 = min(pw.n_rot, rot0 + sb.rot_per_chunk);
   const int n_t = sg.n_t, n_tr = n_t * n_t;
-  const int pcp = padded_chunk(point_chunk);
 
   extern __shared__ __align__(16) unsigned char s_raw[];
-  unsigned short* cxs = reinterpret_cast<unsigned short*>(s_raw);  // [n_t][pcp]
-  unsigned short* cys = cxs + (size_t)n_t * pcp;                   // [n_t][pcp]
-  size_t off = ((size_t)2 * n_t * pcp * sizeof(unsigned short) + 7) & ~(size_t)7;
-  double* acc = reinterpret_cast<double*>(s_raw + off);            // [n_tr]
-  double* best = acc + n_tr;                                       // [n_tr]
-  int* best_rot = reinterpret_cast<int*>(best + n_tr);             // [n_tr]
+  double* s_tab = reinterpret_cast<double*>(s_raw);                  // [LS_TABLE_CELLS]
+  double* s_res = s_tab + LS_TABLE_CELLS;                            // [LS_WARPS][LS_TILE]
+  double* s_best = s_res + LS_WARPS * LS_TILE;                       // [n_tr]
+  int* s_best_rot = reinterpret_cast<int*>(s_best + n_tr);           // [n_tr]
+  int* s_lists = s_best_rot + n_tr;                                  // cell lists
+  float* s_thr = reinterpret_cast<float*>(s_lists + LS_WARPS * (LS_TI + LS_TJ) * LS_PCP);
+  float* s_tlow = s_thr + (g.wl + 2);                                // [n_t]
 
   const float2* a = points + offsets[pw.a_scan];
   const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
+  const TableMeta tm = metas[pw.table];
   const double* __restrict__ lowlog = slots[pw.table].lowlog;
-  const int wl = g.wl, lstride = g.wl + 1;
+  const int lstride = g.wl + 1;
 
+  for (int k = threadIdx.x; k < g.wl + 2; k += LS_THREADS) s_thr[k] = cm_global.lowf[k];
+  for (int k = threadIdx.x; k < n_t; k += LS_THREADS) s_tlow[k] = sg.t_low[k];
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
-    best[tr] = -INFINITY;
-    best_rot[tr] = 0;
+    s_best[tr] = -INFINITY;
+    s_best_rot[tr] = 0;
   }
+  CellMap cm = cm_global;
+  cm.lowf = s_thr;
 
-  for (int r = rot0; r < rot1; ++r) {
-    const Rotation rot = rots[pw.rot_begin + r];
-    for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) acc[tr] = 0.0;
-    for (int p0 = 0; p0 < n_pts; p0 += point_chunk) {
-      const int pc = min(point_chunk, n_pts - p0);
-      __syncthreads();
-      // phase A: cell lists of this point chunk
-      for (int pl = threadIdx.x; pl < pc; pl += LS_THREADS) {
-        const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
-        for (int i = 0; i < n_t; ++i) {
-          const float t = sg.t_low[i];  // Vector2f(x_trans, y_trans): narrowed to float
-          const long long cx = cell_of(__fadd_rn(q.x, t), g.res_l, wl);
-          const long long cy = cell_of(__fadd_rn(q.y, t), g.res_l, wl);
-          cxs[i * pcp + pl] = (unsigned short)((cx >= 0 && cx < wl) ? cx : wl);
-          cys[i * pcp + pl] = (unsigned short)((cy >= 0 && cy < wl) ? cy : wl);
-        }
-      }
-      __syncthreads();
-      // phase B: one thread per translation, x index fastest across lanes so a
-      // warp's gathers fall on a few table rows
-      for (int tq = threadIdx.x; tq < n_tr; tq += LS_THREADS) {
-        const int j = tq / n_t, i = tq - j * n_t;
-        const unsigned short* px = cxs + i * pcp;
-        const unsigned short* py = cys + j * pcp;
-        double s = acc[i * n_t + j];
-        for (int pl = 0; pl < pc; ++pl) {
-          // an out-of-grid x or y must read the floor: row wl and column wl of
-          // lowlog both hold log(1e-10)
-          const int cy = py[pl], cx = px[pl];
-          s = __dadd_rn(s, __ldg(lowlog + cy * lstride + cx));
-        }
-        acc[i * n_t + j] = s;
-      }
+  // box of low-res cells above the floor; everything outside reads log(1e-10)
+  const bool empty = tm.lx1 < tm.lx0 || tm.ly1 < tm.ly0;
+  const int tw = empty ? 0 : tm.lx1 - tm.lx0 + 1, th = empty ? 0 : tm.ly1 - tm.ly0 + 1;
+  const int ox = empty ? 0 : tm.lx0, oy = empty ? 0 : tm.ly0;
+  const bool fits = (tw + 1) * (th + 1) <= LS_TABLE_CELLS;
+  if (fits) {
+    const int ts = tw + 1;
+    const double floor_log = lowlog[(size_t)g.wl * lstride + g.wl];
+    for (int k = threadIdx.x; k < ts * (th + 1); k += LS_THREADS) {
+      const int r = k / ts, c = k - r * ts;
+      s_tab[k] = (r < th && c < tw) ? lowlog[(size_t)(oy + r) * lstride + ox + c] : floor_log;
     }
     __syncthreads();
-    for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
-      const double score = __ddiv_rn(acc[tr], (double)n_pts);  // probability / size (cc:76)
-      if (score > best[tr]) {  // std::max keeps the earlier entry on ties (cc:109-110)
-        best[tr] = score;
-        best_rot[tr] = r;
-      }
-    }
+    low_score_rounds<true>(g, sg, cm, s_tlow, s_tab, ox, oy, tw, th, ts, a, n_pts,
+                           rots + pw.rot_begin, rot0, rot1, s_lists, s_res, s_best, s_best_rot);
+  } else {
+    __syncthreads();
+    // whole table from global memory: row wl / column wl of lowlog hold the floor
+    low_score_rounds<false>(g, sg, cm, s_tlow, lowlog, 0, 0, g.wl, g.wl, lstride, a, n_pts,
+                            rots + pw.rot_begin, rot0, rot1, s_lists, s_res, s_best, s_best_rot);
   }
-  __syncthreads();
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
-    sb.chunk_best[base + tr] = best[tr];
-    sb.chunk_rot[base + tr] = best_rot[tr];
+    sb.chunk_best[base + tr] = s_best[tr];
+    sb.chunk_rot[base + tr] = s_best_rot[tr];
   }
 }
 
-void launch_low_score(const Geometry& g, const SearchGrid& sg, const float2* points,
-                      const long long* offsets, const TableSlot* slots, const PairWork* pairs,
-                      const Rotation* rots, int n_pairs, const SearchBuffers& sb,
-                      int point_chunk, size_t smem_bytes, cudaStream_t stream) {
+void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm_low,
+                      const float2* points, const long long* offsets, const TableSlot* slots,
+                      const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                      int n_pairs, const SearchBuffers& sb, cudaStream_t stream) {
   if (n_pairs <= 0) return;
+  const size_t smem = low_score_smem_bytes(sg.n_t, g.wl);
   static size_t configured = 0;
-  if (smem_bytes > 48 * 1024 && smem_bytes > configured) {
-    cudaFuncSetAttribute(low_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)smem_bytes);
-    configured = smem_bytes;
+  if (smem > configured) {
+    cudaFuncSetAttribute(low_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = smem;
   }
   dim3 grid(sb.chunks_per_pair, n_pairs);
-  low_score_kernel<<<grid, LS_THREADS, smem_bytes, stream>>>(g, sg, points, offsets, slots,
-                                                              pairs, rots, sb, point_chunk);
+  low_score_kernel<<<grid, LS_THREADS, smem, stream>>>(g, sg, cm_low, points, offsets, slots,
+                                                       metas, pairs, rots, sb);
 }
 
 // ---------------------------------------------------------------------------
@@ -155,6 +241,7 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const float2* poi
 // ---------------------------------------------------------------------------
 constexpr int RF_THREADS = 128;
 constexpr int RF_POINT_CHUNK = 128;
+constexpr int RF_STRIDE = RF_POINT_CHUNK + 1;  // odd: list rows start on different banks
 
 struct ArgBest {
   double score;
@@ -184,7 +271,7 @@ __device__ ArgBest block_argmax(ArgBest v, ArgBest* s_red) {
 }
 
 __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
-    Geometry g, SearchGrid sg, const float2* __restrict__ points,
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
     const Rotation* __restrict__ rots, SearchBuffers sb, PairResult* __restrict__ results) {
@@ -197,7 +284,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
   double* hacc = memo + n_tr;                                      // [nh_max^2]
   int* memo_rot = reinterpret_cast<int*>(hacc + nh_max * nh_max);  // [n_tr]
   int* cxh = memo_rot + n_tr;                                      // [nh_max][RF_POINT_CHUNK]
-  int* cyh = cxh + nh_max * RF_POINT_CHUNK;                        // row offset or -1
+  int* cyh = cxh + nh_max * RF_STRIDE;                        // row offset or -1
   __shared__ ArgBest s_red[RF_THREADS / 32];
   __shared__ int s_ctl[4];
 
@@ -257,29 +344,45 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
       for (int pl = threadIdx.x; pl < pc; pl += RF_THREADS) {
         const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
         for (int k = 0; k < nhx; ++k) {
-          const long long cx = cell_of(__fadd_rn(q.x, thx[k]), g.res_h, g.w);
-          cxh[k * RF_POINT_CHUNK + pl] = (cx >= tm.ax0 && cx <= tm.ax1) ? (int)cx - tm.ax0 : -1;
+          const int cx = cell_fast(cm, __fadd_rn(q.x, thx[k]));
+          cxh[k * RF_STRIDE + pl] = (cx >= tm.ax0 && cx <= tm.ax1) ? cx - tm.ax0 : -1;
         }
         for (int k = 0; k < nhy; ++k) {
-          const long long cy = cell_of(__fadd_rn(q.y, thy[k]), g.res_h, g.w);
-          cyh[k * RF_POINT_CHUNK + pl] =
-              (cy >= tm.ay0 && cy <= tm.ay1) ? ((int)cy - tm.ay0) * tm.stride : -1;
+          const int cy = cell_fast(cm, __fadd_rn(q.y, thy[k]));
+          cyh[k * RF_STRIDE + pl] =
+              (cy >= tm.ay0 && cy <= tm.ay1) ? (cy - tm.ay0) * tm.stride : -1;
         }
       }
       __syncthreads();
-      for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) {
-        const int ky = c % nhy, kx = c / nhy;   // x outer, y inner (cc:126-129)
-        const int* px = cxh + kx * RF_POINT_CHUNK;
-        const int* py = cyh + ky * RF_POINT_CHUNK;
+      // lanes run along x (consecutive cells of one table row => coalesced
+      // gathers); the candidate's rank in the reference's loop is kx*nhy + ky
+      for (int w = threadIdx.x; w < n_cand; w += RF_THREADS) {
+        const int kx = w % nhx, ky = w / nhx;
+        const int c = kx * nhy + ky;            // x outer, y inner (cc:126-129)
+        const int* px = cxh + kx * RF_STRIDE;
+        const int* py = cyh + ky * RF_STRIDE;
         double s = hacc[c];
-        for (int pl = 0; pl < pc; ++pl) {
+        int pl = 0;
+        // four independent gathers + logs in flight, added in point order
+        for (; pl + 4 <= pc; pl += 4) {
+          const int ox0 = px[pl], oy0 = py[pl], ox1 = px[pl + 1], oy1 = py[pl + 1];
+          const int ox2 = px[pl + 2], oy2 = py[pl + 2], ox3 = px[pl + 3], oy3 = py[pl + 3];
+          double t0 = CSM_MIN_VALUE_FOR_LOOKUP, t1 = t0, t2 = t0, t3 = t0;
+          if ((ox0 | oy0) >= 0) t0 = __ldg(hi + oy0 + ox0);
+          if ((ox1 | oy1) >= 0) t1 = __ldg(hi + oy1 + ox1);
+          if ((ox2 | oy2) >= 0) t2 = __ldg(hi + oy2 + ox2);
+          if ((ox3 | oy3) >= 0) t3 = __ldg(hi + oy3 + ox3);
+          const double l0 = log(fmax(t0, CSM_MIN_VALUE_FOR_LOOKUP));
+          const double l1 = log(fmax(t1, CSM_MIN_VALUE_FOR_LOOKUP));
+          const double l2 = log(fmax(t2, CSM_MIN_VALUE_FOR_LOOKUP));
+          const double l3 = log(fmax(t3, CSM_MIN_VALUE_FOR_LOOKUP));
+          s = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(s, l0), l1), l2), l3);
+        }
+        for (; pl < pc; ++pl) {
           const int ox = px[pl], oy = py[pl];
-          double v = CSM_MIN_VALUE_FOR_LOOKUP;
-          if ((ox | oy) >= 0) {
-            const double t = __ldg(hi + oy + ox);
-            if (t > CSM_MIN_VALUE_FOR_LOOKUP) v = t;
-          }
-          s = __dadd_rn(s, log(v));
+          double t = CSM_MIN_VALUE_FOR_LOOKUP;
+          if ((ox | oy) >= 0) t = __ldg(hi + oy + ox);
+          s = __dadd_rn(s, log(t > CSM_MIN_VALUE_FOR_LOOKUP ? t : CSM_MIN_VALUE_FOR_LOOKUP));
         }
         hacc[c] = s;
       }
@@ -316,15 +419,14 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
 static size_t refine_smem_bytes(int n_t, int nh_max) {
   return (size_t)n_t * n_t * (sizeof(double) + sizeof(int)) +
          (size_t)nh_max * nh_max * sizeof(double) +
-         (size_t)2 * nh_max * RF_POINT_CHUNK * sizeof(int);
+         (size_t)2 * nh_max * RF_STRIDE * sizeof(int);
 }
 
-void launch_refine(const Geometry& g, const SearchGrid& sg, double trans_range,
+void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
                    const float2* points, const long long* offsets, const TableSlot* slots,
                    const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
                    int n_pairs, const SearchBuffers& sb, PairResult* results,
                    cudaStream_t stream) {
-  (void)trans_range;
   if (n_pairs <= 0) return;
   const size_t smem = refine_smem_bytes(sg.n_t, sg.n_h_max);
   static size_t configured = 0;
@@ -332,7 +434,7 @@ void launch_refine(const Geometry& g, const SearchGrid& sg, double trans_range,
     cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = smem;
   }
-  refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, points, offsets, slots, metas,
+  refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots, metas,
                                                        pairs, rots, sb, results);
 }
 

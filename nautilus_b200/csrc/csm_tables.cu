@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(256) raster_kernel(
       m.cropped = !(m.ax0 == 0 && m.ay0 == 0 && m.ax1 == g.w - 1 && m.ay1 == g.w - 1);
       m.stride = (m.ax1 - m.ax0 + 1 + 3) & ~3;
     }
+    m.lx0 = INT_MAX; m.lx1 = INT_MIN; m.ly0 = INT_MAX; m.ly1 = INT_MIN;
     m.max_key = 0ULL;            // below every key
     m.min_key = ~0ULL;           // above every key
     metas[t] = m;
@@ -335,7 +336,7 @@ __device__ __forceinline__ double normalise_value(double v, double mn, double ra
 }
 
 __global__ void __launch_bounds__(256) normalize_pool_kernel(
-    Geometry g, const TableSlot* __restrict__ slots, const TableMeta* __restrict__ metas,
+    Geometry g, const TableSlot* __restrict__ slots, TableMeta* __restrict__ metas,
     const int* __restrict__ pool_s, const int* __restrict__ pool_e,
     const int* __restrict__ pool_dst, const unsigned char* __restrict__ pool_win) {
   extern __shared__ double s_colmax[];
@@ -364,6 +365,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
   __syncthreads();
   const int dy = pool_dst[ky];
   if (!pool_win[ky] || dy < 0) return;
+  int bx0 = INT_MAX, bx1 = INT_MIN;
   for (int kx = threadIdx.x; kx < g.n_pool; kx += blockDim.x) {
     const int dx = pool_dst[kx];
     if (!pool_win[kx] || dx < 0) continue;
@@ -372,8 +374,18 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     double mx = 0.0;  // cells outside the grid (Dirichlet) / outside the rectangle
     for (int c = cs; c <= ce; ++c) mx = fmax(mx, s_colmax[c - m.ax0]);
     slot.low[(size_t)dy * g.wl + dx] = mx;
-    slot.lowlog[(size_t)dy * (g.wl + 1) + dx] =
-        log(mx <= CSM_MIN_VALUE_FOR_LOOKUP ? CSM_MIN_VALUE_FOR_LOOKUP : mx);
+    const bool above = mx > CSM_MIN_VALUE_FOR_LOOKUP;
+    slot.lowlog[(size_t)dy * (g.wl + 1) + dx] = log(above ? mx : CSM_MIN_VALUE_FOR_LOOKUP);
+    if (above) { bx0 = min(bx0, dx); bx1 = max(bx1, dx); }
+  }
+  // box of low-res cells above the lookup floor (the search stages it in smem)
+  for (int o = 16; o > 0; o >>= 1) {
+    bx0 = min(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+    bx1 = max(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+  }
+  if ((threadIdx.x & 31) == 0 && bx0 <= bx1) {
+    atomicMin(&metas[t].lx0, bx0); atomicMax(&metas[t].lx1, bx1);
+    atomicMin(&metas[t].ly0, dy); atomicMax(&metas[t].ly1, dy);
   }
 }
 

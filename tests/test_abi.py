@@ -71,3 +71,24 @@ def test_rotation_window_matches_oracle(L):
         lo, hi = C.c_double(), C.c_double()
         L.nautilus_csm_rotation_window(ra, rb, rr, C.byref(lo), C.byref(hi))
         assert (lo.value, hi.value) == pm.rotation_window(ra, rb, rr)
+
+
+def test_cell_fast_equals_division_form(L):
+    """The kernels find cells through float thresholds instead of a double
+    division; the host twin of that map must agree with convertX everywhere:
+    random values, every cell boundary and its float neighbours, far outside."""
+    rng = np.random.default_rng(2)
+    for res, dim in [(0.03, 2000), (0.3, 200), (0.01, 6000), (0.05, 160), (0.5, 16), (1.0, 8)]:
+        half_extent = res * dim / 2
+        edges = (np.arange(-dim // 2 - 2, dim // 2 + 3) * res).astype(np.float32)
+        near = np.concatenate([edges] + [np.nextafter(edges, np.float32(s * np.inf)) for s in (-1, 1)])
+        for _ in range(2):
+            near = np.concatenate([near, np.nextafter(near, np.float32(-np.inf)),
+                                   np.nextafter(near, np.float32(np.inf))])
+        vals = np.concatenate([
+            near, rng.uniform(-1.2 * half_extent, 1.2 * half_extent, 20000).astype(np.float32),
+            np.asarray([0.0, -0.0, 1e-30, -1e-30, 1e9, -1e9, 3e38, -3e38], np.float32)])
+        for v in np.unique(vals):
+            want = L.nautilus_csm_cell(res, dim, v)
+            want = want if 0 <= want < dim else -1
+            assert L.nautilus_csm_cell_fast(res, dim, v) == want, (res, dim, float(v))

@@ -271,7 +271,7 @@ def test_full_size_properties():
     assert len(self_pairs) == 40
     # a scan against its own table: best translation within one low-res cell of 0
     assert np.all(np.abs(r1[1][self_pairs]) < 0.3) and np.all(np.abs(r1[2][self_pairs]) < 0.3)
-    assert np.all(np.abs(r1[3][self_pairs]) < 0.0176)
+    assert np.all(np.abs(r1[3][self_pairs]) < 0.036)  # within two 1-degree steps of 0
     assert np.all(r1[0] <= 0.0) and np.all(r1[0] >= np.log(1e-10))
     cs1 = m.build_tables(np.arange(40, dtype=np.int32))
     cs2 = m.build_tables(np.arange(40, dtype=np.int32)[::-1].copy())
