@@ -668,6 +668,8 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   sb.chunk_best = h->chunk_best_dev.p;
   sb.chunk_rot = h->chunk_rot_dev.p;
 
+  if ((size_t)(h->geo.wl + 1) * (h->geo.wl + 1) > 65535)
+    return fail(NAUTILUS_EINVAL, "low-res grid too large for the 16-bit row offsets of the search");
   if (low_score_smem_bytes(n_t, h->geo.wl) > 220 * 1024)
     return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
 

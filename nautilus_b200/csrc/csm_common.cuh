@@ -71,16 +71,26 @@ struct CellMap {
 };
 
 // Returns the cell in [0, dim) or -1 when v falls outside the grid.  The float
-// estimate is within one of the true quotient (relative error 1.2e-7 * |q|,
-// |q| <= 15000), so a single correction step is enough; the host twin of this
-// function is checked against the division form in tests/test_abi.py.
+// estimate e = v * (float)(1/res) is within |q| * 1.2e-7 <= 2e-3 of the true
+// quotient (|q| <= 15000, enforced by create()), so it is only ambiguous when
+// its fractional part is within CELL_EPS of an integer; only then (and at the
+// grid edge) are the thresholds consulted, and one correction step suffices.
+// The host twin of this function is checked against the division form in
+// tests/test_abi.py.
+#define CSM_CELL_EPS 4e-3f
 __host__ __device__ __forceinline__ int cell_fast(const CellMap& m, float v) {
 #ifdef __CUDA_ARCH__
-  int q = __float2int_rd(__fmul_rn(v, m.inv_res));
+  const float e = __fmul_rn(v, m.inv_res);
+  int q = __float2int_rd(e);  // saturating
 #else
-  const float e = floorf(v * m.inv_res);
-  int q = e < -2.0e9f ? -2000000000 : (e > 2.0e9f ? 2000000000 : (int)e);
+  const float e = v * m.inv_res;
+  const float fl0 = floorf(e);
+  int q = !(fl0 > -2.0e9f) ? -2147483647 - 1 : (fl0 > 2.0e9f ? 2147483647 : (int)fl0);
 #endif
+  const float fr = e - (float)q;  // exact while |q| < 2^24; irrelevant once saturated
+  // strictly inside the grid and clear of both cell boundaries: the estimate is the cell
+  const bool inside = (unsigned)(q - m.qlo - 1) < (unsigned)(m.qhi - m.qlo - 1);
+  if (inside && fabsf(fr - 0.5f) < 0.5f - CSM_CELL_EPS) return q + m.half;
   q = q < m.qlo ? m.qlo : (q > m.qhi ? m.qhi : q);
   const float* t = m.lowf + (q - m.qlo);
   if (v < t[0]) --q;

@@ -55,16 +55,24 @@ constexpr int LS_JT = 7;             // y translations per lane
 constexpr int LS_TJ = 2 * LS_JT;     // y translations per tile
 constexpr int LS_TILE = LS_TI * LS_TJ;
 constexpr int LS_TABLE_CELLS = 7680; // shared-memory budget of the staged table (60 KB)
+// per-warp cell lists: LS_TI rows of ints + 2 * LS_PC row records (32 B each)
+constexpr int LS_LIST_INTS = LS_TI * LS_PCP + 2 * LS_PC * 8;
 
 size_t low_score_smem_bytes(int n_t, int wl) {
   size_t b = sizeof(double) * LS_TABLE_CELLS;                       // staged table
   b += sizeof(double) * LS_WARPS * LS_TILE;                          // per-round results
   b += sizeof(double) * (size_t)n_t * n_t;                           // best score
   b += sizeof(int) * (size_t)n_t * n_t;                              // best rotation
-  b += sizeof(int) * LS_WARPS * (LS_TI + LS_TJ) * LS_PCP;            // cell lists
+  b += sizeof(int) * LS_WARPS * LS_LIST_INTS;                        // cell lists
   b += sizeof(float) * ((size_t)wl + 2 + n_t);                       // thresholds, translations
   return b;
 }
+
+// Row offsets (in table cells) of a point for the 7 y-translations of one
+// half-tile; two 16-byte shared loads fetch them.
+struct __align__(16) RowList {
+  int r[8];
+};
 
 template <bool SMEM>
 __device__ __forceinline__ void low_score_rounds(
@@ -77,15 +85,21 @@ __device__ __forceinline__ void low_score_rounds(
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
   const int n_tiles = tiles_x * tiles_y;
   const int n_items = (rot1 - rot0) * n_tiles;
-  int* lx = s_lists + warp * (LS_TI + LS_TJ) * LS_PCP;   // [LS_TI][LS_PCP] column in the box
-  int* ly = lx + LS_TI * LS_PCP;                          // [LS_TJ][LS_PCP] row offset in the box
-  const int li = lane & 15, lj = (lane >> 4) * LS_JT;
+  int* lx = s_lists + warp * LS_LIST_INTS;                       // [LS_TI][LS_PCP] box column
+  RowList* ly = reinterpret_cast<RowList*>(lx + LS_TI * LS_PCP);  // [2][LS_PC] row offsets
+  const int li = lane & 15, half = lane >> 4, lj = half * LS_JT;
+  const bool single = (n_tiles == 1);  // the reference's 14 x 14 grid: best stays in registers
+  double rbest[LS_JT];
+  int rbest_rot[LS_JT];
+#pragma unroll
+  for (int u = 0; u < LS_JT; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
 
   for (int round0 = 0; round0 < n_items; round0 += LS_WARPS) {
     const int item = round0 + warp;
     if (item < n_items) {
       const int r = rot0 + item / n_tiles, tile = item % n_tiles;
       const int ti = tile % tiles_x, tj = tile / tiles_x;
+      const bool lane_on = ti * LS_TI + li < n_t;  // lanes past the grid do not gather
       const Rotation rot = rots[r];
       double acc[LS_JT];
 #pragma unroll
@@ -99,41 +113,65 @@ __device__ __forceinline__ void low_score_rounds(
             const int ii = ti * LS_TI + k;
             int v = tw;  // sentinel column: reads the floor
             if (ii < n_t) {
-              const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii]));  // Vector2f(x_trans, .)
-              if (cx >= ox && cx < ox + tw) v = cx - ox;
+              const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii])) - ox;  // Vector2f(x_trans, .)
+              if ((unsigned)cx < (unsigned)tw) v = cx;
             }
             lx[k * LS_PCP + lane] = v;
           }
-#pragma unroll 2
-          for (int k = 0; k < LS_TJ; ++k) {
-            const int jj = tj * LS_TJ + k;
-            int v = th;  // sentinel row
-            if (jj < n_t) {
-              const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));
-              if (cy >= oy && cy < oy + th) v = cy - oy;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            RowList pr;
+#pragma unroll
+            for (int u = 0; u < LS_JT; ++u) {
+              const int jj = tj * LS_TJ + hh * LS_JT + u;
+              int v = th;  // sentinel row
+              if (jj < n_t) {
+                const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj])) - oy;
+                if ((unsigned)cy < (unsigned)th) v = cy;
+              }
+              pr.r[u] = v * ts;
             }
-            ly[k * LS_PCP + lane] = v * ts;
+            pr.r[7] = 0;
+            ly[hh * LS_PC + lane] = pr;
           }
         }
         __syncwarp();
-        const int* px = lx + li * LS_PCP;
-        const int* py = ly + lj * LS_PCP;
+        if (lane_on) {
+          const int* px = lx + li * LS_PCP;
+          const RowList* py = ly + half * LS_PC;
 #pragma unroll 2
-        for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 gathers + adds per lane, point order
-          const int cxv = px[pl];
+          for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 gathers + adds per lane, point order
+            const int cxv = px[pl];
+            const RowList pr = py[pl];
 #pragma unroll
-          for (int u = 0; u < LS_JT; ++u) {
-            const int at = py[u * LS_PCP + pl] + cxv;
-            const double t = SMEM ? tab[at] : __ldg(tab + at);
-            acc[u] = __dadd_rn(acc[u], t);
+            for (int u = 0; u < LS_JT; ++u) {
+              const int at = pr.r[u] + cxv;
+              double t;
+              if (SMEM) {
+                extern __shared__ __align__(16) unsigned char s_raw[];  // staged table at offset 0
+                t = reinterpret_cast<const double*>(s_raw)[at];
+              } else {
+                t = __ldg(tab + at);
+              }
+              acc[u] = __dadd_rn(acc[u], t);
+            }
           }
         }
         __syncwarp();
       }
+      if (single) {
 #pragma unroll
-      for (int u = 0; u < LS_JT; ++u)  // probability / pointcloud.size() (cc:76)
-        s_res[warp * LS_TILE + (lj + u) * LS_TI + li] = __ddiv_rn(acc[u], (double)n_pts);
+        for (int u = 0; u < LS_JT; ++u) {  // this warp's rotations ascend: '>' keeps the earliest
+          const double sc = __ddiv_rn(acc[u], (double)n_pts);
+          if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r; }
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < LS_JT; ++u)  // probability / pointcloud.size() (cc:76)
+          s_res[warp * LS_TILE + (lj + u) * LS_TI + li] = __ddiv_rn(acc[u], (double)n_pts);
+      }
     }
+    if (single) continue;
     __syncthreads();
     // merge the round in work-item (= ascending rotation) order: std::max keeps
     // the earlier entry on ties (cc:109-110)
@@ -151,6 +189,25 @@ __device__ __forceinline__ void low_score_rounds(
     }
     __syncthreads();
   }
+  if (single) {
+    // merge the warps: higher score wins, equal scores keep the smaller rotation
+    for (int w = 0; w < LS_WARPS; ++w) {
+      if (warp == w && li < n_t) {
+#pragma unroll
+        for (int u = 0; u < LS_JT; ++u) {
+          const int j = lj + u;
+          if (j < n_t) {
+            const int tr = li * n_t + j;
+            if (rbest[u] > s_best[tr] || (rbest[u] == s_best[tr] && rbest_rot[u] < s_best_rot[tr])) {
+              s_best[tr] = rbest[u];
+              s_best_rot[tr] = rbest_rot[u];
+            }
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
 }
 
 __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
@@ -167,10 +224,10 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   extern __shared__ __align__(16) unsigned char s_raw[];
   double* s_tab = reinterpret_cast<double*>(s_raw);                  // [LS_TABLE_CELLS]
   double* s_res = s_tab + LS_TABLE_CELLS;                            // [LS_WARPS][LS_TILE]
-  double* s_best = s_res + LS_WARPS * LS_TILE;                       // [n_tr]
+  int* s_lists = reinterpret_cast<int*>(s_res + LS_WARPS * LS_TILE); // cell lists (16 B aligned)
+  double* s_best = reinterpret_cast<double*>(s_lists + LS_WARPS * LS_LIST_INTS);  // [n_tr]
   int* s_best_rot = reinterpret_cast<int*>(s_best + n_tr);           // [n_tr]
-  int* s_lists = s_best_rot + n_tr;                                  // cell lists
-  float* s_thr = reinterpret_cast<float*>(s_lists + LS_WARPS * (LS_TI + LS_TJ) * LS_PCP);
+  float* s_thr = reinterpret_cast<float*>(s_best_rot + n_tr);
   float* s_tlow = s_thr + (g.wl + 2);                                // [n_t]
 
   const float2* a = points + offsets[pw.a_scan];
