@@ -154,6 +154,48 @@ void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction
 
 int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out);
 
+/* --- point-to-point matching -------------------------------------------------
+ * The nearest-neighbour correspondence search that feeds the Ceres residuals:
+ *   Solver::GetPointToPointMatching   (src/optimization/solver.cc:132-172)
+ *   FindClosestPoint / GetPointNormal (src/optimization/solver.cc:67-89)
+ *   KDTree<float,2>::FindNearestPoint (src/util/kdtree.cc:253-305)
+ * over the clouds uploaded with nautilus_csm_upload_scans.  Results are the
+ * reference KD-tree's, index for index (see nn_kernels.cu for why that holds). */
+
+/* Builds the per-scan search structures (hashed grid on the device; the
+ * reference's KD-tree layout, kdtree.cc:114-150, on the host -- the reference
+ * builds its trees on the host at load time too, slam_types.h:57-75).
+ * cell_size = the largest threshold later calls will use, e.g.
+ * outlier_threshold (config/default_config.lua:66). */
+int nautilus_nn_build(NautilusCsm* h, double cell_size);
+
+/* target_to_world.inverse() * source_to_world as a row-major 2x3 float matrix
+ * from two (x, y, theta) poses: GetPoseAsAffine<float> (src/util/slam_util.h:
+ * 20-40) and solver.cc:159.  A caller that has Eigen should build the matrix
+ * with Eigen itself, as the reference does. */
+void nautilus_nn_pose_transform(const double* source_pose, const double* target_pose,
+                                float* m_2x3);
+
+/* For every pair p and source point i: match_idx[offsets[p] + i] = index in the
+ * target cloud of the point FindClosestPoint returns for (m_p * source_i), or -1
+ * when it returns nullopt (distance >= threshold, compared in double as
+ * solver.cc:85 does).  src_to_tgt: 6 floats per pair.  offsets: n_pairs + 1
+ * entries, filled by the call (prefix sums of the source cloud sizes).
+ * match_dist (optional): the distance FindNearestPoint returned where matched. */
+int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_t* tgt_ids,
+                            const float* src_to_tgt, double threshold, int32_t n_pairs,
+                            int32_t* match_idx, float* match_dist, int64_t* offsets);
+
+/* GetPointNormal (solver.cc:67-77): for every uploaded point, the index (within
+ * its scan) of the tree node the reference would take the normal from, i.e. the
+ * point's nearest neighbour in its own cloud within 1e-5 (itself, or the first
+ * visited duplicate).  out: one entry per uploaded point, scan by scan. */
+int nautilus_nn_self_index(NautilusCsm* h, int32_t* out);
+
+/* Kernel time of the last nautilus_nn_match_batch (CUDA events) and how many of
+ * its queries took the exact tree walk instead of the grid. */
+int nautilus_nn_last_stats(const NautilusCsm* h, float* ms_kernel, uint64_t* n_walked);
+
 #ifdef __cplusplus
 }
 #endif

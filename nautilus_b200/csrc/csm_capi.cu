@@ -20,28 +20,19 @@
 #include <utility>
 #include <vector>
 
-#include "../../include/nautilus_csm.h"
-#include "csm_kernels.h"
+#include "csm_handle.h"
 
 using namespace csm;
+using namespace csmh;
+
+namespace csmh {
+std::string& error_text() {
+  thread_local std::string g_error;
+  return g_error;
+}
+}  // namespace csmh
 
 namespace {
-
-thread_local std::string g_error;
-
-int fail(int code, const std::string& msg) {
-  g_error = msg;
-  return code;
-}
-
-#define CU_TRY(expr)                                                              \
-  do {                                                                            \
-    cudaError_t e_ = (expr);                                                      \
-    if (e_ != cudaSuccess) {                                                      \
-      int code_ = (e_ == cudaErrorMemoryAllocation) ? NAUTILUS_ENOMEM : NAUTILUS_ECUDA; \
-      return fail(code_, std::string(#expr) + ": " + cudaGetErrorString(e_));     \
-    }                                                                             \
-  } while (0)
 
 // convertX / convertY on the host (CorrelativeScanMatcher.h:43-49)
 long long host_cell(float v, double res, uint64_t dim) {
@@ -101,13 +92,6 @@ std::vector<float> make_thresholds(double res, int dim, int* qlo_out, int* qhi_o
   return thr;
 }
 
-// Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
-struct PoolListHost {
-  std::vector<int> s, e, dst;
-  std::vector<unsigned char> win;
-  bool tiles = false;  // windows tile [0, dim) in order without gaps/overlap
-};
-
 PoolListHost make_pool_list(double range, double low_res, double hi_res, uint64_t hi_dim,
                             uint64_t low_dim) {
   PoolListHost pl;
@@ -137,109 +121,8 @@ PoolListHost make_pool_list(double range, double low_res, double hi_res, uint64_
   return pl;
 }
 
-struct DevPool {
-  PoolListDev d{nullptr, nullptr, nullptr, nullptr, 0};
-  void release() {
-    cudaFree(d.s); cudaFree(d.e); cudaFree(d.dst); cudaFree(d.win);
-    d = PoolListDev{nullptr, nullptr, nullptr, nullptr, 0};
-  }
-  int upload(const PoolListHost& h) {
-    release();
-    const int n = (int)h.s.size();
-    d.n = n;
-    if (n == 0) return NAUTILUS_OK;
-    CU_TRY(cudaMalloc(&d.s, sizeof(int) * n));
-    CU_TRY(cudaMalloc(&d.e, sizeof(int) * n));
-    CU_TRY(cudaMalloc(&d.dst, sizeof(int) * n));
-    CU_TRY(cudaMalloc(&d.win, n));
-    CU_TRY(cudaMemcpy(d.s, h.s.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(d.e, h.e.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(d.dst, h.dst.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(d.win, h.win.data(), n, cudaMemcpyHostToDevice));
-    return NAUTILUS_OK;
-  }
-};
-
-// A set of clouds resident on the device.
-struct ScanSet {
-  float2* points = nullptr;
-  long long* offsets = nullptr;
-  std::vector<long long> host_offsets;
-  size_t cap_points = 0, cap_offsets = 0;
-  int n = 0;
-  void release() {
-    cudaFree(points); cudaFree(offsets);
-    points = nullptr; offsets = nullptr; cap_points = cap_offsets = 0; n = 0;
-  }
-};
-
-template <typename T>
-struct DevBuf {
-  T* p = nullptr;
-  size_t cap = 0;
-  int reserve(size_t n) {
-    if (n <= cap) return NAUTILUS_OK;
-    cudaFree(p);
-    p = nullptr; cap = 0;
-    const size_t want = std::max(n, (size_t)16);
-    CU_TRY(cudaMalloc(&p, sizeof(T) * want));
-    cap = want;
-    return NAUTILUS_OK;
-  }
-  void release() { cudaFree(p); p = nullptr; cap = 0; }
-};
-
 }  // namespace
 
-struct NautilusCsm {
-  NautilusCsmParams params;
-  Geometry geo;
-  VanVliet vv;
-  double rot_step;
-  int device;
-  cudaStream_t own_stream = nullptr, stream = nullptr;
-  int sm_count = 148;
-
-  // tables
-  PoolListHost pool_host;
-  DevPool pool_dev;
-  int n_slots = 0;
-  std::vector<TableSlot> slots_host;
-  DevBuf<TableSlot> slots_dev;
-  DevBuf<TableMeta> metas_dev;
-  double* slab_values = nullptr;
-  unsigned* slab_bitmap = nullptr;
-  unsigned char* slab_rowflag = nullptr;
-  double* slab_low = nullptr;
-  double* slab_lowlog = nullptr;
-  DevBuf<double> dense_scratch;
-  DevBuf<double> scalar_scratch;
-
-  // search grid
-  std::vector<float> t_low_host;
-  std::vector<int> slot_rank_host, n_h_host;
-  std::vector<float> t_high_host;
-  DevBuf<float> t_low_dev, t_high_dev;
-  DevBuf<int> slot_rank_dev, n_h_dev;
-  SearchGrid grid{};
-  std::vector<float> thr_low_host, thr_high_host;
-  DevBuf<float> thr_low_dev, thr_high_dev;
-  CellMap cm_low{}, cm_high{};
-  int grid_rc = 0;          // build_search_grid result; matching needs 0
-  std::string grid_error;
-
-  // scans + per-batch buffers
-  ScanSet user_scans, tmp_scans;
-  DevBuf<int> table_scan_dev;
-  DevBuf<PairWork> pairs_dev;
-  DevBuf<Rotation> rots_dev;
-  DevBuf<PairResult> results_dev;
-  DevBuf<double> chunk_best_dev;
-  DevBuf<int> chunk_rot_dev;
-  std::vector<cudaEvent_t> events;
-  NautilusCsmTimings timings{};
-  int last_n_pairs = 0;
-};
 
 namespace {
 
@@ -423,7 +306,7 @@ cudaEvent_t get_event(NautilusCsm* h, size_t k) {
 
 extern "C" {
 
-const char* nautilus_csm_last_error(void) { return g_error.c_str(); }
+const char* nautilus_csm_last_error(void) { return error_text().c_str(); }
 const char* nautilus_csm_version(void) { return "nautilus_csm_b200 sm_100a r1"; }
 
 int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v) {
@@ -513,7 +396,7 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
     nautilus_csm_destroy(h);
     return rc;
   }
-  if (h->grid_rc) h->grid_error = g_error;
+  if (h->grid_rc) h->grid_error = error_text();
   *out = h;
   return NAUTILUS_OK;
 }
@@ -523,6 +406,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   free_slots(h);
+  h->nn.release();
   h->pool_dev.release();
   h->slots_dev.release(); h->metas_dev.release(); h->dense_scratch.release();
   h->scalar_scratch.release();
@@ -553,7 +437,12 @@ int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* of
                               int32_t n_scans) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
   CU_TRY(cudaSetDevice(h->device));
-  return upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
+  h->nn.built = false;  // the NN index belongs to the previous scan set
+  int rc = upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
+  if (rc) return rc;
+  const long long total = n_scans > 0 ? offsets[n_scans] : 0;
+  h->user_scans.host_xy.assign(xy, xy + 2 * total);
+  return NAUTILUS_OK;
 }
 
 int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out) {

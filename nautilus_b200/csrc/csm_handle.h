@@ -1,0 +1,152 @@
+// Host-side handle of libnautilus_csm_b200.so, shared by the C-ABI translation
+// units (csm_capi.cu: tables + search, nn_capi.cu: nearest-neighbour matching).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/nautilus_csm.h"
+#include "csm_kernels.h"
+#include "nn_kernels.h"
+
+namespace csmh {
+using namespace csm;
+
+// thread-local error text behind nautilus_csm_last_error() (defined in csm_capi.cu)
+std::string& error_text();
+inline int fail(int code, const std::string& msg) {
+  error_text() = msg;
+  return code;
+}
+
+#define CU_TRY(expr)                                                              \
+  do {                                                                            \
+    cudaError_t e_ = (expr);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      int code_ = (e_ == cudaErrorMemoryAllocation) ? NAUTILUS_ENOMEM : NAUTILUS_ECUDA; \
+      return fail(code_, std::string(#expr) + ": " + cudaGetErrorString(e_));     \
+    }                                                                             \
+  } while (0)
+
+// Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
+// Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
+struct PoolListHost {
+  std::vector<int> s, e, dst;
+  std::vector<unsigned char> win;
+  bool tiles = false;  // windows tile [0, dim) in order without gaps/overlap
+};
+
+struct DevPool {
+  PoolListDev d{nullptr, nullptr, nullptr, nullptr, 0};
+  void release() {
+    cudaFree(d.s); cudaFree(d.e); cudaFree(d.dst); cudaFree(d.win);
+    d = PoolListDev{nullptr, nullptr, nullptr, nullptr, 0};
+  }
+  int upload(const PoolListHost& h) {
+    release();
+    const int n = (int)h.s.size();
+    d.n = n;
+    if (n == 0) return NAUTILUS_OK;
+    CU_TRY(cudaMalloc(&d.s, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.e, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.dst, sizeof(int) * n));
+    CU_TRY(cudaMalloc(&d.win, n));
+    CU_TRY(cudaMemcpy(d.s, h.s.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.e, h.e.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.dst, h.dst.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(d.win, h.win.data(), n, cudaMemcpyHostToDevice));
+    return NAUTILUS_OK;
+  }
+};
+
+// A set of clouds resident on the device.
+struct ScanSet {
+  float2* points = nullptr;
+  long long* offsets = nullptr;
+  std::vector<long long> host_offsets;
+  std::vector<float> host_xy;  // host copy of the clouds (KD-tree build of the NN path)
+  size_t cap_points = 0, cap_offsets = 0;
+  int n = 0;
+  void release() {
+    cudaFree(points); cudaFree(offsets);
+    points = nullptr; offsets = nullptr; cap_points = cap_offsets = 0; n = 0;
+  }
+};
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return NAUTILUS_OK;
+    cudaFree(p);
+    p = nullptr; cap = 0;
+    const size_t want = std::max(n, (size_t)16);
+    CU_TRY(cudaMalloc(&p, sizeof(T) * want));
+    cap = want;
+    return NAUTILUS_OK;
+  }
+  void release() { cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace csmh
+
+// internal header: the handle is written in terms of the two namespaces above
+using namespace csm;
+using namespace csmh;
+
+struct NautilusCsm {
+  NautilusCsmParams params;
+  Geometry geo;
+  VanVliet vv;
+  double rot_step;
+  int device;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  int sm_count = 148;
+
+  // tables
+  PoolListHost pool_host;
+  DevPool pool_dev;
+  int n_slots = 0;
+  std::vector<TableSlot> slots_host;
+  DevBuf<TableSlot> slots_dev;
+  DevBuf<TableMeta> metas_dev;
+  double* slab_values = nullptr;
+  unsigned* slab_bitmap = nullptr;
+  unsigned char* slab_rowflag = nullptr;
+  double* slab_low = nullptr;
+  double* slab_lowlog = nullptr;
+  DevBuf<double> dense_scratch;
+  DevBuf<double> scalar_scratch;
+
+  // search grid
+  std::vector<float> t_low_host;
+  std::vector<int> slot_rank_host, n_h_host;
+  std::vector<float> t_high_host;
+  DevBuf<float> t_low_dev, t_high_dev;
+  DevBuf<int> slot_rank_dev, n_h_dev;
+  SearchGrid grid{};
+  std::vector<float> thr_low_host, thr_high_host;
+  DevBuf<float> thr_low_dev, thr_high_dev;
+  CellMap cm_low{}, cm_high{};
+  int grid_rc = 0;          // build_search_grid result; matching needs 0
+  std::string grid_error;
+
+  // scans + per-batch buffers
+  ScanSet user_scans, tmp_scans;
+  DevBuf<int> table_scan_dev;
+  DevBuf<PairWork> pairs_dev;
+  DevBuf<Rotation> rots_dev;
+  DevBuf<PairResult> results_dev;
+  DevBuf<double> chunk_best_dev;
+  DevBuf<int> chunk_rot_dev;
+  std::vector<cudaEvent_t> events;
+  NautilusCsmTimings timings{};
+  int last_n_pairs = 0;
+
+  // nearest-neighbour matching (nn_capi.cu)
+  csmh::NnState nn;
+};

@@ -93,6 +93,7 @@ class CorrelativeScanMatcher:
         check(self._L.nautilus_csm_table_dims(self._h, C.byref(wh), C.byref(wl)))
         self.w_high, self.w_low = int(wh.value), int(wl.value)
         self.n_scans = 0
+        self._scan_sizes = np.zeros(0, np.int64)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -163,6 +164,7 @@ class CorrelativeScanMatcher:
         offsets = np.ascontiguousarray(offsets, dtype=np.int64)
         check(self._L.nautilus_csm_upload_scans(self._h, ptr(xy), ptr(offsets), len(offsets) - 1))
         self.n_scans = len(offsets) - 1
+        self._scan_sizes = (offsets[1:] - offsets[:-1]).astype(np.int64)
 
     def match_batch(self, a_ids, b_ids, rot_min, rot_max, *, with_stats: bool = False):
         a_ids = np.ascontiguousarray(a_ids, dtype=np.int32)
@@ -190,6 +192,40 @@ class CorrelativeScanMatcher:
         check(self._L.nautilus_csm_build_tables(self._h, ptr(ids), len(ids),
                                                 C.byref(cs) if checksum else None))
         return cs.value
+
+    # ---- point-to-point matching (solver.cc:67-172 over kdtree.cc) -----------
+    def nn_build(self, cell_size: float) -> None:
+        """Per-scan search structures for the uploaded clouds; cell_size = the
+        largest threshold later calls use (outlier_threshold)."""
+        check(self._L.nautilus_nn_build(self._h, float(cell_size)))
+
+    def nn_match_batch(self, src_ids, tgt_ids, transforms, threshold: float, *,
+                       with_dist: bool = False):
+        """-> (match_idx int32 [sum of source sizes], offsets int64 [n_pairs+1][, dist])."""
+        src_ids = np.ascontiguousarray(src_ids, dtype=np.int32)
+        tgt_ids = np.ascontiguousarray(tgt_ids, dtype=np.int32)
+        n = len(src_ids)
+        m = np.ascontiguousarray(transforms, dtype=np.float32).reshape(n, 6)
+        sizes = self._scan_sizes[src_ids] if n else np.zeros(0, np.int64)
+        total = int(sizes.sum())
+        idx = np.empty(max(total, 1), np.int32)
+        dist = np.empty(max(total, 1), np.float32) if with_dist else None
+        offsets = np.zeros(n + 1, np.int64)
+        check(self._L.nautilus_nn_match_batch(
+            self._h, ptr(src_ids), ptr(tgt_ids), ptr(m), float(threshold), n, ptr(idx),
+            ptr(dist) if with_dist else None, ptr(offsets)))
+        idx = idx[:total]
+        return (idx, offsets, dist[:total]) if with_dist else (idx, offsets)
+
+    def nn_self_index(self) -> np.ndarray:
+        out = np.empty(max(int(self._scan_sizes.sum()), 1), np.int32)
+        check(self._L.nautilus_nn_self_index(self._h, ptr(out)))
+        return out[:int(self._scan_sizes.sum())]
+
+    def nn_last_stats(self) -> dict:
+        ms, walked = C.c_float(), C.c_uint64()
+        check(self._L.nautilus_nn_last_stats(self._h, C.byref(ms), C.byref(walked)))
+        return {"ms_kernel": ms.value, "n_walked": int(walked.value)}
 
     def last_timings(self) -> dict:
         t = Timings()

@@ -107,14 +107,14 @@ def make_pair(seed: int, trans_range: float = 2.0, max_rot: float = 0.4,
 
 def make_scan_set(n_scans: int, group: int = 5, seed: int = 0,
                   trans_range: float = 2.0, max_rot: float = 0.2,
-                  n_beams: int = N_BEAMS):
+                  n_beams: int = N_BEAMS, return_poses: bool = False):
     """n_scans scans in groups of `group` taken near one base pose of one world
     (the shape of a loop-closure candidate list: several revisits of a place).
 
     Returns (xy, offsets): concatenated float32 [sum n_i, 2] and int64 [n_scans+1].
     Scans inside a group are within 0.8*trans_range and 2*max_rot of each other.
     """
-    clouds = []
+    clouds, poses = [], []
     for g in range((n_scans + group - 1) // group):
         world = make_world(seed * 1000003 + g)
         rng = np.random.default_rng(7777 + seed * 1000003 + g)
@@ -128,9 +128,13 @@ def make_scan_set(n_scans: int, group: int = 5, seed: int = 0,
             p = (float(np.clip(p[0], -hw + 0.3, hw - 0.3)),
                  float(np.clip(p[1], -hh + 0.3, hh - 0.3)), p[2])
             clouds.append(cast_scan(world, p, rng, n_beams))
+            poses.append(p)
     offsets = np.zeros(n_scans + 1, dtype=np.int64)
     offsets[1:] = np.cumsum([len(c) for c in clouds])
-    return np.ascontiguousarray(np.concatenate(clouds, axis=0)), offsets
+    xy = np.ascontiguousarray(np.concatenate(clouds, axis=0))
+    if return_poses:
+        return xy, offsets, np.asarray(poses, dtype=np.float64)
+    return xy, offsets
 
 
 def make_pair_list(n_scans: int, group: int = 5):

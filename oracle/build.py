@@ -1,6 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- builds the two CPU checkers.
 
-  oracle/_build/libcsm_oracle.so   plain-C restatement (csm_oracle.c, nn_oracle.c)
+  oracle/_build/libcsm_oracle.so   plain-C restatement of the CSM path (csm_oracle.c)
+  oracle/_build/libnn_oracle.so    restatement of the KD-tree / NN path (nn_oracle.cc)
   oracle/_ref/libnautilus_ref.so   the UNMODIFIED reference sources, compiled where
                                    they lie under /root/reference (only when that
                                    tree is present, i.e. in the build container;
@@ -23,6 +24,7 @@ REF_ROOT = "/root/reference"
 BUILD_DIR = os.path.join(HERE, "_build")
 REF_DIR = os.path.join(HERE, "_ref")
 PORT_LIB = os.path.join(BUILD_DIR, "libcsm_oracle.so")
+NN_PORT_LIB = os.path.join(BUILD_DIR, "libnn_oracle.so")
 REF_LIB = os.path.join(REF_DIR, "libnautilus_ref.so")
 
 
@@ -41,13 +43,15 @@ def _run(cmd: list[str]) -> None:
 
 
 def build_port(force: bool = False) -> str:
-    srcs = [os.path.join(HERE, f) for f in ("csm_oracle.c", "nn_oracle.c")]
-    srcs = [s for s in srcs if os.path.exists(s)]
-    if not force and _newer(PORT_LIB, srcs):
-        return PORT_LIB
+    srcs = [os.path.join(HERE, "csm_oracle.c")]
+    nn_src = os.path.join(HERE, "nn_oracle.cc")
     os.makedirs(BUILD_DIR, exist_ok=True)
-    _run(["gcc", "-std=c11", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wall",
-          *srcs, "-o", PORT_LIB, "-lm"])
+    if force or not _newer(PORT_LIB, srcs):
+        _run(["gcc", "-std=c11", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wall",
+              *srcs, "-o", PORT_LIB, "-lm"])
+    if force or not _newer(NN_PORT_LIB, [nn_src]):
+        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wall",
+              nn_src, "-o", NN_PORT_LIB])
     return PORT_LIB
 
 

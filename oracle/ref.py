@@ -56,6 +56,14 @@ def lib():
     L.ref_lowres_from_table.argtypes = [d, d, d, d, vp]
     L.ref_highres_table.restype = vp
     L.ref_highres_table.argtypes = [d, d, d, d, _f32p, i64]
+    if hasattr(L, "ref_kd_new"):  # KD-tree part (ref_nn_wrap.cc)
+        L.ref_kd_new.restype = vp
+        L.ref_kd_new.argtypes = [_f32p, i64]
+        L.ref_kd_free.argtypes = [vp]
+        L.ref_kd_nearest.argtypes = [vp, _f32p, i64, f, _f32p, _i32p]
+        L.ref_nn_match_batch.restype = d
+        L.ref_nn_match_batch.argtypes = [_f32p, _i64p, C.c_int32, _i32p, _i32p, _f32p, d,
+                                         C.c_int32, _i64p, _i32p, vp, C.c_int32]
     pd, pf = C.POINTER(d), C.POINTER(f)
     L.ref_match.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, d, d, pd, pf, pf, pf]
     L.ref_match_restricted.argtypes = [d, d, d, d, _f32p, i64, _f32p, i64, d, d, d,
@@ -195,3 +203,48 @@ class RefMatcher:
 
 def max_threads() -> int:
     return int(lib().ref_max_threads())
+
+
+class RefKDTree:
+    """KDTree<float, 2> of the reference (src/util/kdtree.{h,cc}), unmodified."""
+
+    def __init__(self, points):
+        self._L = lib()
+        self.points = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 2)
+        self._t = self._L.ref_kd_new(self.points, len(self.points))
+
+    def __del__(self):
+        try:
+            self._L.ref_kd_free(self._t)
+        except Exception:
+            pass
+
+    def nearest(self, queries, threshold):
+        """FindNearestPoint per query -> (float dist, int index of neighbor_node)."""
+        q = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, 2)
+        dist = np.zeros(len(q), np.float32)
+        idx = np.zeros(len(q), np.int32)
+        self._L.ref_kd_nearest(self._t, q, len(q), np.float32(threshold), dist, idx)
+        return dist, idx
+
+
+def nn_match_batch(xy, offsets, src_ids, tgt_ids, transforms, threshold, threads=0,
+                   with_dist=False):
+    """GetPointToPointMatching's search (solver.cc:146-170) for a batch of pairs over
+    the compiled reference KD-tree.  -> (seconds, match_idx, out_offsets[, dist])."""
+    L = lib()
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    src_ids = np.ascontiguousarray(src_ids, np.int32)
+    tgt_ids = np.ascontiguousarray(tgt_ids, np.int32)
+    m = np.ascontiguousarray(transforms, np.float32).reshape(-1, 6)
+    sizes = (offsets[1:] - offsets[:-1])[src_ids]
+    out_off = np.zeros(len(src_ids) + 1, np.int64)
+    np.cumsum(sizes, out=out_off[1:])
+    idx = np.full(int(out_off[-1]), -2, np.int32)
+    dist = np.zeros(int(out_off[-1]), np.float32) if with_dist else None
+    secs = L.ref_nn_match_batch(xy, offsets, len(offsets) - 1, src_ids, tgt_ids, m,
+                                float(threshold), len(src_ids), out_off, idx,
+                                dist.ctypes.data_as(C.c_void_p) if with_dist else None,
+                                threads or max_threads())
+    return (secs, idx, out_off, dist) if with_dist else (secs, idx, out_off)

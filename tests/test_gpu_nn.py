@@ -1,0 +1,138 @@
+"""GPU parity tests of the point-to-point nearest-neighbour path (K7), called
+through the C ABI, against outputs of the compiled reference KD-tree
+(tests/golden/nn_golden.npz), the CPU restatement (oracle/nn_oracle.cc) and,
+when present, the compiled reference itself (oracle/_ref).
+
+Bar: matched target indices bit-exact (index work), returned distances
+bit-exact where matched (they are the reference's float distances)."""
+import numpy as np
+import pytest
+
+from nautilus_b200 import (CorrelativeScanMatcher, CsmError, GetPointToPointMatching,
+                           pose_transform, synth)
+from oracle import nn_port
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nn_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "nn_golden.npz"))
+
+
+def make_matcher(xy, offs, cell):
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    m.nn_build(cell)
+    return m
+
+
+@pytest.mark.parametrize("name", ["scan", "adv"])
+def test_matches_vs_reference_golden(nn_golden, name):
+    g = nn_golden
+    m = make_matcher(g[f"{name}_xy"], g[f"{name}_offsets"], 0.7)
+    walked = 0
+    for k, thr in enumerate(g["thresholds"]):
+        idx, offs, dist = m.nn_match_batch(g[f"{name}_src"], g[f"{name}_tgt"], g[f"{name}_m"],
+                                           float(thr), with_dist=True)
+        want = g[f"{name}_idx_{k}"]
+        assert np.array_equal(offs, g[f"{name}_out_offsets"])
+        assert np.array_equal(idx, want), (name, thr, int((idx != want).sum()))
+        hit = want >= 0
+        assert np.array_equal(dist[hit], g[f"{name}_dist_{k}"][hit])
+        walked += m.nn_last_stats()["n_walked"]
+    if name == "adv":
+        assert walked > 0  # lattice / duplicate clouds must exercise the exact tree walk
+    assert np.array_equal(m.nn_self_index(), g[f"{name}_self_idx"])
+    m.close()
+
+
+def test_pose_transform_matches_golden_and_float64(nn_golden):
+    g = nn_golden
+    for p, (s, t) in enumerate(zip(g["scan_src"][:40], g["scan_tgt"][:40])):
+        got = pose_transform(g["scan_poses"][s], g["scan_poses"][t])
+        assert np.array_equal(got, g["scan_m"][p])
+        (xs, ys, ts), (xt, yt, tt) = g["scan_poses"][s], g["scan_poses"][t]
+        c, sn = np.cos(ts - tt), np.sin(ts - tt)
+        ct, st = np.cos(tt), np.sin(tt)
+        dx, dy = xs - xt, ys - yt
+        want = [c, -sn, ct * dx + st * dy, sn, c, -st * dx + ct * dy]
+        assert np.allclose(got, want, atol=2e-6)
+
+
+def test_random_pairs_vs_port_and_quirk():
+    """Fresh seeds at BASELINE beam count; the tree's single-child corner must
+    show up (reference != exact nearest neighbour) and be reproduced."""
+    xy, offs, poses = synth.make_scan_set(40, group=5, seed=3, return_poses=True)
+    rng = np.random.default_rng(9)
+    est = poses + np.concatenate([rng.normal(0, 0.1, (40, 2)), rng.normal(0, 0.03, (40, 1))], 1)
+    src, tgt = synth.make_pair_list(40, group=5)
+    tr = np.stack([pose_transform(est[s], est[t]) for s, t in zip(src, tgt)])
+    m = make_matcher(xy, offs, 0.25)
+    idx, o, dist = m.nn_match_batch(src, tgt, tr, 0.25, with_dist=True)
+    want, wo, wdist = nn_port.match_batch(xy, offs, src, tgt, tr, 0.25)
+    assert np.array_equal(o, wo) and np.array_equal(idx, want)
+    assert np.array_equal(dist[want >= 0], wdist[want >= 0])
+    exact = nn_port.brute_force(xy, offs, src, tgt, tr, 0.25)
+    assert (exact != want).any()
+    stats = m.nn_last_stats()
+    assert stats["n_walked"] < 0.01 * len(idx)  # the grid answers all but the ambiguous queries
+    m.close()
+
+
+def test_against_compiled_reference(ref_lib):
+    xy, offs, poses = synth.make_scan_set(30, group=5, seed=77, n_beams=720, return_poses=True)
+    src, tgt = synth.make_pair_list(30, group=5)
+    tr = np.stack([pose_transform(poses[s], poses[t]) for s, t in zip(src, tgt)])
+    m = make_matcher(xy, offs, 1.0)
+    for thr in (1.0, 0.25, 0.1):
+        idx, o = m.nn_match_batch(src, tgt, tr, thr)
+        _, want, wo = ref_lib.nn_match_batch(xy, offs, src, tgt, tr, thr)
+        assert np.array_equal(o, wo) and np.array_equal(idx, want), thr
+    m.close()
+
+
+def test_get_point_to_point_matching_struct():
+    xy, offs, poses = synth.make_scan_set(5, group=5, seed=5, n_beams=360, return_poses=True)
+    rng = np.random.default_rng(1)
+    normals = rng.normal(size=xy.shape).astype(np.float32)
+    m = make_matcher(xy, offs, 0.25)
+    c = GetPointToPointMatching(m, xy, offs, normals, poses, 1, 3, 0.25)
+    want, wo, _ = nn_port.match_batch(xy, offs, [1], [3], pose_transform(poses[1], poses[3]), 0.25)
+    hit = np.nonzero(want >= 0)[0]
+    assert (c.source_index, c.target_index) == (1, 3)
+    assert np.array_equal(c.source_points, xy[offs[1] + hit])
+    assert np.array_equal(c.target_points, xy[offs[3] + want[hit]])
+    assert np.array_equal(c.source_normals, normals[offs[1] + hit])   # no duplicates: self index
+    assert np.array_equal(c.target_normals, normals[offs[3] + want[hit]])
+    d = c.source_points - c.target_points
+    ref_diff = 0.0
+    for v in np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]).astype(np.float32)):
+        ref_diff += float(v)
+    assert c.difference == ref_diff
+    m.close()
+
+
+def test_nn_errors_and_edges():
+    xy = np.asarray([[0, 0], [1, 0], [5, 5]], np.float32)
+    offs = np.asarray([0, 2, 2, 3], np.int64)   # scan 1 is empty
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    ident = np.asarray([1, 0, 0, 0, 1, 0], np.float32)
+    with pytest.raises(CsmError):     # build first
+        m.nn_match_batch([0], [0], ident, 0.25)
+    m.nn_build(0.25)
+    with pytest.raises(CsmError):     # threshold above the grid cell
+        m.nn_match_batch([0], [0], ident, 0.5)
+    with pytest.raises(CsmError):
+        m.nn_match_batch([0], [7], ident, 0.25)
+    idx, o = m.nn_match_batch([0, 1, 0, 2], [0, 0, 1, 0], np.tile(ident, (4, 1)), 0.25)
+    assert o.tolist() == [0, 2, 2, 4, 5]
+    assert idx.tolist() == [0, 1, -1, -1, -1]   # self, empty source, empty target, too far
+    idx, o = m.nn_match_batch([], [], np.zeros((0, 6), np.float32), 0.25)
+    assert len(idx) == 0 and o.tolist() == [0]
+    m.upload_scans(xy, offs)          # a new scan set invalidates the index
+    with pytest.raises(CsmError):
+        m.nn_match_batch([0], [0], ident, 0.25)
+    m.close()

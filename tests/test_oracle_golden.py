@@ -164,3 +164,42 @@ def test_port_edge_inputs(ref_lib):
     assert rm.match(a, a, -0.2, 0.2) == pm.match(a, a, -0.2, 0.2)
     with pytest.raises(ValueError):
         pm.match(empty, a, -0.1, 0.1)
+
+
+# ---- nearest-neighbour path: the restatement against reference outputs ----------
+def test_nn_port_vs_reference_golden():
+    """oracle/nn_oracle.cc reproduces the compiled reference KD-tree's matches
+    (tests/golden/nn_golden.npz, generated by tests/golden/make_nn_golden.py)."""
+    import os
+    from oracle import nn_port
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "nn_golden.npz"))
+    quirk = 0
+    for name in ("scan", "adv"):
+        for k, thr in enumerate(g["thresholds"]):
+            idx, off, dist = nn_port.match_batch(g[f"{name}_xy"], g[f"{name}_offsets"],
+                                                 g[f"{name}_src"], g[f"{name}_tgt"],
+                                                 g[f"{name}_m"], float(thr))
+            want = g[f"{name}_idx_{k}"]
+            assert np.array_equal(off, g[f"{name}_out_offsets"])
+            assert np.array_equal(idx, want), (name, thr)
+            assert np.array_equal(dist[want >= 0], g[f"{name}_dist_{k}"][want >= 0])
+        exact = nn_port.brute_force(g["scan_xy"], g["scan_offsets"], g["scan_src"][:20],
+                                    g["scan_tgt"][:20], g["scan_m"][:20], 0.25)
+        n = len(exact)
+        quirk += int((exact != g["scan_idx_0"][:n]).sum())
+    # the reference walk is not an exact nearest-neighbour search (single-child leaves)
+    assert quirk > 0
+
+
+def test_nn_port_vs_compiled_reference(ref_lib):
+    from nautilus_b200 import synth
+    from oracle import nn_port
+    xy, offs, poses = synth.make_scan_set(10, group=5, seed=123, n_beams=360, return_poses=True)
+    src, tgt = synth.make_pair_list(10, group=5)
+    rng = np.random.default_rng(0)
+    tr = np.tile(np.asarray([1, 0, 0, 0, 1, 0], np.float32), (len(src), 1))
+    tr[:, [2, 5]] = rng.normal(0, 0.1, (len(src), 2))
+    for thr in (0.25, 0.7):
+        idx, off, _ = nn_port.match_batch(xy, offs, src, tgt, tr, thr)
+        _, want, wo = ref_lib.nn_match_batch(xy, offs, src, tgt, tr, thr)
+        assert np.array_equal(off, wo) and np.array_equal(idx, want)
