@@ -1,0 +1,53 @@
+"""The C++ drop-in header (nautilus_b200/cpp/CorrelativeScanMatcher.h) compiled
+the way a reference caller would compile it (g++, Eigen on the include path --
+here the oracle's Eigen stand-in, since Eigen itself is absent from the image)
+and linked against libnautilus_csm_b200.so."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from nautilus_b200 import CorrelativeScanMatcher, _lib, synth
+
+
+def build_shim_test(tmp_path):
+    exe = str(tmp_path / "shim_test")
+    cmd = ["g++", "-std=c++17", "-O1", os.path.join(ROOT, "tests", "cpp", "shim_test.cc"),
+           "-I" + os.path.join(ROOT, "nautilus_b200", "cpp"), "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "oracle", "shim"), "-L" + _lib.LIB_DIR,
+           "-lnautilus_csm_b200", "-Wl,-rpath," + _lib.LIB_DIR, "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_shim_compiles_and_links(tmp_path):
+    _lib.build()
+    build_shim_test(tmp_path)
+
+
+@pytest.mark.gpu
+def test_shim_runs_reference_unit_tests_and_matches(tmp_path):
+    exe = build_shim_test(tmp_path)
+    a, b, _ = synth.make_pair(5, n_beams=360)
+    blob = tmp_path / "pair.bin"
+    with open(blob, "wb") as f:
+        np.asarray([len(a), len(b)], np.int32).tofile(f)
+        a.tofile(f)
+        b.tofile(f)
+    r = subprocess.run([exe, str(blob)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "SHIM OK" in r.stdout
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    want = m.GetTransformation(a, b, -0.5, 0.5)
+    want5 = m.GetTransformationRestricted(a, b, 0.1, 0.3, np.pi / 2)
+    got = {ln.split()[0]: [float(v) for v in ln.split()[1:]] for ln in r.stdout.splitlines()
+           if ln.startswith(("MATCH", "TABLEMAX"))}
+    for key, w in (("MATCH", want), ("MATCH5", want5)):
+        assert got[key][0] == w[0]
+        assert np.float32(got[key][1]) == w[1][0][0] and np.float32(got[key][2]) == w[1][0][1]
+        assert np.float32(got[key][3]) == w[1][1]
+    assert got["TABLEMAX"] == [1.0, 2000.0]
+    m.close()
