@@ -54,7 +54,7 @@ struct LookupTable {
   uint64_t height;
   double resolution;
   nautilus_b200_detail::Image values;
-  LookupTable(const uint64_t range, const double resolution)
+  LookupTable(const double range, const double resolution)
       : width(floor((range * 2.0) / resolution)),
         height(floor((range * 2.0) / resolution)),
         resolution(resolution) {  // h:32-39
