@@ -581,7 +581,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     const int t0 = w * n_slots, t1 = std::min(n_targets, t0 + n_slots);
     const int k0 = first_pair[t0], k1 = first_pair[t1];
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
-                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, st, &launches);
+                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, &launches);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));
     launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
                      h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, st);
@@ -677,7 +677,7 @@ int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points
   cudaStream_t st = h->stream;
   CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, &zero, sizeof(int), cudaMemcpyHostToDevice, st));
   launch_table_wave(h->geo, h->vv, h->tmp_scans.points, h->tmp_scans.offsets, h->table_scan_dev.p,
-                    h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, 1, st, nullptr);
+                    h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, 1, false, st, nullptr);
   const size_t w = h->geo.w, wl = h->geo.wl;
   if (out_high) {
     if ((rc = h->dense_scratch.reserve(w * w))) return rc;
@@ -747,7 +747,7 @@ int nautilus_csm_build_tables(NautilusCsm* h, const int32_t* scan_ids, int32_t n
   for (int t0 = 0; t0 < n; t0 += h->n_slots, ++waves) {
     const int cnt = std::min(n - t0, h->n_slots);
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
-                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, cnt, st, &launches);
+                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, cnt, false, st, &launches);
     if (checksum) { launch_low_checksum(h->geo, h->slots_dev.p, cnt, h->scalar_scratch.p, st); ++launches; }
   }
   CU_TRY(cudaEventRecord(get_event(h, 1), st));

@@ -13,6 +13,15 @@
 
 namespace csm {
 
+// log(MIN_VALUE_FOR_LOOKUP) correctly rounded (what glibc's log returns, cc:72);
+// one constant everywhere so that every floor lookup adds the same bits.
+#define CSM_FLOOR_LOG (-23.025850929940457)
+
+// log(GetPointValue) of a table cell value (h:51-59 + cc:72).
+__device__ __forceinline__ double lookup_log(double v) {
+  return v > CSM_MIN_VALUE_FOR_LOOKUP ? log(v) : CSM_FLOOR_LOG;
+}
+
 // Van Vliet-Young order-0 coefficients + Triggs-Sdika matrix
 // (CImg.h:49267-49284, 49066-49081); filled on the host.
 struct VanVliet {
@@ -40,7 +49,9 @@ struct TableMeta {
 
 // One resident table slot.
 struct TableSlot {
-  double* values;      // active rectangle, row-major, stride meta.stride
+  double* values;      // active rectangle, row-major, stride meta.stride; holds the
+                       // normalised values, or their lookup_log when the wave was
+                       // built for matching (launch_table_wave store_log)
   unsigned* bitmap;    // occupied-box bitmap, bm_stride words per row
   unsigned char* rowflag;  // 1 per occupied-box row that has a point
   double* low;         // wl*wl low-res values (max-pool of the normalised table)

@@ -19,7 +19,7 @@ struct PoolListDev {
 
 void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
-                       TableMeta* metas, const PoolListDev& pool, int n_tables,
+                       TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
                        cudaStream_t stream, int* launches);
 void launch_pool_generic(const double* hi, int w, int h, const PoolListDev& px,
                          const PoolListDev& py, double* low, int wl, cudaStream_t stream);

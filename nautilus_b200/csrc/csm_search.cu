@@ -420,26 +420,21 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
         const int* py = cyh + ky * RF_STRIDE;
         double s = hacc[c];
         int pl = 0;
-        // four independent gathers + logs in flight, added in point order
-        for (; pl + 4 <= pc; pl += 4) {
-          const int ox0 = px[pl], oy0 = py[pl], ox1 = px[pl + 1], oy1 = py[pl + 1];
-          const int ox2 = px[pl + 2], oy2 = py[pl + 2], ox3 = px[pl + 3], oy3 = py[pl + 3];
-          double t0 = CSM_MIN_VALUE_FOR_LOOKUP, t1 = t0, t2 = t0, t3 = t0;
-          if ((ox0 | oy0) >= 0) t0 = __ldg(hi + oy0 + ox0);
-          if ((ox1 | oy1) >= 0) t1 = __ldg(hi + oy1 + ox1);
-          if ((ox2 | oy2) >= 0) t2 = __ldg(hi + oy2 + ox2);
-          if ((ox3 | oy3) >= 0) t3 = __ldg(hi + oy3 + ox3);
-          const double l0 = log(fmax(t0, CSM_MIN_VALUE_FOR_LOOKUP));
-          const double l1 = log(fmax(t1, CSM_MIN_VALUE_FOR_LOOKUP));
-          const double l2 = log(fmax(t2, CSM_MIN_VALUE_FOR_LOOKUP));
-          const double l3 = log(fmax(t3, CSM_MIN_VALUE_FOR_LOOKUP));
-          s = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(s, l0), l1), l2), l3);
+        // the table holds lookup_log of every cell (normalize_pool_kernel); eight
+        // independent gathers in flight, added in point order
+        for (; pl + 8 <= pc; pl += 8) {
+          double t[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int ox = px[pl + u], oy = py[pl + u];
+            t[u] = ((ox | oy) >= 0) ? __ldg(hi + oy + ox) : CSM_FLOOR_LOG;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) s = __dadd_rn(s, t[u]);
         }
         for (; pl < pc; ++pl) {
           const int ox = px[pl], oy = py[pl];
-          double t = CSM_MIN_VALUE_FOR_LOOKUP;
-          if ((ox | oy) >= 0) t = __ldg(hi + oy + ox);
-          s = __dadd_rn(s, log(t > CSM_MIN_VALUE_FOR_LOOKUP ? t : CSM_MIN_VALUE_FOR_LOOKUP));
+          s = __dadd_rn(s, ((ox | oy) >= 0) ? __ldg(hi + oy + ox) : CSM_FLOOR_LOG);
         }
         hacc[c] = s;
       }

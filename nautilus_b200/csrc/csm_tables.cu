@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) raster_kernel(
 
   // low-res tables start as "all zero" / "all floor"; the pool kernel fills
   // the cells its windows reach.
-  const double floor_log = log(CSM_MIN_VALUE_FOR_LOOKUP);
+  const double floor_log = CSM_FLOOR_LOG;
   for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
   for (int i = threadIdx.x; i < (g.wl + 1) * (g.wl + 1); i += blockDim.x)
     slot.lowlog[i] = floor_log;
@@ -338,7 +338,8 @@ __device__ __forceinline__ double normalise_value(double v, double mn, double ra
 __global__ void __launch_bounds__(256) normalize_pool_kernel(
     Geometry g, const TableSlot* __restrict__ slots, TableMeta* __restrict__ metas,
     const int* __restrict__ pool_s, const int* __restrict__ pool_e,
-    const int* __restrict__ pool_dst, const unsigned char* __restrict__ pool_win) {
+    const int* __restrict__ pool_dst, const unsigned char* __restrict__ pool_win,
+    int store_log) {
   extern __shared__ double s_colmax[];
   const int t = blockIdx.y;
   const TableMeta m = metas[t];
@@ -357,7 +358,9 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
     for (int r = rs; r <= re; ++r, p += m.stride) {
       const double nv = constant ? 0.0 : normalise_value(*p, mn, range);
-      *p = nv;
+      // matching only ever needs log(GetPointValue): take it once per cell here
+      // instead of once per (candidate, point) in the search
+      *p = store_log ? lookup_log(nv) : nv;
       cm = fmax(cm, nv);
     }
     s_colmax[c] = cm;
@@ -375,7 +378,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     for (int c = cs; c <= ce; ++c) mx = fmax(mx, s_colmax[c - m.ax0]);
     slot.low[(size_t)dy * g.wl + dx] = mx;
     const bool above = mx > CSM_MIN_VALUE_FOR_LOOKUP;
-    slot.lowlog[(size_t)dy * (g.wl + 1) + dx] = log(above ? mx : CSM_MIN_VALUE_FOR_LOOKUP);
+    slot.lowlog[(size_t)dy * (g.wl + 1) + dx] = lookup_log(mx);
     if (above) { bx0 = min(bx0, dx); bx1 = max(bx1, dx); }
   }
   // box of low-res cells above the lookup floor (the search stages it in smem)
@@ -446,7 +449,7 @@ __global__ void low_checksum_kernel(Geometry g, const TableSlot* __restrict__ sl
 // ---- launchers --------------------------------------------------------------
 void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
-                       TableMeta* metas, const PoolListDev& pool, int n_tables,
+                       TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
                        cudaStream_t stream, int* launches) {
   if (n_tables <= 0) return;
   raster_kernel<<<n_tables, 256, 0, stream>>>(g, points, offsets, scan_ids, slots, metas);
@@ -456,7 +459,7 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   ypass_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   dim3 gn(g.n_pool, n_tables);
   normalize_pool_kernel<<<gn, 256, sizeof(double) * g.w, stream>>>(
-      g, slots, metas, pool.s, pool.e, pool.dst, pool.win);
+      g, slots, metas, pool.s, pool.e, pool.dst, pool.win, store_log ? 1 : 0);
   if (launches) *launches += 4;
 }
 
