@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scans", type=int, default=N_SCANS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stage-cells", type=int, default=0, help="tuning: staged low-res table budget")
     return ap.parse_args()
 
 
@@ -229,7 +230,7 @@ def run_ours(args):
 
     xy, offs, pa, pb = make_batch(args.scans, seed=rank)
     n_pairs = len(pa)
-    m = CorrelativeScanMatcher(*PARAMS, device=local)
+    m = CorrelativeScanMatcher(*PARAMS, device=local, stage_cells=args.stage_cells)
     stream = torch.cuda.current_stream()
     m.set_stream(stream.cuda_stream)
 

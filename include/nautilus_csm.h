@@ -60,7 +60,8 @@ typedef struct NautilusCsmParams {
                            reference); 0 => default (160: truncated tails are
                            below 1e-20 of the table maximum)                   */
   int32_t max_tables;   /* resident hi-res table slots per wave; 0 => auto     */
-  int32_t reserved;
+  int32_t stage_cells;  /* shared-memory budget of the low-res scorer's staged table,
+                           in doubles; 0 => default                             */
 } NautilusCsmParams;
 
 /* Per-pair search statistics, counted by the same rule as the oracle:

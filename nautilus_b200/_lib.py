@@ -34,7 +34,7 @@ class Params(C.Structure):
                 ("low_res", C.c_double), ("high_res", C.c_double),
                 ("rot_step", C.c_double), ("blur_sigma", C.c_double),
                 ("device", C.c_int32), ("margin_cells", C.c_int32),
-                ("max_tables", C.c_int32), ("reserved", C.c_int32)]
+                ("max_tables", C.c_int32), ("stage_cells", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -137,7 +137,7 @@ void free_slots(NautilusCsm* h) {
 size_t slot_bytes(const Geometry& g) {
   const size_t w = g.w, wl = g.wl;
   return sizeof(double) * ((w + 3) & ~(size_t)3) * w + sizeof(unsigned) * g.bm_stride * w + w +
-         sizeof(double) * (wl * wl + (wl + 1) * (wl + 1));
+         sizeof(double) * (wl * wl + (wl + 1) * (size_t)lowlog_stride((int)wl));
 }
 
 // Makes at least `want` table slots resident (bounded by params.max_tables and
@@ -159,7 +159,7 @@ int ensure_slots(NautilusCsm* h, int want) {
   CU_TRY(cudaMalloc(&h->slab_bitmap, sizeof(unsigned) * (size_t)g.bm_stride * w * want));
   CU_TRY(cudaMalloc(&h->slab_rowflag, w * (size_t)want));
   CU_TRY(cudaMalloc(&h->slab_low, sizeof(double) * wl * wl * want));
-  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 1) * (wl + 1) * want));
+  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 1) * lowlog_stride((int)wl) * want));
   h->slots_host.resize(want);
   for (int i = 0; i < want; ++i) {
     TableSlot& s = h->slots_host[i];
@@ -167,7 +167,7 @@ int ensure_slots(NautilusCsm* h, int want) {
     s.bitmap = h->slab_bitmap + (size_t)g.bm_stride * w * i;
     s.rowflag = h->slab_rowflag + w * (size_t)i;
     s.low = h->slab_low + wl * wl * (size_t)i;
-    s.lowlog = h->slab_lowlog + (wl + 1) * (wl + 1) * (size_t)i;
+    s.lowlog = h->slab_lowlog + (wl + 1) * lowlog_stride((int)wl) * (size_t)i;
   }
   int rc = h->slots_dev.reserve(want);
   if (rc) return rc;
@@ -557,9 +557,14 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   sb.chunk_best = h->chunk_best_dev.p;
   sb.chunk_rot = h->chunk_rot_dev.p;
 
-  if ((size_t)(h->geo.wl + 1) * (h->geo.wl + 1) > 65535)
-    return fail(NAUTILUS_EINVAL, "low-res grid too large for the 16-bit row offsets of the search");
-  if (low_score_smem_bytes(n_t, h->geo.wl) > 220 * 1024)
+  if (h->geo.wl + 1 > 65535)
+    return fail(NAUTILUS_EINVAL, "low-res grid too large for the 16-bit row lists of the search");
+  // staged-table budget: three blocks per SM when the translation grid is the
+  // reference's 14 x 14, whatever fits otherwise
+  int table_cells = h->params.stage_cells > 0 ? h->params.stage_cells : 11776;
+  while (table_cells > 1024 && low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
+    table_cells -= 512;
+  if (low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
     return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
 
   if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
@@ -584,7 +589,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
                       h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, &launches);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));
     launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
-                     h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, st);
+                     h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, table_cells, st);
     CU_TRY(cudaEventRecord(get_event(h, ev++), st));
     launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p,
                   h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,

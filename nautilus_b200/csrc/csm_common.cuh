@@ -22,6 +22,11 @@ __device__ __forceinline__ double lookup_log(double v) {
   return v > CSM_MIN_VALUE_FOR_LOOKUP ? log(v) : CSM_FLOOR_LOG;
 }
 
+// Floor columns on either side of a lowlog row = x translations one lane of the
+// low-res scorer owns (csm_search.cu LS_IU).
+#define CSM_LOW_PAD 7
+__host__ __device__ __forceinline__ int lowlog_stride(int wl) { return (wl + 2 * CSM_LOW_PAD) | 1; }
+
 // Van Vliet-Young order-0 coefficients + Triggs-Sdika matrix
 // (CImg.h:49267-49284, 49066-49081); filled on the host.
 struct VanVliet {
@@ -55,7 +60,10 @@ struct TableSlot {
   unsigned* bitmap;    // occupied-box bitmap, bm_stride words per row
   unsigned char* rowflag;  // 1 per occupied-box row that has a point
   double* low;         // wl*wl low-res values (max-pool of the normalised table)
-  double* lowlog;      // (wl+1)*(wl+1) log(max(low,1e-10)); last row/col = floor
+  double* lowlog;      // lookup_log of the low-res table in the padded layout the
+                       // scorer reads: (wl+1) rows of lowlog_stride(wl) doubles,
+                       // cell (x, y) at [y * stride + x + CSM_LOW_PAD]; the pad
+                       // columns on either side and row wl hold the floor
 };
 
 // Grid geometry shared by all kernels.

@@ -74,12 +74,12 @@ struct SearchBuffers {
 void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm_low,
                       const float2* points, const long long* offsets, const TableSlot* slots,
                       const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
-                      int n_pairs, const SearchBuffers& sb, cudaStream_t stream);
+                      int n_pairs, const SearchBuffers& sb, int table_cells, cudaStream_t stream);
 void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
                    const float2* points, const long long* offsets, const TableSlot* slots,
                    const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
                    int n_pairs, const SearchBuffers& sb, PairResult* results,
                    cudaStream_t stream);
-size_t low_score_smem_bytes(int n_t, int wl);
+size_t low_score_smem_bytes(int n_t, int wl, int table_cells);
 
 }  // namespace csm

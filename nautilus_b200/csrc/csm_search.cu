@@ -34,126 +34,154 @@ __device__ __forceinline__ float2 rotate_point(float2 p, float c, float s) {
 // K5  low-res exhaustive scoring + per-translation max over a theta chunk.
 // grid = (theta chunks, pairs), 8 warps per block.
 //
-// A warp scores one (rotation, translation tile) work item: a tile is 16
-// x-translations (lane & 15) by 14 y-translations (7 per lane, lane >> 4 picks
-// the half), so the reference's 14 x 14 grid is exactly one tile and every lane
-// keeps 7 running sums in registers.  Per chunk of 32 points the warp first
-// turns the rotated points into per-axis cell lists (lane = point; exact cells
-// through the float threshold map, no division), then every lane adds its 7
-// table values per point, in point order.  The part of the pooled log table
-// that lies above the lookup floor (TableMeta::lx0..ly1) is staged in shared
-// memory once per block; a half-warp reads 14 consecutive doubles of one table
-// row, which is conflict-free.  Tables whose box does not fit fall back to
-// gathering from global memory through L1.
+// A warp scores one (rotation, translation tile) work item.  A tile is 14
+// x-translations by 16 y-translations: lane & 15 picks the y-translation, lane
+// >> 4 the group of 7 consecutive x-translations whose running sums the lane
+// keeps in registers (the reference's 14 x 14 grid is exactly one tile).
+// Because the translation step equals the cell size (both are low_res_,
+// cc:96-99), the 7 cells a lane needs for one point are 7 CONSECUTIVE doubles
+// of one table row: per point the lane loads its row offset (per-lane list)
+// and the half-warp's first column (one broadcast word), then issues 7 loads at
+// compile-time offsets -- no index arithmetic per lookup.  The rare point whose
+// x cells are not consecutive (a sum that lands within float rounding of a cell
+// edge) is flagged in phase A and recomputed cell by cell.
+//
+// The part of the pooled log table that lies above the lookup floor
+// (TableMeta::lx0..ly1) is staged in shared memory once per block with 7 floor
+// columns on either side and one floor row, so windows that leave the box need
+// no special case.  The row stride is odd: the 16 lanes of a half-warp read 16
+// different rows at the same column and hit 16 different bank pairs.  Tables
+// whose box does not fit the budget are gathered from global memory through L1.
+// Sums run over points in point order, one lane per candidate, like cc:66-77.
 // ---------------------------------------------------------------------------
 constexpr int LS_WARPS = 8;
 constexpr int LS_THREADS = LS_WARPS * 32;
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
-constexpr int LS_PCP = LS_PC + 1;    // odd row stride: rows start on different banks
-constexpr int LS_TI = 16;            // x translations per tile
-constexpr int LS_JT = 7;             // y translations per lane
-constexpr int LS_TJ = 2 * LS_JT;     // y translations per tile
+constexpr int LS_TJ = 16;            // y translations per tile
+constexpr int LS_IU = 7;             // x translations per lane
+constexpr int LS_TI = 2 * LS_IU;     // x translations per tile
 constexpr int LS_TILE = LS_TI * LS_TJ;
-constexpr int LS_TABLE_CELLS = 7680; // shared-memory budget of the staged table (60 KB)
-// per-warp cell lists: LS_TI rows of ints + 2 * LS_PC row records (32 B each)
-constexpr int LS_LIST_INTS = LS_TI * LS_PCP + 2 * LS_PC * 8;
+constexpr int LS_XPAD = CSM_LOW_PAD;  // floor columns on either side of the staged box
+static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding");
+constexpr int LS_LROW = LS_PC + 2;   // u16 entries per row-list row (17 words: odd)
+// per-warp lists: row index per (y translation, point), first column per
+// (half, point), rotated x per point
+constexpr int LS_LIST_BYTES = LS_TJ * LS_LROW * 2 + 2 * LS_PC * 4 + LS_PC * 4;
 
-size_t low_score_smem_bytes(int n_t, int wl) {
-  size_t b = sizeof(double) * LS_TABLE_CELLS;                       // staged table
-  b += sizeof(double) * LS_WARPS * LS_TILE;                          // per-round results
+size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
+  const bool single = n_t <= LS_TI;
+  size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
+  if (!single) b += sizeof(double) * LS_WARPS * LS_TILE;             // per-round results
   b += sizeof(double) * (size_t)n_t * n_t;                           // best score
+  b += (size_t)LS_WARPS * LS_LIST_BYTES;                             // lists
   b += sizeof(int) * (size_t)n_t * n_t;                              // best rotation
-  b += sizeof(int) * LS_WARPS * LS_LIST_INTS;                        // cell lists
   b += sizeof(float) * ((size_t)wl + 2 + n_t);                       // thresholds, translations
   return b;
 }
 
-// Row offsets (in table cells) of a point for the 7 y-translations of one
-// half-tile; two 16-byte shared loads fetch them.
-struct __align__(16) RowList {
-  int r[8];
+// Geometry of the table a block scores against (staged box or the whole table).
+struct LowTab {
+  const double* tab;  // shared (staged) or global (lowlog)
+  int ox, oy;         // low-res cell of box column / row 0
+  int tw, th;         // box width / height in cells
+  int ts;             // row stride in doubles
+  int xpad;           // floor columns left of the box (column 0 always reads the floor)
+  int floor_row;      // a row that reads the floor
 };
 
 template <bool SMEM>
+__device__ __forceinline__ double tab_load(const double* p) {
+  if (SMEM) return *p;
+  return __ldg(p);
+}
+
+template <bool SMEM>
 __device__ __forceinline__ void low_score_rounds(
-    const Geometry& g, const SearchGrid& sg, const CellMap& cm, const float* s_tlow,
-    const double* __restrict__ tab, int ox, int oy, int tw, int th, int ts,
+    const SearchGrid& sg, const CellMap& cm, const float* s_tlow, const LowTab lt,
     const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
-    int rot1, int* s_lists, double* s_res, double* s_best, int* s_best_rot) {
+    int rot1, unsigned char* s_lists, double* s_res, double* s_best, int* s_best_rot) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
   const int n_tiles = tiles_x * tiles_y;
   const int n_items = (rot1 - rot0) * n_tiles;
-  int* lx = s_lists + warp * LS_LIST_INTS;                       // [LS_TI][LS_PCP] box column
-  RowList* ly = reinterpret_cast<RowList*>(lx + LS_TI * LS_PCP);  // [2][LS_PC] row offsets
-  const int li = lane & 15, half = lane >> 4, lj = half * LS_JT;
+  unsigned short* ly = reinterpret_cast<unsigned short*>(s_lists + warp * LS_LIST_BYTES);
+  int* lxb = reinterpret_cast<int*>(ly + LS_TJ * LS_LROW);   // [2][LS_PC]
+  float* lqx = reinterpret_cast<float*>(lxb + 2 * LS_PC);    // [LS_PC]
+  const int lj = lane & 15, half = lane >> 4;
   const bool single = (n_tiles == 1);  // the reference's 14 x 14 grid: best stays in registers
-  double rbest[LS_JT];
-  int rbest_rot[LS_JT];
+  double rbest[LS_IU];
+  int rbest_rot[LS_IU];
 #pragma unroll
-  for (int u = 0; u < LS_JT; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
+  for (int u = 0; u < LS_IU; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
 
   for (int round0 = 0; round0 < n_items; round0 += LS_WARPS) {
     const int item = round0 + warp;
     if (item < n_items) {
       const int r = rot0 + item / n_tiles, tile = item % n_tiles;
       const int ti = tile % tiles_x, tj = tile / tiles_x;
-      const bool lane_on = ti * LS_TI + li < n_t;  // lanes past the grid do not gather
+      const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
       const Rotation rot = rots[r];
-      double acc[LS_JT];
+      double acc[LS_IU];
 #pragma unroll
-      for (int u = 0; u < LS_JT; ++u) acc[u] = 0.0;
+      for (int u = 0; u < LS_IU; ++u) acc[u] = 0.0;
       for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
         const int pc = min(LS_PC, n_pts - p0);
-        if (lane < pc) {  // phase A: this lane's point -> cells for the tile's translations
+        bool odd = false;  // this lane's point has x cells that are not consecutive
+        if (lane < pc) {  // phase A: this lane's point -> rows / first columns of the tile
           const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
 #pragma unroll 4
-          for (int k = 0; k < LS_TI; ++k) {
-            const int ii = ti * LS_TI + k;
-            int v = tw;  // sentinel column: reads the floor
-            if (ii < n_t) {
-              const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii])) - ox;  // Vector2f(x_trans, .)
-              if ((unsigned)cx < (unsigned)tw) v = cx;
+          for (int k = 0; k < LS_TJ; ++k) {
+            const int jj = tj * LS_TJ + k;
+            int row = lt.floor_row;
+            if (jj < n_t) {
+              const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj])) - lt.oy;  // Vector2f(., y_trans)
+              if ((unsigned)cy < (unsigned)lt.th) row = cy;
             }
-            lx[k * LS_PCP + lane] = v;
+            ly[k * LS_LROW + lane] = (unsigned short)row;
           }
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
-            RowList pr;
+            const int ii0 = ti * LS_TI + hh * LS_IU;
+            int word = 0;  // a group past the grid reads the floor padding
+            if (ii0 < n_t) {
+              const int c0 = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii0]));  // Vector2f(x_trans, .)
+              bool regular = c0 >= 0;
 #pragma unroll
-            for (int u = 0; u < LS_JT; ++u) {
-              const int jj = tj * LS_TJ + hh * LS_JT + u;
-              int v = th;  // sentinel row
-              if (jj < n_t) {
-                const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj])) - oy;
-                if ((unsigned)cy < (unsigned)th) v = cy;
-              }
-              pr.r[u] = v * ts;
+              for (int u = 1; u < LS_IU; ++u)
+                if (ii0 + u < n_t)
+                  regular = regular && (cell_fast(cm, __fadd_rn(q.x, s_tlow[ii0 + u])) == c0 + u);
+              // columns c0 .. c0+6 relative to the padded box; a window entirely
+              // outside the box is moved onto the floor padding
+              word = regular ? max(0, min(c0 - lt.ox + lt.xpad, lt.tw + lt.xpad)) : -1;
             }
-            pr.r[7] = 0;
-            ly[hh * LS_PC + lane] = pr;
+            lxb[hh * LS_PC + lane] = word;
+            odd = odd || word < 0;
           }
+          lqx[lane] = q.x;
         }
-        __syncwarp();
-        if (lane_on) {
-          const int* px = lx + li * LS_PCP;
-          const RowList* py = ly + half * LS_PC;
-#pragma unroll 2
-          for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 gathers + adds per lane, point order
-            const int cxv = px[pl];
-            const RowList pr = py[pl];
+        const bool any_odd = __any_sync(0xffffffffu, odd);  // also orders the list writes
+        const unsigned short* py = ly + lj * LS_LROW;
+        const int* px = lxb + half * LS_PC;
+        if (!any_odd) {
+#pragma unroll 4
+          for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 consecutive cells per lane, point order
+            const double* t = lt.tab + ((int)py[pl] * lt.ts + px[pl]);
 #pragma unroll
-            for (int u = 0; u < LS_JT; ++u) {
-              const int at = pr.r[u] + cxv;
-              double t;
-              if (SMEM) {
-                extern __shared__ __align__(16) unsigned char s_raw[];  // staged table at offset 0
-                t = reinterpret_cast<const double*>(s_raw)[at];
-              } else {
-                t = __ldg(tab + at);
+            for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], tab_load<SMEM>(t + u));
+          }
+        } else {
+          for (int pl = 0; pl < pc; ++pl) {  // same sums, every cell looked up on its own
+            const int ro = (int)py[pl] * lt.ts;
+            const float qx = lqx[pl];
+#pragma unroll
+            for (int u = 0; u < LS_IU; ++u) {
+              int col = 0;
+              if (i0 + u < n_t) {
+                const int cx = cell_fast(cm, __fadd_rn(qx, s_tlow[i0 + u])) - lt.ox;
+                if ((unsigned)cx < (unsigned)lt.tw) col = cx + lt.xpad;
               }
-              acc[u] = __dadd_rn(acc[u], t);
+              acc[u] = __dadd_rn(acc[u], tab_load<SMEM>(lt.tab + ro + col));
             }
           }
         }
@@ -161,14 +189,14 @@ __device__ __forceinline__ void low_score_rounds(
       }
       if (single) {
 #pragma unroll
-        for (int u = 0; u < LS_JT; ++u) {  // this warp's rotations ascend: '>' keeps the earliest
+        for (int u = 0; u < LS_IU; ++u) {  // this warp's rotations ascend: '>' keeps the earliest
           const double sc = __ddiv_rn(acc[u], (double)n_pts);
           if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r; }
         }
       } else {
 #pragma unroll
-        for (int u = 0; u < LS_JT; ++u)  // probability / pointcloud.size() (cc:76)
-          s_res[warp * LS_TILE + (lj + u) * LS_TI + li] = __ddiv_rn(acc[u], (double)n_pts);
+        for (int u = 0; u < LS_IU; ++u)  // probability / pointcloud.size() (cc:76)
+          s_res[warp * LS_TILE + (half * LS_IU + u) * LS_TJ + lj] = __ddiv_rn(acc[u], (double)n_pts);
       }
     }
     if (single) continue;
@@ -179,7 +207,7 @@ __device__ __forceinline__ void low_score_rounds(
       const int t = threadIdx.x;
       for (int w = 0; w < LS_WARPS && round0 + w < n_items; ++w) {
         const int it = round0 + w, r = rot0 + it / n_tiles, tile = it % n_tiles;
-        const int i = (tile % tiles_x) * LS_TI + (t & 15), j = (tile / tiles_x) * LS_TJ + (t >> 4);
+        const int i = (tile % tiles_x) * LS_TI + t / LS_TJ, j = (tile / tiles_x) * LS_TJ + t % LS_TJ;
         if (i < n_t && j < n_t) {
           const double sc = s_res[w * LS_TILE + t];
           const int tr = i * n_t + j;
@@ -192,12 +220,12 @@ __device__ __forceinline__ void low_score_rounds(
   if (single) {
     // merge the warps: higher score wins, equal scores keep the smaller rotation
     for (int w = 0; w < LS_WARPS; ++w) {
-      if (warp == w && li < n_t) {
+      if (warp == w && lj < n_t) {
 #pragma unroll
-        for (int u = 0; u < LS_JT; ++u) {
-          const int j = lj + u;
-          if (j < n_t) {
-            const int tr = li * n_t + j;
+        for (int u = 0; u < LS_IU; ++u) {
+          const int i = half * LS_IU + u;
+          if (i < n_t) {
+            const int tr = i * n_t + lj;
             if (rbest[u] > s_best[tr] || (rbest[u] == s_best[tr] && rbest_rot[u] < s_best_rot[tr])) {
               s_best[tr] = rbest[u];
               s_best_rot[tr] = rbest_rot[u];
@@ -214,19 +242,20 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
     Geometry g, SearchGrid sg, CellMap cm_global, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
-    const Rotation* __restrict__ rots, SearchBuffers sb) {
+    const Rotation* __restrict__ rots, SearchBuffers sb, int table_cells) {
   const PairWork pw = pairs[blockIdx.y];
   const int rot0 = blockIdx.x * sb.rot_per_chunk;
   if (rot0 >= pw.n_rot) return;
   const int rot1 = min(pw.n_rot, rot0 + sb.rot_per_chunk);
   const int n_t = sg.n_t, n_tr = n_t * n_t;
+  const bool single = n_t <= LS_TI;
 
   extern __shared__ __align__(16) unsigned char s_raw[];
-  double* s_tab = reinterpret_cast<double*>(s_raw);                  // [LS_TABLE_CELLS]
-  double* s_res = s_tab + LS_TABLE_CELLS;                            // [LS_WARPS][LS_TILE]
-  int* s_lists = reinterpret_cast<int*>(s_res + LS_WARPS * LS_TILE); // cell lists (16 B aligned)
-  double* s_best = reinterpret_cast<double*>(s_lists + LS_WARPS * LS_LIST_INTS);  // [n_tr]
-  int* s_best_rot = reinterpret_cast<int*>(s_best + n_tr);           // [n_tr]
+  double* s_tab = reinterpret_cast<double*>(s_raw);                  // [table_cells]
+  double* s_res = s_tab + table_cells;                               // [LS_WARPS][LS_TILE] or none
+  double* s_best = s_res + (single ? 0 : LS_WARPS * LS_TILE);        // [n_tr]
+  unsigned char* s_lists = reinterpret_cast<unsigned char*>(s_best + n_tr);
+  int* s_best_rot = reinterpret_cast<int*>(s_lists + LS_WARPS * LS_LIST_BYTES);  // [n_tr]
   float* s_thr = reinterpret_cast<float*>(s_best_rot + n_tr);
   float* s_tlow = s_thr + (g.wl + 2);                                // [n_t]
 
@@ -234,7 +263,7 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
   const TableMeta tm = metas[pw.table];
   const double* __restrict__ lowlog = slots[pw.table].lowlog;
-  const int lstride = g.wl + 1;
+  const int lstride = lowlog_stride(g.wl);
 
   for (int k = threadIdx.x; k < g.wl + 2; k += LS_THREADS) s_thr[k] = cm_global.lowf[k];
   for (int k = threadIdx.x; k < n_t; k += LS_THREADS) s_tlow[k] = sg.t_low[k];
@@ -247,24 +276,30 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
 
   // box of low-res cells above the floor; everything outside reads log(1e-10)
   const bool empty = tm.lx1 < tm.lx0 || tm.ly1 < tm.ly0;
-  const int tw = empty ? 0 : tm.lx1 - tm.lx0 + 1, th = empty ? 0 : tm.ly1 - tm.ly0 + 1;
-  const int ox = empty ? 0 : tm.lx0, oy = empty ? 0 : tm.ly0;
-  const bool fits = (tw + 1) * (th + 1) <= LS_TABLE_CELLS;
+  LowTab lt;
+  lt.tw = empty ? 0 : tm.lx1 - tm.lx0 + 1;
+  lt.th = empty ? 0 : tm.ly1 - tm.ly0 + 1;
+  lt.ox = empty ? 0 : tm.lx0;
+  lt.oy = empty ? 0 : tm.ly0;
+  const int ts = (lt.tw + 2 * LS_XPAD) | 1;  // odd stride: see the bank note above
+  const bool fits = ts * (lt.th + 1) <= table_cells && lt.th < 65535;
   if (fits) {
-    const int ts = tw + 1;
-    const double floor_log = lowlog[(size_t)g.wl * lstride + g.wl];
-    for (int k = threadIdx.x; k < ts * (th + 1); k += LS_THREADS) {
-      const int r = k / ts, c = k - r * ts;
-      s_tab[k] = (r < th && c < tw) ? lowlog[(size_t)(oy + r) * lstride + ox + c] : floor_log;
+    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD; lt.floor_row = lt.th;
+    for (int k = threadIdx.x; k < ts * (lt.th + 1); k += LS_THREADS) {
+      const int r = k / ts, c = k - r * ts - LS_XPAD;
+      s_tab[k] = (r < lt.th && (unsigned)c < (unsigned)lt.tw)
+                     ? lowlog[(size_t)(lt.oy + r) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
     }
     __syncthreads();
-    low_score_rounds<true>(g, sg, cm, s_tlow, s_tab, ox, oy, tw, th, ts, a, n_pts,
-                           rots + pw.rot_begin, rot0, rot1, s_lists, s_res, s_best, s_best_rot);
+    low_score_rounds<true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
+                           s_res, s_best, s_best_rot);
   } else {
+    // whole table from global memory: lowlog has the same padded layout
+    lt.tab = lowlog; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
+    lt.xpad = CSM_LOW_PAD; lt.floor_row = g.wl;
     __syncthreads();
-    // whole table from global memory: row wl / column wl of lowlog hold the floor
-    low_score_rounds<false>(g, sg, cm, s_tlow, lowlog, 0, 0, g.wl, g.wl, lstride, a, n_pts,
-                            rots + pw.rot_begin, rot0, rot1, s_lists, s_res, s_best, s_best_rot);
+    low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
+                            s_res, s_best, s_best_rot);
   }
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
@@ -276,9 +311,9 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
 void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm_low,
                       const float2* points, const long long* offsets, const TableSlot* slots,
                       const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
-                      int n_pairs, const SearchBuffers& sb, cudaStream_t stream) {
+                      int n_pairs, const SearchBuffers& sb, int table_cells, cudaStream_t stream) {
   if (n_pairs <= 0) return;
-  const size_t smem = low_score_smem_bytes(sg.n_t, g.wl);
+  const size_t smem = low_score_smem_bytes(sg.n_t, g.wl, table_cells);
   static size_t configured = 0;
   if (smem > configured) {
     cudaFuncSetAttribute(low_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -286,7 +321,7 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
   }
   dim3 grid(sb.chunks_per_pair, n_pairs);
   low_score_kernel<<<grid, LS_THREADS, smem, stream>>>(g, sg, cm_low, points, offsets, slots,
-                                                       metas, pairs, rots, sb);
+                                                       metas, pairs, rots, sb, table_cells);
 }
 
 // ---------------------------------------------------------------------------

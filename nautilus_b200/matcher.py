@@ -80,12 +80,13 @@ class CorrelativeScanMatcher:
 
     def __init__(self, scanner_range: float, trans_range: float, low_res: float,
                  high_res: float, *, rot_step: float = 0.0, device: int = 0,
-                 margin_cells: int = 0, max_tables: int = 0, blur_sigma: float = 0.0):
+                 margin_cells: int = 0, max_tables: int = 0, blur_sigma: float = 0.0,
+                 stage_cells: int = 0):
         self._L = _lib.lib()
         self.range_, self.trans_range_ = float(scanner_range), float(trans_range)
         self.low_res_, self.high_res_ = float(low_res), float(high_res)
         p = Params(scanner_range, trans_range, low_res, high_res, rot_step, blur_sigma,
-                   device, margin_cells, max_tables, 0)
+                   device, margin_cells, max_tables, stage_cells)
         h = C.c_void_p()
         check(self._L.nautilus_csm_create(C.byref(p), C.byref(h)))
         self._h = h
