@@ -86,7 +86,9 @@ struct LowTab {
   int tw, th;         // box width / height in cells
   int ts;             // row stride in doubles
   int xpad;           // floor columns left of the box (column 0 always reads the floor)
-  int floor_row;      // a row that reads the floor
+  int row0;           // list value of box row 0 (1 when a floor row is staged above the box)
+  int row_above;      // list value for cells above the box (cy < 0): a floor row
+  int row_below;      // list value for cells below the box or outside the grid
 };
 
 template <bool SMEM>
@@ -130,13 +132,19 @@ __device__ __forceinline__ void low_score_rounds(
         bool odd = false;  // this lane's point has x cells that are not consecutive
         if (lane < pc) {  // phase A: this lane's point -> rows / first columns of the tile
           const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
+          // Rows of the 16 y translations: consecutive cells clamped to the floor
+          // rows on either side of the box, so the 16 lanes of a half-warp read
+          // rows inside one span of 16 -> 16 different bank pairs (odd stride).
+          // Lanes past the grid repeat the last row (same address: a broadcast).
+          int row = lt.row_below;
 #pragma unroll 4
           for (int k = 0; k < LS_TJ; ++k) {
             const int jj = tj * LS_TJ + k;
-            int row = lt.floor_row;
             if (jj < n_t) {
-              const int cy = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj])) - lt.oy;  // Vector2f(., y_trans)
-              if ((unsigned)cy < (unsigned)lt.th) row = cy;
+              const int cg = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));  // Vector2f(., y_trans)
+              const int cy = cg - lt.oy;
+              row = cg < 0 ? lt.row_below
+                           : (cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0));
             }
             ly[k * LS_LROW + lane] = (unsigned short)row;
           }
@@ -282,12 +290,14 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   lt.ox = empty ? 0 : tm.lx0;
   lt.oy = empty ? 0 : tm.ly0;
   const int ts = (lt.tw + 2 * LS_XPAD) | 1;  // odd stride: see the bank note above
-  const bool fits = ts * (lt.th + 1) <= table_cells && lt.th < 65535;
+  const bool fits = ts * (lt.th + 2) <= table_cells && lt.th < 65533;
   if (fits) {
-    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD; lt.floor_row = lt.th;
-    for (int k = threadIdx.x; k < ts * (lt.th + 1); k += LS_THREADS) {
-      const int r = k / ts, c = k - r * ts - LS_XPAD;
-      s_tab[k] = (r < lt.th && (unsigned)c < (unsigned)lt.tw)
+    // staged rows: 0 = floor, 1 .. th = box, th + 1 = floor
+    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD;
+    lt.row0 = 1; lt.row_above = 0; lt.row_below = lt.th + 1;
+    for (int k = threadIdx.x; k < ts * (lt.th + 2); k += LS_THREADS) {
+      const int r = k / ts - 1, c = k - (r + 1) * ts - LS_XPAD;
+      s_tab[k] = ((unsigned)r < (unsigned)lt.th && (unsigned)c < (unsigned)lt.tw)
                      ? lowlog[(size_t)(lt.oy + r) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
     }
     __syncthreads();
@@ -296,7 +306,7 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   } else {
     // whole table from global memory: lowlog has the same padded layout
     lt.tab = lowlog; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
-    lt.xpad = CSM_LOW_PAD; lt.floor_row = g.wl;
+    lt.xpad = CSM_LOW_PAD; lt.row0 = 0; lt.row_above = g.wl; lt.row_below = g.wl;
     __syncthreads();
     low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
                             s_res, s_best, s_best_rot);
