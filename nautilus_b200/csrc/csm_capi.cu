@@ -244,7 +244,25 @@ int build_search_grid(NautilusCsm* h) {
   h->grid.n_h_max = nh_max;
   h->grid.n_h = h->n_h_dev.p;
   h->grid.t_high = h->t_high_dev.p;
-  h->grid.trans_low_x0 = 0.f;
+  {
+    // Regular-cell shortcut of the low-res scorer.  With x_k = (double)fl(p + t_k) / rl
+    // the exact quotient of translation k, x_k - x_k0 - (k - k0) is bounded by the
+    // two float additions (one ulp at the largest |p + t|) plus how far the stored
+    // float translations are from an exact one-cell step; the device estimate of
+    // x_k0 (float product with the rounded 1/rl) is within 2^-22 * |x|.  reg_eps
+    // is four times the sum, so floor(x_k) = floor(estimate) + (k - k0).
+    const double vmax = h->params.scanner_range + T + rl;
+    const double qmax = vmax / rl + 2.0;
+    double dev = 0.0;
+    for (int k0 = 0; k0 < n_t; ++k0)
+      for (int k = k0; k < std::min(n_t, k0 + 16); ++k)
+        dev = std::max(dev, fabs((double)h->t_low_host[k] - (double)h->t_low_host[k0] - (k - k0) * rl));
+    const double ulp = (double)nextafterf((float)vmax, INFINITY) - (double)(float)vmax;
+    const double eps = 4.0 * (qmax * ldexp(1.0, -22) + (ulp + dev) / rl) + 1e-6;
+    h->grid.reg_eps = (float)std::min(eps, 0.49);  // >= 0.5 never passes: always cell_fast
+    if (eps >= 0.49) h->grid.reg_eps = 0.5f;
+    h->grid.reg_qmax = (float)qmax;
+  }
   // exact cell maps for the two grids
   int rc2;
   h->thr_low_host = make_thresholds(rl, h->geo.wl, &h->cm_low.qlo, &h->cm_low.qhi);

@@ -39,7 +39,11 @@ struct SearchGrid {
   int n_h_max;           // max hi-res steps per window axis
   const int* n_h;        // [n_t] hi-res steps of the window opened at low index i
   const float* t_high;   // [n_t*n_h_max] (float)x_trans of the hi-res steps (cc:126-129)
-  float trans_low_x0;    // unused placeholder for alignment
+  // Low-res scorer shortcut: if the float estimate e of (p + t_low[k0]) / low_res
+  // has |e| < reg_qmax and a fractional part in (reg_eps, 1 - reg_eps), then the
+  // cells of t_low[k0 + k], k < 16, are floor(e) + k (proved on the host from the
+  // actual t_low values and float error bounds, build_search_grid).
+  float reg_eps, reg_qmax;
 };
 
 // Per-pair work item.

@@ -30,6 +30,18 @@ __device__ __forceinline__ float2 rotate_point(float2 p, float c, float s) {
   return q;
 }
 
+// floor(v / res) + dim/2 (possibly outside the grid) when the float estimate of
+// the quotient lies more than eps from a cell edge and below qmax; false when
+// the caller has to use cell_fast.  See SearchGrid::reg_eps.
+__device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps, float qmax,
+                                           int* cell) {
+  const float e = __fmul_rn(v, m.inv_res);
+  const float fl = floorf(e);
+  const float fr = e - fl;
+  *cell = (int)fl + m.half;
+  return fabsf(e) < qmax && fr > eps && fr < 1.0f - eps;
+}
+
 // ---------------------------------------------------------------------------
 // K5  low-res exhaustive scoring + per-translation max over a theta chunk.
 // grid = (theta chunks, pairs), 8 warps per block.
@@ -63,10 +75,9 @@ constexpr int LS_TI = 2 * LS_IU;     // x translations per tile
 constexpr int LS_TILE = LS_TI * LS_TJ;
 constexpr int LS_XPAD = CSM_LOW_PAD;  // floor columns on either side of the staged box
 static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding");
-constexpr int LS_LROW = LS_PC + 2;   // u16 entries per row-list row (17 words: odd)
-// per-warp lists: row index per (y translation, point), first column per
-// (half, point), rotated x per point
-constexpr int LS_LIST_BYTES = LS_TJ * LS_LROW * 2 + 2 * LS_PC * 4 + LS_PC * 4;
+// per-warp lists, one entry per point of the chunk: first row, first column of
+// either half, rotated x and y
+constexpr int LS_LIST_BYTES = 5 * LS_PC * 4;
 
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   const bool single = n_t <= LS_TI;
@@ -107,9 +118,10 @@ __device__ __forceinline__ void low_score_rounds(
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
   const int n_tiles = tiles_x * tiles_y;
   const int n_items = (rot1 - rot0) * n_tiles;
-  unsigned short* ly = reinterpret_cast<unsigned short*>(s_lists + warp * LS_LIST_BYTES);
-  int* lxb = reinterpret_cast<int*>(ly + LS_TJ * LS_LROW);   // [2][LS_PC]
+  int* lyb = reinterpret_cast<int*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC]
+  int* lxb = lyb + LS_PC;                                     // [2][LS_PC]
   float* lqx = reinterpret_cast<float*>(lxb + 2 * LS_PC);    // [LS_PC]
+  float* lqy = lqx + LS_PC;                                   // [LS_PC]
   const int lj = lane & 15, half = lane >> 4;
   const bool single = (n_tiles == 1);  // the reference's 14 x 14 grid: best stays in registers
   double rbest[LS_IU];
@@ -129,58 +141,60 @@ __device__ __forceinline__ void low_score_rounds(
       for (int u = 0; u < LS_IU; ++u) acc[u] = 0.0;
       for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
         const int pc = min(LS_PC, n_pts - p0);
-        bool odd = false;  // this lane's point has x cells that are not consecutive
-        if (lane < pc) {  // phase A: this lane's point -> rows / first columns of the tile
+        // phase A (lane = point): first cell of the tile's 16 y translations and of
+        // each group of 7 x translations.  The translations step by exactly one
+        // cell, so when the first sum lies clear of a cell edge (cell_clear, margin
+        // SearchGrid::reg_eps proven on the host) the others are the next cells.
+        bool odd = false;  // this lane's point needs every cell looked up on its own
+        if (lane < pc) {
           const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
-          // Rows of the 16 y translations: consecutive cells clamped to the floor
-          // rows on either side of the box, so the 16 lanes of a half-warp read
-          // rows inside one span of 16 -> 16 different bank pairs (odd stride).
-          // Lanes past the grid repeat the last row (same address: a broadcast).
-          int row = lt.row_below;
-#pragma unroll 4
-          for (int k = 0; k < LS_TJ; ++k) {
-            const int jj = tj * LS_TJ + k;
-            if (jj < n_t) {
-              const int cg = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));  // Vector2f(., y_trans)
-              const int cy = cg - lt.oy;
-              row = cg < 0 ? lt.row_below
-                           : (cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0));
-            }
-            ly[k * LS_LROW + lane] = (unsigned short)row;
-          }
+          int cy0, wy = INT_MIN;
+          if (cell_clear(cm, __fadd_rn(q.y, s_tlow[tj * LS_TJ]), sg.reg_eps, sg.reg_qmax, &cy0))
+            wy = cy0 - lt.oy;  // Vector2f(., y_trans): box row of the first y translation
+          odd = wy == INT_MIN;
+          lyb[lane] = wy;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             const int ii0 = ti * LS_TI + hh * LS_IU;
             int word = 0;  // a group past the grid reads the floor padding
             if (ii0 < n_t) {
-              const int c0 = cell_fast(cm, __fadd_rn(q.x, s_tlow[ii0]));  // Vector2f(x_trans, .)
-              bool regular = c0 >= 0;
-#pragma unroll
-              for (int u = 1; u < LS_IU; ++u)
-                if (ii0 + u < n_t)
-                  regular = regular && (cell_fast(cm, __fadd_rn(q.x, s_tlow[ii0 + u])) == c0 + u);
+              int c0;
               // columns c0 .. c0+6 relative to the padded box; a window entirely
               // outside the box is moved onto the floor padding
-              word = regular ? max(0, min(c0 - lt.ox + lt.xpad, lt.tw + lt.xpad)) : -1;
+              if (cell_clear(cm, __fadd_rn(q.x, s_tlow[ii0]), sg.reg_eps, sg.reg_qmax, &c0))
+                word = max(0, min(c0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+              else
+                odd = true;
             }
             lxb[hh * LS_PC + lane] = word;
-            odd = odd || word < 0;
           }
           lqx[lane] = q.x;
+          lqy[lane] = q.y;
         }
         const bool any_odd = __any_sync(0xffffffffu, odd);  // also orders the list writes
-        const unsigned short* py = ly + lj * LS_LROW;
         const int* px = lxb + half * LS_PC;
         if (!any_odd) {
 #pragma unroll 4
           for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 consecutive cells per lane, point order
-            const double* t = lt.tab + ((int)py[pl] * lt.ts + px[pl]);
+            // rows of the 16 lanes are consecutive, clamped to the floor rows on
+            // either side of the box: one span of 16 rows -> 16 different bank pairs
+            const int cy = lyb[pl] + lj;
+            const int row = cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0);
+            const double* t = lt.tab + (row * lt.ts + px[pl]);
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], tab_load<SMEM>(t + u));
           }
         } else {
+          const int jj = tj * LS_TJ + lj;
           for (int pl = 0; pl < pc; ++pl) {  // same sums, every cell looked up on its own
-            const int ro = (int)py[pl] * lt.ts;
+            int row = lt.row_below;
+            if (jj < n_t) {
+              const int cg = cell_fast(cm, __fadd_rn(lqy[pl], s_tlow[jj]));
+              const int cy = cg - lt.oy;
+              row = cg < 0 ? lt.row_below
+                           : (cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0));
+            }
+            const int ro = row * lt.ts;
             const float qx = lqx[pl];
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) {
