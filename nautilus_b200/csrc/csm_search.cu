@@ -66,7 +66,7 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // whose box does not fit the budget are gathered from global memory through L1.
 // Sums run over points in point order, one lane per candidate, like cc:66-77.
 // ---------------------------------------------------------------------------
-constexpr int LS_WARPS = 8;
+constexpr int LS_WARPS = 12;
 constexpr int LS_THREADS = LS_WARPS * 32;
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
 constexpr int LS_TJ = 16;            // y translations per tile

@@ -247,6 +247,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
 // the anti-causal pass walks back to the rectangle's first row.
 // ---------------------------------------------------------------------------
 constexpr int YP_THREADS = 128;
+constexpr int YP_B = 8;  // rows loaded ahead of the recursion
 
 __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
@@ -278,13 +279,24 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
     if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
       iplus = colp[(size_t)(g.w - 1 - m.ay0) * stride];
 
-    // causal pass: rows cy0 .. ay1
-    for (int r = m.cy0; r <= m.ay1; ++r) {
-      double* p = colp + (size_t)(r - m.ay0) * stride;
-      const double x = (r <= m.cy1 && flag[r - m.cy0]) ? *p : 0.0;
-      const double v0 = vv_step(x, v1, v2, v3, a1, a2, a3);
-      *p = v0;
-      v3 = v2; v2 = v1; v1 = v0;
+    // causal pass: rows cy0 .. ay1.  The recursion is serial but its inputs are
+    // not: YP_B rows are loaded first (independent loads in flight), then stepped.
+    for (int r0 = m.cy0; r0 <= m.ay1; r0 += YP_B) {
+      double xin[YP_B];
+#pragma unroll
+      for (int u = 0; u < YP_B; ++u) {
+        const int r = r0 + u;
+        xin[u] = (r <= m.cy1 && flag[r - m.cy0]) ? colp[(size_t)(r - m.ay0) * stride] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < YP_B; ++u) {
+        const int r = r0 + u;
+        if (r <= m.ay1) {
+          const double v0 = vv_step(xin[u], v1, v2, v3, a1, a2, a3);
+          colp[(size_t)(r - m.ay0) * stride] = v0;
+          v3 = v2; v2 = v1; v1 = v0;
+        }
+      }
     }
     int r = m.ay1;
     if (m.ay1 == g.w - 1) {  // Triggs boundary at the grid edge
@@ -297,14 +309,24 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
     } else {
       v1 = v2 = v3 = 0.0;
     }
-    // anti-causal pass down to the rectangle's first row
-    for (; r >= m.ay0; --r) {
-      double* p = colp + (size_t)(r - m.ay0) * stride;
-      const double y = (r >= m.cy0) ? *p : 0.0;
-      const double v0 = vv_step(__dmul_rn(y, sum), v1, v2, v3, a1, a2, a3);
-      *p = v0;
-      vmax = fmax(vmax, v0); vmin = fmin(vmin, v0);
-      v3 = v2; v2 = v1; v1 = v0;
+    // anti-causal pass down to the rectangle's first row, same batching
+    for (int r0 = r; r0 >= m.ay0; r0 -= YP_B) {
+      double yin[YP_B];
+#pragma unroll
+      for (int u = 0; u < YP_B; ++u) {
+        const int rr = r0 - u;
+        yin[u] = (rr >= m.cy0) ? colp[(size_t)(rr - m.ay0) * stride] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < YP_B; ++u) {
+        const int rr = r0 - u;
+        if (rr >= m.ay0) {
+          const double v0 = vv_step(__dmul_rn(yin[u], sum), v1, v2, v3, a1, a2, a3);
+          colp[(size_t)(rr - m.ay0) * stride] = v0;
+          vmax = fmax(vmax, v0); vmin = fmin(vmin, v0);
+          v3 = v2; v2 = v1; v1 = v0;
+        }
+      }
     }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -330,6 +352,8 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
 // maxima in shared memory, then reduces them per x-window.  Normalisation is
 // monotone, so max(normalise(v)) == normalise(max(v)) bit for bit.
 // ---------------------------------------------------------------------------
+constexpr int NP_B = 6;  // rows of a pooling window loaded ahead (windows are 9-11 rows)
+
 __device__ __forceinline__ double normalise_value(double v, double mn, double range) {
   // (v - m) / (M - m) * (1 - 0) + 0 ; the last two operations are exact no-ops
   return __ddiv_rn(__dsub_rn(v, mn), range);
@@ -356,12 +380,20 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
   for (int c = threadIdx.x; c < aw; c += blockDim.x) {
     double cm = -INFINITY;
     double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
-    for (int r = rs; r <= re; ++r, p += m.stride) {
-      const double nv = constant ? 0.0 : normalise_value(*p, mn, range);
-      // matching only ever needs log(GetPointValue): take it once per cell here
-      // instead of once per (candidate, point) in the search
-      *p = store_log ? lookup_log(nv) : nv;
-      cm = fmax(cm, nv);
+    for (int r0 = rs; r0 <= re; r0 += NP_B, p += (size_t)NP_B * m.stride) {
+      double v[NP_B];  // the rows of a window are independent: all loads first
+#pragma unroll
+      for (int u = 0; u < NP_B; ++u) v[u] = (r0 + u <= re) ? p[(size_t)u * m.stride] : 0.0;
+#pragma unroll
+      for (int u = 0; u < NP_B; ++u) {
+        if (r0 + u <= re) {
+          const double nv = constant ? 0.0 : normalise_value(v[u], mn, range);
+          // matching only ever needs log(GetPointValue): take it once per cell here
+          // instead of once per (candidate, point) in the search
+          p[(size_t)u * m.stride] = store_log ? lookup_log(nv) : nv;
+          cm = fmax(cm, nv);
+        }
+      }
     }
     s_colmax[c] = cm;
   }
