@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -401,6 +402,12 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
     return fail(NAUTILUS_ECUDA, "cudaStreamCreate failed");
   }
   h->stream = h->own_stream;
+  {
+    int lo = 0, hi = 0;  // table builds get the highest priority: they fill the slots
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);  // the searching kernels leave free
+    if (cudaStreamCreateWithPriority(&h->table_stream, cudaStreamNonBlocking, hi) != cudaSuccess)
+      h->table_stream = nullptr;
+  }
   h->pool_host = make_pool_list(p->scanner_range, p->low_res, p->high_res, (uint64_t)h->geo.w,
                                 (uint64_t)h->geo.wl);
   h->geo.n_pool = (int)h->pool_host.s.size();
@@ -434,6 +441,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();
   h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
   for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
+  if (h->table_stream) cudaStreamDestroy(h->table_stream);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -553,11 +561,28 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
 
   rc = ensure_slots(h, n_targets);
   if (rc) return rc;
+  // ---- waves.  A batch whose targets fit the resident slots is one wave.  With
+  // more targets than slots the slots are reused wave after wave.  Splitting a
+  // batch that fits into several waves (NAUTILUS_CSM_WAVES) builds the tables of
+  // wave w+1 on a second stream while wave w is searched; measured on B200 it
+  // loses more to the per-wave tails of the search than the overlap gains
+  // (61.5 / 68.2 / 71.7 ms per step for 1 / 2 / 3 waves), so the default is one.
   const int n_slots = h->n_slots;
-  const int n_waves = (n_targets + n_slots - 1) / n_slots;
+  const bool ring = n_targets > n_slots;
+  int wave_tables;
+  if (ring) {
+    wave_tables = n_slots;
+  } else {
+    const char* env = getenv("NAUTILUS_CSM_WAVES");
+    int n_sub = env ? atoi(env) : 1;
+    n_sub = std::max(1, std::min(n_sub, n_targets));
+    wave_tables = (n_targets + n_sub - 1) / n_sub;
+  }
+  const int n_waves = (n_targets + wave_tables - 1) / wave_tables;
+  auto slot_base = [&](int w) { return ring ? 0 : w * wave_tables; };
   int max_wave_pairs = 0;
   for (int w = 0; w < n_waves; ++w) {
-    const int t0 = w * n_slots, t1 = std::min(n_targets, t0 + n_slots);
+    const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
     for (int k = first_pair[t0]; k < first_pair[t1]; ++k) sorted[k].table -= t0;
     max_wave_pairs = std::max(max_wave_pairs, first_pair[t1] - first_pair[t0]);
   }
@@ -598,22 +623,42 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
                          cudaMemcpyHostToDevice, st));
 
   int launches = 0;
-  size_t ev = 0;
-  CU_TRY(cudaEventRecord(get_event(h, ev++), st));
-  for (int w = 0; w < n_waves; ++w) {
-    const int t0 = w * n_slots, t1 = std::min(n_targets, t0 + n_slots);
-    const int k0 = first_pair[t0], k1 = first_pair[t1];
+  // events: 0 = start; per wave w: 1+5w tables begin, +1 tables end (table stream),
+  // +2 search begin, +3 low-res end, +4 refine end (caller stream)
+  auto evt = [&](int w, int k) { return get_event(h, 1 + 5 * (size_t)w + k); };
+  cudaStream_t tst = h->table_stream ? h->table_stream : st;
+  CU_TRY(cudaEventRecord(get_event(h, 0), st));
+  CU_TRY(cudaStreamWaitEvent(tst, get_event(h, 0), 0));  // the lists above are uploaded on st
+  auto issue_tables = [&](int w) -> int {
+    const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
+    const int base = slot_base(w);
+    if (ring && w >= 1) CU_TRY(cudaStreamWaitEvent(tst, evt(w - 1, 4), 0));  // slots still being searched
+    CU_TRY(cudaEventRecord(evt(w, 0), tst));
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
-                      h->slots_dev.p, h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, &launches);
-    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
-    launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
-                     h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, table_cells, st);
-    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
-    launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p,
-                  h->metas_dev.p, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
+                      h->slots_dev.p + base, h->metas_dev.p + base, h->pool_dev.d, t1 - t0, true,
+                      tst, &launches);
+    CU_TRY(cudaEventRecord(evt(w, 1), tst));
+    return NAUTILUS_OK;
+  };
+  if ((rc = issue_tables(0))) return rc;
+  if (!ring && n_waves > 1 && (rc = issue_tables(1))) return rc;
+  for (int w = 0; w < n_waves; ++w) {
+    const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
+    const int k0 = first_pair[t0], k1 = first_pair[t1];
+    const int base = slot_base(w);
+    CU_TRY(cudaStreamWaitEvent(st, evt(w, 1), 0));
+    CU_TRY(cudaEventRecord(evt(w, 2), st));
+    launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p + base,
+                     h->metas_dev.p + base, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
+                     table_cells, st);
+    CU_TRY(cudaEventRecord(evt(w, 3), st));
+    launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p + base,
+                  h->metas_dev.p + base, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
                   h->results_dev.p, st);
-    CU_TRY(cudaEventRecord(get_event(h, ev++), st));
+    CU_TRY(cudaEventRecord(evt(w, 4), st));
     launches += 2;
+    const int next = ring ? w + 1 : w + 2;  // issued after the event it may wait on is recorded
+    if (next < n_waves && (rc = issue_tables(next))) return rc;
   }
   CU_TRY(cudaGetLastError());
   std::vector<PairResult> res(n_pairs);
@@ -625,12 +670,12 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   h->timings.waves = n_waves;
   for (int w = 0; w < n_waves; ++w) {
     float a = 0, b = 0, c = 0;
-    cudaEventElapsedTime(&a, h->events[3 * w], h->events[3 * w + 1]);
-    cudaEventElapsedTime(&b, h->events[3 * w + 1], h->events[3 * w + 2]);
-    cudaEventElapsedTime(&c, h->events[3 * w + 2], h->events[3 * w + 3]);
+    cudaEventElapsedTime(&a, evt(w, 0), evt(w, 1));
+    cudaEventElapsedTime(&b, evt(w, 2), evt(w, 3));
+    cudaEventElapsedTime(&c, evt(w, 3), evt(w, 4));
     h->timings.ms_tables += a; h->timings.ms_low += b; h->timings.ms_refine += c;
   }
-  cudaEventElapsedTime(&h->timings.ms_total, h->events[0], h->events[3 * n_waves]);
+  cudaEventElapsedTime(&h->timings.ms_total, get_event(h, 0), evt(n_waves - 1, 4));
 
   h->last_n_pairs = n_pairs;
   int bad = 0;

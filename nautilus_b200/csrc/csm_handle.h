@@ -105,6 +105,7 @@ struct NautilusCsm {
   double rot_step;
   int device;
   cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaStream_t table_stream = nullptr;  // table builds of the next wave overlap the search
   int sm_count = 148;
 
   // tables
