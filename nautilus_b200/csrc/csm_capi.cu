@@ -138,7 +138,7 @@ void free_slots(NautilusCsm* h) {
 size_t slot_bytes(const Geometry& g) {
   const size_t w = g.w, wl = g.wl;
   return sizeof(double) * ((w + 3) & ~(size_t)3) * w + sizeof(unsigned) * g.bm_stride * w + w +
-         sizeof(double) * (wl * wl + (wl + 1) * (size_t)lowlog_stride((int)wl));
+         sizeof(double) * (wl * wl + (wl + 2) * (size_t)lowlog_stride((int)wl));
 }
 
 // Makes at least `want` table slots resident (bounded by params.max_tables and
@@ -160,7 +160,7 @@ int ensure_slots(NautilusCsm* h, int want) {
   CU_TRY(cudaMalloc(&h->slab_bitmap, sizeof(unsigned) * (size_t)g.bm_stride * w * want));
   CU_TRY(cudaMalloc(&h->slab_rowflag, w * (size_t)want));
   CU_TRY(cudaMalloc(&h->slab_low, sizeof(double) * wl * wl * want));
-  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 1) * lowlog_stride((int)wl) * want));
+  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 2) * lowlog_stride((int)wl) * want));
   h->slots_host.resize(want);
   for (int i = 0; i < want; ++i) {
     TableSlot& s = h->slots_host[i];
@@ -168,7 +168,7 @@ int ensure_slots(NautilusCsm* h, int want) {
     s.bitmap = h->slab_bitmap + (size_t)g.bm_stride * w * i;
     s.rowflag = h->slab_rowflag + w * (size_t)i;
     s.low = h->slab_low + wl * wl * (size_t)i;
-    s.lowlog = h->slab_lowlog + (wl + 1) * lowlog_stride((int)wl) * (size_t)i;
+    s.lowlog = h->slab_lowlog + (wl + 2) * lowlog_stride((int)wl) * (size_t)i;
   }
   int rc = h->slots_dev.reserve(want);
   if (rc) return rc;

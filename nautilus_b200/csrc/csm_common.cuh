@@ -61,9 +61,9 @@ struct TableSlot {
   unsigned char* rowflag;  // 1 per occupied-box row that has a point
   double* low;         // wl*wl low-res values (max-pool of the normalised table)
   double* lowlog;      // lookup_log of the low-res table in the padded layout the
-                       // scorer reads: (wl+1) rows of lowlog_stride(wl) doubles,
-                       // cell (x, y) at [y * stride + x + CSM_LOW_PAD]; the pad
-                       // columns on either side and row wl hold the floor
+                       // scorer reads: (wl+2) rows of lowlog_stride(wl) doubles,
+                       // cell (x, y) at [(y + 1) * stride + x + CSM_LOW_PAD]; the
+                       // pad columns on either side, row 0 and row wl+1 hold the floor
 };
 
 // Grid geometry shared by all kernels.

@@ -44,46 +44,52 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 
 // ---------------------------------------------------------------------------
 // K5  low-res exhaustive scoring + per-translation max over a theta chunk.
-// grid = (theta chunks, pairs), 8 warps per block.
+// grid = (theta chunks, pairs), LS_WARPS warps per block.
 //
-// A warp scores one (rotation, translation tile) work item.  A tile is 14
-// x-translations by 16 y-translations: lane & 15 picks the y-translation, lane
-// >> 4 the group of 7 consecutive x-translations whose running sums the lane
-// keeps in registers (the reference's 14 x 14 grid is exactly one tile).
-// Because the translation step equals the cell size (both are low_res_,
-// cc:96-99), the 7 cells a lane needs for one point are 7 CONSECUTIVE doubles
-// of one table row: per point the lane loads its row offset (per-lane list)
-// and the half-warp's first column (one broadcast word), then issues 7 loads at
-// compile-time offsets -- no index arithmetic per lookup.  The rare point whose
-// x cells are not consecutive (a sum that lands within float rounding of a cell
-// edge) is flagged in phase A and recomputed cell by cell.
+// Lanes.  A tile is 14 x-translations by 16 y-translations: lane & 15 picks the
+// y-translation, lane >> 4 the group of 7 consecutive x-translations whose
+// running sums the lane keeps in registers (the reference's 14 x 14 grid is one
+// tile).  Because the translation step equals the cell size (both are low_res_,
+// cc:96-99), the 7 cells a lane needs for one point are 7 CONSECUTIVE doubles of
+// one table row and the 16 lanes of a half-warp read 16 consecutive rows: a
+// point's 14 x 16 patch is addressed by one word (first row, first column of
+// either half), computed once per (rotation, point) in phase A (lane = point).
+// The rare sum that lands within float rounding of a cell edge is flagged there
+// and looked up cell by cell (cell_fast) instead.
 //
-// The part of the pooled log table that lies above the lookup floor
-// (TableMeta::lx0..ly1) is staged in shared memory once per block with 7 floor
-// columns on either side and one floor row, so windows that leave the box need
-// no special case.  The row stride is odd: the 16 lanes of a half-warp read 16
-// different rows at the same column and hit 16 different bank pairs.  Tables
-// whose box does not fit the budget are gathered from global memory through L1.
-// Sums run over points in point order, one lane per candidate, like cc:66-77.
+// Rotations.  A warp scores LS_R consecutive rotations of one tile together.
+// One degree moves a point 5 m away by 9 cm, a third of a cell, so consecutive
+// rotations mostly address the SAME patch: its 7 values are loaded once and
+// added to each rotation's own sums (the word of rotation k is compared with
+// that of k-1; warp-uniform).  Every sum still runs over the points in point
+// order, one lane per candidate, like cc:66-77 -- only the loads are shared.
+//
+// Table.  The part of the pooled log table above the lookup floor (TableMeta::
+// lx0..ly1) is staged in shared memory once per block with 7 floor columns on
+// either side and a floor row above and below, so patches that leave the box
+// need no special case; the row stride is odd, so the 16 rows of a half-warp
+// hit 16 different bank pairs.  Tables whose box does not fit the budget are
+// read from global memory (same padded layout) through L1.
 // ---------------------------------------------------------------------------
-constexpr int LS_WARPS = 12;
+constexpr int LS_WARPS = 8;
 constexpr int LS_THREADS = LS_WARPS * 32;
+constexpr int LS_R = 4;              // rotations scored together by a warp
+static_assert(LS_R == 4, "phase B reads the four patch words of a point as one uint4");
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
 constexpr int LS_TJ = 16;            // y translations per tile
 constexpr int LS_IU = 7;             // x translations per lane
 constexpr int LS_TI = 2 * LS_IU;     // x translations per tile
-constexpr int LS_TILE = LS_TI * LS_TJ;
 constexpr int LS_XPAD = CSM_LOW_PAD;  // floor columns on either side of the staged box
 static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding");
-// per-warp lists, one entry per point of the chunk: first row, first column of
-// either half, rotated x and y
-constexpr int LS_LIST_BYTES = 5 * LS_PC * 4;
+// patch word: bits 0-9 first row + LS_YB, bits 10-20 / 21-31 first column of half 0 / 1
+constexpr int LS_YB = 32;
+constexpr unsigned LS_ODD = 0xffffffffu;  // look every cell up on its own
+// per-warp list: one patch word per (point of the chunk, rotation)
+constexpr int LS_LIST_BYTES = LS_PC * LS_R * 4;
 
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
-  const bool single = n_t <= LS_TI;
   size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
-  if (!single) b += sizeof(double) * LS_WARPS * LS_TILE;             // per-round results
-  b += sizeof(double) * (size_t)n_t * n_t;                           // best score
+  b += sizeof(double) * (((size_t)n_t * n_t + 1) & ~(size_t)1);      // best score
   b += (size_t)LS_WARPS * LS_LIST_BYTES;                             // lists
   b += sizeof(int) * (size_t)n_t * n_t;                              // best rotation
   b += sizeof(float) * ((size_t)wl + 2 + n_t);                       // thresholds, translations
@@ -97,9 +103,8 @@ struct LowTab {
   int tw, th;         // box width / height in cells
   int ts;             // row stride in doubles
   int xpad;           // floor columns left of the box (column 0 always reads the floor)
-  int row0;           // list value of box row 0 (1 when a floor row is staged above the box)
-  int row_above;      // list value for cells above the box (cy < 0): a floor row
-  int row_below;      // list value for cells below the box or outside the grid
+  // rows of tab: 0 = floor, 1 .. th = box rows, th + 1 = floor
+  int row_below;      // th + 1
 };
 
 template <bool SMEM>
@@ -108,146 +113,174 @@ __device__ __forceinline__ double tab_load(const double* p) {
   return __ldg(p);
 }
 
+// The 7 table values of one lane for one (rotation, point), every cell looked up
+// on its own (cell_fast): the path of a point flagged LS_ODD.
+template <bool SMEM>
+__device__ __noinline__ void low_patch_slow(const CellMap& cm, const float* s_tlow, const LowTab& lt,
+                                            float2 q, int n_t, int jj, int i0, double* t) {
+  int row = lt.row_below;
+  if (jj < n_t) {
+    const int cg = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));  // Vector2f(., y_trans)
+    const int cy = cg - lt.oy;
+    row = cg < 0 ? lt.row_below : min(max(cy + 1, 0), lt.row_below);
+  }
+  const int ro = row * lt.ts;
+#pragma unroll
+  for (int u = 0; u < LS_IU; ++u) {
+    int col = 0;  // column 0 reads the floor
+    if (i0 + u < n_t) {
+      const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[i0 + u])) - lt.ox;  // Vector2f(x_trans, .)
+      if ((unsigned)cx < (unsigned)lt.tw) col = cx + lt.xpad;
+    }
+    t[u] = tab_load<SMEM>(lt.tab + ro + col);
+  }
+}
+
 template <bool SMEM>
 __device__ __forceinline__ void low_score_rounds(
     const SearchGrid& sg, const CellMap& cm, const float* s_tlow, const LowTab lt,
     const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
-    int rot1, unsigned char* s_lists, double* s_res, double* s_best, int* s_best_rot) {
+    int rot1, unsigned char* s_lists, double* s_best, int* s_best_rot, bool packable) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
-  const int n_tiles = tiles_x * tiles_y;
-  const int n_items = (rot1 - rot0) * n_tiles;
-  int* lyb = reinterpret_cast<int*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC]
-  int* lxb = lyb + LS_PC;                                     // [2][LS_PC]
-  float* lqx = reinterpret_cast<float*>(lxb + 2 * LS_PC);    // [LS_PC]
-  float* lqy = lqx + LS_PC;                                   // [LS_PC]
+  const int n_groups = (rot1 - rot0 + LS_R - 1) / LS_R;
+  unsigned* lw = reinterpret_cast<unsigned*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC][LS_R]
   const int lj = lane & 15, half = lane >> 4;
-  const bool single = (n_tiles == 1);  // the reference's 14 x 14 grid: best stays in registers
-  double rbest[LS_IU];
-  int rbest_rot[LS_IU];
-#pragma unroll
-  for (int u = 0; u < LS_IU; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
+  const int xshift = half ? 21 : 10;
+  const int ljc = lj - LS_YB + 1;  // row of a patch word = clamp(word row + ljc, floor row above, floor row below)
 
-  for (int round0 = 0; round0 < n_items; round0 += LS_WARPS) {
-    const int item = round0 + warp;
-    if (item < n_items) {
-      const int r = rot0 + item / n_tiles, tile = item % n_tiles;
-      const int ti = tile % tiles_x, tj = tile / tiles_x;
-      const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
-      const Rotation rot = rots[r];
-      double acc[LS_IU];
+  for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
+    const int ti = tile % tiles_x, tj = tile / tiles_x;
+    const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
+    const int jj = tj * LS_TJ + lj;             // this lane's y translation
+    double rbest[LS_IU];  // best of this warp's rotations, which ascend: '>' keeps the earliest
+    int rbest_rot[LS_IU];
 #pragma unroll
-      for (int u = 0; u < LS_IU; ++u) acc[u] = 0.0;
+    for (int u = 0; u < LS_IU; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
+
+    for (int grp = warp; grp < n_groups; grp += LS_WARPS) {
+      const int r0 = rot0 + grp * LS_R;
+      const int nr = min(LS_R, rot1 - r0);
+      double acc[LS_R][LS_IU];
+#pragma unroll
+      for (int k = 0; k < LS_R; ++k)
+#pragma unroll
+        for (int u = 0; u < LS_IU; ++u) acc[k][u] = 0.0;
+
       for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
         const int pc = min(LS_PC, n_pts - p0);
-        // phase A (lane = point): first cell of the tile's 16 y translations and of
-        // each group of 7 x translations.  The translations step by exactly one
-        // cell, so when the first sum lies clear of a cell edge (cell_clear, margin
-        // SearchGrid::reg_eps proven on the host) the others are the next cells.
-        bool odd = false;  // this lane's point needs every cell looked up on its own
+        // phase A (lane = point): patch word of every rotation of the group.  The
+        // translations step by exactly one cell, so when the first sum of an axis
+        // lies clear of a cell edge (cell_clear, margin SearchGrid::reg_eps proven
+        // on the host) the other translations hit the next cells.
+        bool odd = false;
         if (lane < pc) {
-          const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
-          int cy0, wy = INT_MIN;
-          if (cell_clear(cm, __fadd_rn(q.y, s_tlow[tj * LS_TJ]), sg.reg_eps, sg.reg_qmax, &cy0))
-            wy = cy0 - lt.oy;  // Vector2f(., y_trans): box row of the first y translation
-          odd = wy == INT_MIN;
-          lyb[lane] = wy;
+          const float2 p = a[p0 + lane];
+          unsigned word = LS_ODD;
 #pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            const int ii0 = ti * LS_TI + hh * LS_IU;
-            int word = 0;  // a group past the grid reads the floor padding
-            if (ii0 < n_t) {
-              int c0;
-              // columns c0 .. c0+6 relative to the padded box; a window entirely
-              // outside the box is moved onto the floor padding
-              if (cell_clear(cm, __fadd_rn(q.x, s_tlow[ii0]), sg.reg_eps, sg.reg_qmax, &c0))
-                word = max(0, min(c0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+          for (int k = 0; k < LS_R; ++k) {
+            if (k < nr) {  // (past the last rotation the previous word repeats: no loads)
+              word = LS_ODD;
+              const Rotation rot = rots[r0 + k];
+              const float2 q = rotate_point(p, rot.c, rot.s);
+              int cy0, cx0, cx1 = 0;
+              bool ok = packable;
+              ok = cell_clear(cm, __fadd_rn(q.y, s_tlow[tj * LS_TJ]), sg.reg_eps, sg.reg_qmax, &cy0) && ok;
+              ok = cell_clear(cm, __fadd_rn(q.x, s_tlow[ti * LS_TI]), sg.reg_eps, sg.reg_qmax, &cx0) && ok;
+              if (ti * LS_TI + LS_IU < n_t)
+                ok = cell_clear(cm, __fadd_rn(q.x, s_tlow[ti * LS_TI + LS_IU]), sg.reg_eps,
+                                sg.reg_qmax, &cx1) && ok;
               else
-                odd = true;
+                cx1 = cx0;  // no second group in this tile: any window will do
+              if (ok) {
+                // rows yb + lj are clamped to the floor rows by phase B, so yb only
+                // matters within [-17, th]; columns c .. c+6 relative to the padded
+                // box, a window entirely outside moved onto the floor padding
+                const int yb = max(-LS_TJ - 1, min(cy0 - lt.oy, lt.th)) + LS_YB;
+                const int xa = max(0, min(cx0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+                const int xb = max(0, min(cx1 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+                word = (unsigned)yb | ((unsigned)xa << 10) | ((unsigned)xb << 21);
+              }
+              odd = odd || word == LS_ODD;
             }
-            lxb[hh * LS_PC + lane] = word;
+            lw[lane * LS_R + k] = word;
           }
-          lqx[lane] = q.x;
-          lqy[lane] = q.y;
         }
         const bool any_odd = __any_sync(0xffffffffu, odd);  // also orders the list writes
-        const int* px = lxb + half * LS_PC;
+        __syncwarp();
+        // phase B (lane = candidate column): per point, per rotation, 7 consecutive
+        // cells; a rotation whose patch word equals the previous one reuses its loads
         if (!any_odd) {
-#pragma unroll 4
-          for (int pl = 0; pl < pc; ++pl) {  // phase B: 7 consecutive cells per lane, point order
-            // rows of the 16 lanes are consecutive, clamped to the floor rows on
-            // either side of the box: one span of 16 rows -> 16 different bank pairs
-            const int cy = lyb[pl] + lj;
-            const int row = cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0);
-            const double* t = lt.tab + (row * lt.ts + px[pl]);
+#pragma unroll 1
+          for (int pl = 0; pl < pc; ++pl) {
+            const uint4 w4 = *reinterpret_cast<const uint4*>(lw + pl * LS_R);
+            const unsigned wk[LS_R] = {w4.x, w4.y, w4.z, w4.w};
+            double t[LS_IU];
 #pragma unroll
-            for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], tab_load<SMEM>(t + u));
+            for (int k = 0; k < LS_R; ++k) {
+              // the words are the same in every lane: a vote makes the branch uniform
+              if (k == 0 || __any_sync(0xffffffffu, wk[k] != wk[k - 1])) {
+                const int row = min(max((int)(wk[k] & 1023u) + ljc, 0), lt.row_below);
+                const double* src = lt.tab + (row * lt.ts + (int)((wk[k] >> xshift) & 2047u));
+#pragma unroll
+                for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
+              }
+#pragma unroll
+              for (int u = 0; u < LS_IU; ++u) acc[k][u] = __dadd_rn(acc[k][u], t[u]);
+            }
           }
         } else {
-          const int jj = tj * LS_TJ + lj;
-          for (int pl = 0; pl < pc; ++pl) {  // same sums, every cell looked up on its own
-            int row = lt.row_below;
-            if (jj < n_t) {
-              const int cg = cell_fast(cm, __fadd_rn(lqy[pl], s_tlow[jj]));
-              const int cy = cg - lt.oy;
-              row = cg < 0 ? lt.row_below
-                           : (cy < 0 ? lt.row_above : (cy >= lt.th ? lt.row_below : cy + lt.row0));
-            }
-            const int ro = row * lt.ts;
-            const float qx = lqx[pl];
+#pragma unroll 1
+          for (int pl = 0; pl < pc; ++pl) {  // same sums; flagged points cell by cell
+            double t[LS_IU];
+            unsigned prev = LS_ODD;
 #pragma unroll
-            for (int u = 0; u < LS_IU; ++u) {
-              int col = 0;
-              if (i0 + u < n_t) {
-                const int cx = cell_fast(cm, __fadd_rn(qx, s_tlow[i0 + u])) - lt.ox;
-                if ((unsigned)cx < (unsigned)lt.tw) col = cx + lt.xpad;
+            for (int k = 0; k < LS_R; ++k) {
+              const unsigned w = lw[pl * LS_R + k];
+              if (k < nr) {
+                if (w == LS_ODD) {
+                  const Rotation rot = rots[r0 + k];
+                  double ts[LS_IU];  // (a local array: keeps t itself in registers)
+                  low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + pl], rot.c, rot.s), n_t,
+                                       jj, i0, ts);
+#pragma unroll
+                  for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
+                } else if (w != prev) {
+                  const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
+                  const double* src = lt.tab + (row * lt.ts + (int)((w >> xshift) & 2047u));
+#pragma unroll
+                  for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
+                }
+                prev = w;
+#pragma unroll
+                for (int u = 0; u < LS_IU; ++u) acc[k][u] = __dadd_rn(acc[k][u], t[u]);
               }
-              acc[u] = __dadd_rn(acc[u], tab_load<SMEM>(lt.tab + ro + col));
             }
           }
         }
         __syncwarp();
       }
-      if (single) {
 #pragma unroll
-        for (int u = 0; u < LS_IU; ++u) {  // this warp's rotations ascend: '>' keeps the earliest
-          const double sc = __ddiv_rn(acc[u], (double)n_pts);
-          if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r; }
-        }
-      } else {
+      for (int k = 0; k < LS_R; ++k) {
+        if (k < nr) {
 #pragma unroll
-        for (int u = 0; u < LS_IU; ++u)  // probability / pointcloud.size() (cc:76)
-          s_res[warp * LS_TILE + (half * LS_IU + u) * LS_TJ + lj] = __ddiv_rn(acc[u], (double)n_pts);
-      }
-    }
-    if (single) continue;
-    __syncthreads();
-    // merge the round in work-item (= ascending rotation) order: std::max keeps
-    // the earlier entry on ties (cc:109-110)
-    if (threadIdx.x < LS_TILE) {
-      const int t = threadIdx.x;
-      for (int w = 0; w < LS_WARPS && round0 + w < n_items; ++w) {
-        const int it = round0 + w, r = rot0 + it / n_tiles, tile = it % n_tiles;
-        const int i = (tile % tiles_x) * LS_TI + t / LS_TJ, j = (tile / tiles_x) * LS_TJ + t % LS_TJ;
-        if (i < n_t && j < n_t) {
-          const double sc = s_res[w * LS_TILE + t];
-          const int tr = i * n_t + j;
-          if (sc > s_best[tr]) { s_best[tr] = sc; s_best_rot[tr] = r; }
+          for (int u = 0; u < LS_IU; ++u) {
+            const double sc = __ddiv_rn(acc[k][u], (double)n_pts);  // probability / size (cc:76)
+            if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r0 + k; }
+          }
         }
       }
     }
-    __syncthreads();
-  }
-  if (single) {
     // merge the warps: higher score wins, equal scores keep the smaller rotation
+    // (std::max keeps the earlier entry on ties, cc:109-110)
     for (int w = 0; w < LS_WARPS; ++w) {
-      if (warp == w && lj < n_t) {
+      if (warp == w && jj < n_t) {
 #pragma unroll
         for (int u = 0; u < LS_IU; ++u) {
-          const int i = half * LS_IU + u;
-          if (i < n_t) {
-            const int tr = i * n_t + lj;
+          const int i = i0 + u;
+          if (i < n_t && i < ti * LS_TI + LS_TI) {
+            const int tr = i * n_t + jj;
             if (rbest[u] > s_best[tr] || (rbest[u] == s_best[tr] && rbest_rot[u] < s_best_rot[tr])) {
               s_best[tr] = rbest[u];
               s_best_rot[tr] = rbest_rot[u];
@@ -260,7 +293,7 @@ __device__ __forceinline__ void low_score_rounds(
   }
 }
 
-__global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
+__global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
     Geometry g, SearchGrid sg, CellMap cm_global, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
@@ -270,13 +303,11 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   if (rot0 >= pw.n_rot) return;
   const int rot1 = min(pw.n_rot, rot0 + sb.rot_per_chunk);
   const int n_t = sg.n_t, n_tr = n_t * n_t;
-  const bool single = n_t <= LS_TI;
 
   extern __shared__ __align__(16) unsigned char s_raw[];
   double* s_tab = reinterpret_cast<double*>(s_raw);                  // [table_cells]
-  double* s_res = s_tab + table_cells;                               // [LS_WARPS][LS_TILE] or none
-  double* s_best = s_res + (single ? 0 : LS_WARPS * LS_TILE);        // [n_tr]
-  unsigned char* s_lists = reinterpret_cast<unsigned char*>(s_best + n_tr);
+  double* s_best = s_tab + table_cells;                              // [n_tr]
+  unsigned char* s_lists = reinterpret_cast<unsigned char*>(s_best + ((n_tr + 1) & ~1));  // 16 B aligned
   int* s_best_rot = reinterpret_cast<int*>(s_lists + LS_WARPS * LS_LIST_BYTES);  // [n_tr]
   float* s_thr = reinterpret_cast<float*>(s_best_rot + n_tr);
   float* s_tlow = s_thr + (g.wl + 2);                                // [n_t]
@@ -307,23 +338,22 @@ __global__ void __launch_bounds__(LS_THREADS) low_score_kernel(
   const bool fits = ts * (lt.th + 2) <= table_cells && lt.th < 65533;
   if (fits) {
     // staged rows: 0 = floor, 1 .. th = box, th + 1 = floor
-    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD;
-    lt.row0 = 1; lt.row_above = 0; lt.row_below = lt.th + 1;
+    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD; lt.row_below = lt.th + 1;
     for (int k = threadIdx.x; k < ts * (lt.th + 2); k += LS_THREADS) {
       const int r = k / ts - 1, c = k - (r + 1) * ts - LS_XPAD;
       s_tab[k] = ((unsigned)r < (unsigned)lt.th && (unsigned)c < (unsigned)lt.tw)
-                     ? lowlog[(size_t)(lt.oy + r) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
+                     ? lowlog[(size_t)(lt.oy + r + 1) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
     }
     __syncthreads();
     low_score_rounds<true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
-                           s_res, s_best, s_best_rot);
+                           s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
   } else {
     // whole table from global memory: lowlog has the same padded layout
     lt.tab = lowlog; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
-    lt.xpad = CSM_LOW_PAD; lt.row0 = 0; lt.row_above = g.wl; lt.row_below = g.wl;
+    lt.xpad = CSM_LOW_PAD; lt.row_below = g.wl + 1;
     __syncthreads();
     low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
-                            s_res, s_best, s_best_rot);
+                            s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
   }
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {

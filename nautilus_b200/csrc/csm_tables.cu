@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(256) raster_kernel(
   // the cells its windows reach.
   const double floor_log = CSM_FLOOR_LOG;
   for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
-  for (int i = threadIdx.x; i < (g.wl + 1) * lowlog_stride(g.wl); i += blockDim.x)
+  for (int i = threadIdx.x; i < (g.wl + 2) * lowlog_stride(g.wl); i += blockDim.x)
     slot.lowlog[i] = floor_log;
   if (s_box[4] == 0) return;
 
@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     for (int c = cs; c <= ce; ++c) mx = fmax(mx, s_colmax[c - m.ax0]);
     slot.low[(size_t)dy * g.wl + dx] = mx;
     const bool above = mx > CSM_MIN_VALUE_FOR_LOOKUP;
-    slot.lowlog[(size_t)dy * lowlog_stride(g.wl) + dx + CSM_LOW_PAD] = lookup_log(mx);
+    slot.lowlog[(size_t)(dy + 1) * lowlog_stride(g.wl) + dx + CSM_LOW_PAD] = lookup_log(mx);
     if (above) { bx0 = min(bx0, dx); bx1 = max(bx1, dx); }
   }
   // box of low-res cells above the lookup floor (the search stages it in smem)
