@@ -1,0 +1,160 @@
+"""Side measurements for the BASELINE configs that are not bench.py's headline
+(SURVEY.md 8d): table build (configs[1]), wide search (configs[3]) and the
+point-to-point NN path (configs[4]).  One JSON line per config, CUDA-event times
+from the library, the reference's CPU code (oracle/_ref) timed beside it on a
+bounded sample.  Usage (on a B200):
+
+  python scripts/bench_configs.py [tables] [wide] [nn] [--cpu]
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from nautilus_b200 import CorrelativeScanMatcher, pose_transform, synth  # noqa: E402
+
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] \
+    if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+
+def cores():
+    return len(os.sched_getaffinity(0))
+
+
+def bench_tables(cpu):
+    n = 4096
+    xy, offs = synth.make_scan_set(n, group=8, seed=2)
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    ids = np.arange(n, dtype=np.int32)
+    m.build_tables(ids[:256])
+    ms = []
+    for _ in range(3):
+        cs = m.build_tables(ids)
+        ms.append(m.last_timings()["ms_tables"])
+    t = float(np.median(ms)) * 1e-3
+    alg = 8.0 * (m.w_high ** 2 + m.w_low ** 2) * n
+    line = {"config": "batch lookup-table rasterisation + blur, 4096 scans (BASELINE configs[1])",
+            "metric": "tables_per_sec", "value": n / t, "ms": t * 1e3,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_table": alg / n,
+                         "achieved": alg / t / 1e9, "peak": PEAK, "unit": "GB/s",
+                         "frac": alg / t / 1e9 / PEAK},
+            "low_res_checksum": cs}
+    if cpu:
+        from oracle import ref
+        k = 4 * cores()
+        sub_off = offs[:k + 1] - offs[0]
+        secs, rcs = ref.RefMatcher(30, 2, 0.3, 0.03).build_tables_batch(xy[:offs[k]], sub_off,
+                                                                       threads=cores())
+        gcs = m.build_tables(ids[:k])
+        line["cpu_baseline"] = {"value": k / secs, "unit": "tables/s", "cores": cores(),
+                                "kind": "reference", "sample": f"{k} tables, {secs:.1f} s",
+                                "checksum_rel_diff": abs(gcs - rcs) / abs(rcs)}
+    m.close()
+    return line
+
+
+def bench_wide(cpu):
+    n_scans, group = 40, 5
+    xy, offs = synth.make_scan_set(n_scans, group=group, seed=4, trans_range=10.0, max_rot=1.5)
+    pa, pb = synth.make_pair_list(n_scans, group=group)        # 200 pairs
+    reps = 5                                                   # 1000 pair matches
+    pa, pb = np.tile(pa, reps), np.tile(pb, reps)
+    m = CorrelativeScanMatcher(30, 10, 0.3, 0.03, rot_step=np.pi / 720)
+    m.upload_scans(xy, offs)
+    m.match_batch(pa[:40], pb[:40], -np.pi, np.pi)
+    t0 = time.perf_counter()
+    s, x, y, th, st = m.match_batch(pa, pb, -np.pi, np.pi, with_stats=True)
+    wall = time.perf_counter() - t0
+    tm = m.last_timings()
+    cand = int(st[:, 0].sum() + st[:, 1].sum())
+    line = {"config": "wide search: +-pi at 0.25 deg, +-10 m at 0.03 m, 1000 pairs (BASELINE configs[3])",
+            "metric": "candidate_transforms_scored_per_sec", "value": cand / (tm["ms_total"] * 1e-3),
+            "pairs_per_sec": len(pa) / (tm["ms_total"] * 1e-3), "ms": tm["ms_total"],
+            "ms_wall": wall * 1e3, "kernels_ms": {k: tm[k] for k in ("ms_tables", "ms_low", "ms_refine")},
+            "low_candidates_per_pair": int(st[0, 0]), "mean_pops": float(st[:, 2].mean())}
+    if cpu:
+        from oracle import ref
+        k = min(cores(), 8)
+        rm = ref.RefMatcher(30, 10, 0.3, 0.03)
+        # the reference hard-codes 1 degree (cc:92): its wide search is timed at 1 degree
+        # and compared through candidates/s, which is step-independent
+        idx = np.arange(k)
+        secs, rs, rx, ry, rt = rm.match_batch(xy, offs, pa[idx], pb[idx], np.full(k, -np.pi),
+                                              np.full(k, np.pi), threads=k)
+        m1 = CorrelativeScanMatcher(30, 10, 0.3, 0.03)
+        m1.upload_scans(xy, offs)
+        g = m1.match_batch(pa[idx], pb[idx], -np.pi, np.pi, with_stats=True)
+        c1 = int(g[4][:, 0].sum() + g[4][:, 1].sum())
+        line["cpu_baseline"] = {"value": c1 / secs, "unit": "candidates/s", "cores": k,
+                                "kind": "reference", "sample": f"{k} pairs at the reference's 1 degree step, {secs:.1f} s",
+                                "poses_bit_identical_to_gpu": bool(np.array_equal(rx, g[1]) and np.array_equal(ry, g[2]) and np.array_equal(rt, g[3]))}
+        m1.close()
+    m.close()
+    return line
+
+
+def bench_nn(cpu):
+    n_scans, window = 2000, 10
+    xy, offs, poses = synth.make_scan_set(n_scans, group=40, seed=6, trans_range=4.0, max_rot=0.5,
+                                          return_poses=True)
+    rng = np.random.default_rng(3)
+    est = poses + np.concatenate([rng.normal(0, 0.05, (n_scans, 2)), rng.normal(0, 0.01, (n_scans, 1))], 1)
+    src, tgt = [], []
+    for i in range(n_scans):                      # BuildOptimizationOverWindow: 10 previous nodes
+        g0 = (i // 40) * 40
+        for j in range(max(g0, i - window), i):
+            src.append(i); tgt.append(j)
+    src, tgt = np.asarray(src, np.int32), np.asarray(tgt, np.int32)
+    tr = np.stack([pose_transform(est[s], est[t]) for s, t in zip(src, tgt)])
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    t0 = time.perf_counter()
+    m.nn_build(0.25)
+    build_s = time.perf_counter() - t0
+    m.nn_match_batch(src[:100], tgt[:100], tr[:100], 0.25)
+    ms, walls = [], []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        idx, o = m.nn_match_batch(src, tgt, tr, 0.25)
+        walls.append(time.perf_counter() - t0)
+        ms.append(m.nn_last_stats()["ms_kernel"])
+    st = m.nn_last_stats()
+    t = float(np.median(ms)) * 1e-3
+    pts = (offs[1:] - offs[:-1]).astype(np.int64)
+    alg = float((8 * pts[src] + 8 * pts[tgt] + 4 * pts[src]).sum())
+    line = {"config": "point-to-point NN correspondences, 2000-pose trajectory slice, window 10 "
+                      "(BASELINE configs[4] shape; 20k poses = 10x this batch)",
+            "metric": "nn_pairs_per_sec", "value": len(src) / t, "queries_per_sec": len(idx) / t,
+            "ms_kernel": t * 1e3, "ms_wall_with_d2h": float(np.median(walls)) * 1e3,
+            "n_pairs": int(len(src)), "n_queries": int(len(idx)), "matched_frac": float((idx >= 0).mean()),
+            "tree_walk_frac": st["n_walked"] / max(1, len(idx)), "index_build_s": build_s,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_pair": alg / len(src),
+                         "achieved": alg / t / 1e9, "peak": PEAK, "unit": "GB/s",
+                         "frac": alg / t / 1e9 / PEAK}}
+    if cpu:
+        from oracle import ref
+        k = min(len(src), 4000)
+        secs, ridx, ro = ref.nn_match_batch(xy, offs, src[:k], tgt[:k], tr[:k], 0.25, threads=cores())
+        line["cpu_baseline"] = {"value": k / secs, "unit": "pairs/s", "cores": cores(),
+                                "kind": "reference", "sample": f"{k} pairs (trees prebuilt, untimed), {secs:.1f} s",
+                                "indices_identical_to_gpu": bool(np.array_equal(ridx, idx[:ro[-1]]))}
+    m.close()
+    return line
+
+
+def main():
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "nn"]
+    cpu = "--cpu" in sys.argv
+    for w in which:
+        line = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn}[w](cpu)
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
