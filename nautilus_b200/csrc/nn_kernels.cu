@@ -152,7 +152,7 @@ struct WalkFrame {
   float thr, best, pd;
 };
 
-__device__ float nn_walk(const KdNode* __restrict__ nodes, const float2* __restrict__ pts,
+__device__ __noinline__ float nn_walk(const KdNode* __restrict__ nodes, const float2* __restrict__ pts,
                          float2 q, float threshold, int* out) {
   WalkFrame st[NN_MAX_DEPTH];
   int sp = 0;
@@ -297,9 +297,10 @@ __global__ void __launch_bounds__(NM_THREADS) nn_match_kernel(
     bool tie = false;
     if (n_tgt > 0) {
       const int cx = nn_cell(q.x, ix.inv_cell), cy = nn_cell(q.y, ix.inv_cell);
-#pragma unroll
+      // (rolled on purpose: the unrolled 3 x 3 probe overflows the instruction cache)
+#pragma unroll 1
       for (int oy = -1; oy <= 1; ++oy) {
-#pragma unroll
+#pragma unroll 1
         for (int ox = -1; ox <= 1; ++ox) {
           const int b = nn_bucket(cx + ox, cy + oy, mask);
           const int k1 = bs[b + 1];
