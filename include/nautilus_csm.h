@@ -149,6 +149,14 @@ int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* 
                        int64_t nb, double rot_min, double rot_max, double* score,
                        float* x, float* y, float* theta, NautilusCsmStats* stats);
 
+/* GetUncertaintyMatrix: dims == 3 -> the 3x3 form over all rotations
+ * (cc:267-319, `rotation` ignored); dims == 2 -> the 2x2 form at `rotation`
+ * (cc:322-373).  out: dims*dims floats, row-major.  Float moment sums in the
+ * reference's loop order; expect agreement to ~1e-4 relative (exp / log differ
+ * from glibc's by ulps), not bit parity. */
+int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const float* b,
+                             int64_t nb, int32_t dims, double rotation, float* out);
+
 /* The rotation window of the 5-argument GetTransformation (cc:247-264). */
 void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,
                                   double* rot_min, double* rot_max);

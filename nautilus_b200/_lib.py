@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
-SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu"]
+SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu"]
 HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
@@ -52,7 +52,7 @@ EXPORTS = [
     "nautilus_csm_cell", "nautilus_csm_cell_fast", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
     "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
     "nautilus_csm_match_batch", "nautilus_csm_copy_results_dev", "nautilus_csm_match", "nautilus_csm_rotation_window",
-    "nautilus_csm_last_timings",
+    "nautilus_csm_last_timings", "nautilus_csm_uncertainty",
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
 ]
@@ -118,6 +118,7 @@ def lib():
     L.nautilus_csm_rotation_window.restype = None
     L.nautilus_csm_rotation_window.argtypes = [d, d, d, C.POINTER(d), C.POINTER(d)]
     L.nautilus_csm_last_timings.argtypes = [vp, C.POINTER(Timings)]
+    L.nautilus_csm_uncertainty.argtypes = [vp, vp, i64, vp, i64, i32, d, vp]
     L.nautilus_nn_build.argtypes = [vp, d]
     L.nautilus_nn_pose_transform.restype = None
     L.nautilus_nn_pose_transform.argtypes = [vp, vp, vp]

@@ -4,8 +4,7 @@
 // method forwards to libnautilus_csm_b200.so (include/nautilus_csm.h), i.e. to
 // the sm_100a kernels.  Header-only; link with -lnautilus_csm_b200.
 //
-// What is NOT here: GetUncertaintyMatrix / GetLocalUncertaintyStats
-// (CorrelativeScanMatcher.cc:267-398) abort with a message.
+// Every public member of the reference class is here (h:112-152).
 #ifndef SRC_CORRELATIVESCANMATCHER_H_
 #define SRC_CORRELATIVESCANMATCHER_H_
 
@@ -158,20 +157,52 @@ class CorrelativeScanMatcher {
     return t;
   }
 
-  Eigen::Matrix3f GetUncertaintyMatrix(const std::vector<Eigen::Vector2f>&,
-                                       const std::vector<Eigen::Vector2f>&) {
-    nautilus_b200_detail::Fatal("GetUncertaintyMatrix is not ported yet");
-    return Eigen::Matrix3f();
+  // cc:267-319
+  Eigen::Matrix3f GetUncertaintyMatrix(const std::vector<Eigen::Vector2f>& pointcloud_a,
+                                       const std::vector<Eigen::Vector2f>& pointcloud_b) {
+    float out[9];
+    nautilus_b200_detail::Check(
+        nautilus_csm_uncertainty(Handle(), Data(pointcloud_a), (int64_t)pointcloud_a.size(),
+                                 Data(pointcloud_b), (int64_t)pointcloud_b.size(), 3, 0.0, out),
+        "GetUncertaintyMatrix");
+    Eigen::Matrix3f u;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) u(i, j) = out[i * 3 + j];
+    return u;
   }
-  Eigen::Matrix2f GetUncertaintyMatrix(const std::vector<Eigen::Vector2f>&,
-                                       const std::vector<Eigen::Vector2f>&, double) {
-    nautilus_b200_detail::Fatal("GetUncertaintyMatrix is not ported yet");
-    return Eigen::Matrix2f();
+  // cc:322-373
+  Eigen::Matrix2f GetUncertaintyMatrix(const std::vector<Eigen::Vector2f>& pointcloud_a,
+                                       const std::vector<Eigen::Vector2f>& pointcloud_b,
+                                       const double rotation) {
+    float out[4];
+    nautilus_b200_detail::Check(
+        nautilus_csm_uncertainty(Handle(), Data(pointcloud_a), (int64_t)pointcloud_a.size(),
+                                 Data(pointcloud_b), (int64_t)pointcloud_b.size(), 2, rotation, out),
+        "GetUncertaintyMatrix");
+    Eigen::Matrix2f u;
+    for (int i = 0; i < 2; ++i)
+      for (int j = 0; j < 2; ++j) u(i, j) = out[i * 2 + j];
+    return u;
   }
+  // cc:375-398 (the per-cloud loop runs serially here: every call already fills the GPU)
   std::pair<double, double> GetLocalUncertaintyStats(
-      const std::vector<std::vector<Eigen::Vector2f>>&, const std::vector<Eigen::Vector2f>) {
-    nautilus_b200_detail::Fatal("GetLocalUncertaintyStats is not ported yet");
-    return std::make_pair(0.0, 0.0);
+      const std::vector<std::vector<Eigen::Vector2f>>& comparisonClouds,
+      const std::vector<Eigen::Vector2f> targetCloud) {
+    double condition_avg = 0.0;
+    double scale_avg = 0.0;
+    for (size_t i = 0; i < comparisonClouds.size(); i++) {
+      std::pair<double, std::pair<Eigen::Vector2f, float>> result =
+          GetTransformation(targetCloud, comparisonClouds[i]);
+      Eigen::Matrix2f uncertainty =
+          GetUncertaintyMatrix(targetCloud, comparisonClouds[i], result.second.second);
+      Eigen::EigenSolver<Eigen::Matrix2f> es(uncertainty);
+      Eigen::Vector2f eigenvalues = es.eigenvalues().real();
+      condition_avg += eigenvalues.maxCoeff() / eigenvalues.minCoeff();
+      scale_avg += eigenvalues.maxCoeff();
+    }
+    condition_avg /= (comparisonClouds.size());
+    scale_avg /= (comparisonClouds.size());
+    return std::make_pair(condition_avg, scale_avg);
   }
 
   // New, batch-first: what a batched SolveAutoLC / AddLCConstraints calls

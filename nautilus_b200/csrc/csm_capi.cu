@@ -730,6 +730,75 @@ int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* 
                           stats);
 }
 
+int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,
+                             int32_t dims, double rotation, float* out) {
+  if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  if (dims != 2 && dims != 3) return fail(NAUTILUS_EINVAL, "dims must be 2 or 3");
+  if (na <= 0 || nb < 0) return fail(NAUTILUS_EEMPTY, "empty query cloud");
+  if (h->grid_rc) return fail(h->grid_rc, h->grid_error);
+  CU_TRY(cudaSetDevice(h->device));
+  int rc = require_tiling(h);
+  if (rc) return rc;
+  std::vector<float> xy((size_t)2 * (na + nb));
+  memcpy(xy.data(), a, sizeof(float) * 2 * na);
+  if (nb) memcpy(xy.data() + 2 * na, b, sizeof(float) * 2 * nb);
+  const int64_t offs[3] = {0, na, na + nb};
+  if ((rc = upload_scan_set(h, h->tmp_scans, xy.data(), offs, 2))) return rc;
+  ScanSet& ss = h->tmp_scans;
+  // rotations: 0 .. 2 pi (cc:281,286) or the single given rotation
+  // (MemoizeLowRes(rotation, rotation + EPSILON), cc:341-343)
+  const double rmin = dims == 3 ? 0.0 : rotation;
+  const double rmax = dims == 3 ? 2 * M_PI : rotation + CSM_EPSILON;
+  std::vector<Rotation> rots;
+  for (double r = rmin; r < rmax; r += h->rot_step) {
+    Rotation ro;
+    ro.theta = (float)r; ro.c = cosf(ro.theta); ro.s = sinf(ro.theta); ro.pad = 0.f;
+    rots.push_back(ro);
+    if (rots.size() > 1000000) return fail(NAUTILUS_EINVAL, "rotation list too large");
+  }
+  const int n_rot = (int)rots.size(), n_t = h->grid.n_t, n_tr = n_t * n_t;
+  if (n_rot == 0) return fail(NAUTILUS_EEMPTY, "empty rotation window");
+  PairWork pw;
+  pw.a_scan = 0; pw.table = 0; pw.rot_begin = 0; pw.n_rot = n_rot; pw.out_index = 0; pw.pad = 0;
+  if ((rc = ensure_slots(h, 1))) return rc;
+  const int chunks_want = std::max(1, std::min(n_rot, h->sm_count * 2));
+  SearchBuffers sb;
+  sb.rot_per_chunk = (n_rot + chunks_want - 1) / chunks_want;
+  sb.chunks_per_pair = (n_rot + sb.rot_per_chunk - 1) / sb.rot_per_chunk;
+  if ((rc = h->chunk_best_dev.reserve((size_t)sb.chunks_per_pair * n_tr))) return rc;
+  if ((rc = h->chunk_rot_dev.reserve((size_t)sb.chunks_per_pair * n_tr))) return rc;
+  sb.chunk_best = h->chunk_best_dev.p;
+  sb.chunk_rot = h->chunk_rot_dev.p;
+  int table_cells = h->params.stage_cells > 0 ? h->params.stage_cells : 11776;
+  while (table_cells > 1024 && low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
+    table_cells -= 512;
+  if (low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
+    return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
+  if ((rc = h->table_scan_dev.reserve(1))) return rc;
+  if ((rc = h->pairs_dev.reserve(1))) return rc;
+  if ((rc = h->rots_dev.reserve(rots.size()))) return rc;
+  if ((rc = h->dense_scratch.reserve((size_t)n_rot * n_tr + 16))) return rc;
+  cudaStream_t st = h->stream;
+  const int one = 1;  // the table of cloud b
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, &pw, sizeof(PairWork), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
+                         cudaMemcpyHostToDevice, st));
+  launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p, h->slots_dev.p,
+                    h->metas_dev.p, h->pool_dev.d, 1, true, st, nullptr);
+  launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
+                   h->metas_dev.p, h->pairs_dev.p, h->rots_dev.p, 1, sb, table_cells, st);
+  double* costs = h->dense_scratch.p;
+  float* out_dev = reinterpret_cast<float*>(costs + (size_t)n_rot * n_tr);
+  launch_uncertainty(h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p, h->metas_dev.p, pw,
+                     h->rots_dev.p, sb, log(1e-4) /* UNCERTAINTY_USELESS_THRESHOLD, cc:12 */, costs,
+                     dims, out_dev, st);
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(out, out_dev, sizeof(float) * dims * dims, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  return NAUTILUS_OK;
+}
+
 int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points, double* out_high,
                                double* out_low) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");

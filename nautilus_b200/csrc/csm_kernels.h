@@ -85,5 +85,12 @@ void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hi
                    int n_pairs, const SearchBuffers& sb, PairResult* results,
                    cudaStream_t stream);
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells);
+// GetUncertaintyMatrix (cc:267-373) after launch_low_score filled sb for the pair:
+// costs[n_rot][n_t*n_t] scratch, out = dims x dims floats (row-major).
+void launch_uncertainty(const SearchGrid& sg, const CellMap& cm_high, const float2* points,
+                        const long long* offsets, const TableSlot* slots, const TableMeta* metas,
+                        const PairWork& pw, const Rotation* rots, const SearchBuffers& sb,
+                        double useless_threshold, double* costs, int dims, float* out,
+                        cudaStream_t stream);
 
 }  // namespace csm

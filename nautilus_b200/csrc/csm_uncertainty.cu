@@ -1,0 +1,110 @@
+// Olson's covariance estimate on sm_100a.  Replaces
+//   CorrelativeScanMatcher::GetUncertaintyMatrix (3x3)  CorrelativeScanMatcher.cc:267-319
+//   CorrelativeScanMatcher::GetUncertaintyMatrix (2x2)  CorrelativeScanMatcher.cc:322-373
+// Both walk rotations x low-grid translations, take the low-res memo value when
+// it is negligible (<= log 1e-4, cc:12) and the cost on the HIGH-res table at the
+// low-grid translation otherwise, and accumulate exp(cost)-weighted moments in
+// float matrices.  The costs are computed in parallel (unc_cost_kernel); the
+// moments are accumulated by one thread in the reference's loop order
+// (unc_moments_kernel), because float accumulation is order-dependent.
+#include "csm_common.cuh"
+#include "csm_kernels.h"
+
+namespace csm {
+
+__device__ __forceinline__ float2 unc_rotate(float2 p, float c, float s) {
+  float2 q;  // Rotation2Df(theta).toRotationMatrix() * p, Eigen's evaluation order
+  q.x = __fadd_rn(__fmul_rn(c, p.x), __fmul_rn(-s, p.y));
+  q.y = __fadd_rn(__fmul_rn(s, p.x), __fmul_rn(c, p.y));
+  return q;
+}
+
+// grid.x = rotation; one thread per low-grid translation tr = i * n_t + j.
+__global__ void __launch_bounds__(256) unc_cost_kernel(
+    SearchGrid sg, CellMap cm_high, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, PairWork pw, const Rotation* __restrict__ rots,
+    SearchBuffers sb, double useless_threshold, double* __restrict__ costs) {
+  const int r = blockIdx.x;
+  const int n_t = sg.n_t, n_tr = n_t * n_t;
+  const float2* a = points + offsets[pw.a_scan];
+  const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
+  const TableMeta tm = metas[pw.table];
+  const double* __restrict__ hi = slots[pw.table].values;  // lookup_log of every cell
+  const Rotation rot = rots[pw.rot_begin + r];
+  const int n_chunks = (pw.n_rot + sb.rot_per_chunk - 1) / sb.rot_per_chunk;
+  for (int tr = threadIdx.x; tr < n_tr; tr += blockDim.x) {
+    // low_res_costs[AbsCoords(x, y)].first: the memo, best over all rotations (cc:296-297)
+    double memo = -INFINITY;
+    for (int ch = 0; ch < n_chunks; ++ch) {
+      const double s = sb.chunk_best[(size_t)ch * n_tr + tr];
+      if (s > memo) memo = s;
+    }
+    double cost = memo;
+    if (!(memo <= useless_threshold)) {
+      // CalculatePointcloudCost(rotated a, x_trans, y_trans, high-res table) (cc:301-302)
+      const int i = tr / n_t, j = tr - i * n_t;
+      const float tx = sg.t_low[i], ty = sg.t_low[j];
+      double sum = 0.0;
+      for (int p = 0; p < n_pts; ++p) {
+        const float2 q = unc_rotate(a[p], rot.c, rot.s);
+        const int cx = cell_fast(cm_high, __fadd_rn(q.x, tx));
+        const int cy = cell_fast(cm_high, __fadd_rn(q.y, ty));
+        double v = CSM_FLOOR_LOG;
+        if (cx >= tm.ax0 && cx <= tm.ax1 && cy >= tm.ay0 && cy <= tm.ay1)
+          v = __ldg(hi + (size_t)(cy - tm.ay0) * tm.stride + (cx - tm.ax0));
+        sum = __dadd_rn(sum, v);
+      }
+      cost = __ddiv_rn(sum, (double)n_pts);
+    }
+    costs[(size_t)r * n_tr + tr] = cost;
+  }
+}
+
+// One thread, the reference's loop order: rotation outer, x, then y (cc:286-312 /
+// 346-366).  Float matrices, double s; the scalar cost is narrowed to float before
+// it multiplies a float matrix (Eigen's scalar promotion).
+__global__ void unc_moments_kernel(SearchGrid sg, const Rotation* __restrict__ rots, int n_rot,
+                                   const double* __restrict__ costs, int dims,
+                                   float* __restrict__ out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const int n_t = sg.n_t, n_tr = n_t * n_t;
+  float K[9], u[3];
+  for (int k = 0; k < 9; ++k) K[k] = 0.f;
+  for (int k = 0; k < 3; ++k) u[k] = 0.f;
+  double s = 0.0;
+  for (int r = 0; r < n_rot; ++r) {
+    for (int i = 0; i < n_t; ++i) {
+      for (int j = 0; j < n_t; ++j) {
+        const double cost = exp(costs[(size_t)r * n_tr + i * n_t + j]);
+        const float cf = (float)cost;
+        float x[3] = {sg.t_low[i], sg.t_low[j], rots[r].theta};
+        for (int aa = 0; aa < dims; ++aa) {
+          for (int bb = 0; bb < dims; ++bb)
+            K[aa * 3 + bb] = __fadd_rn(K[aa * 3 + bb], __fmul_rn(__fmul_rn(x[aa], x[bb]), cf));
+          u[aa] = __fadd_rn(u[aa], __fmul_rn(x[aa], cf));
+        }
+        s = __dadd_rn(s, cost);
+      }
+    }
+  }
+  // (1.0 / s) * K - (1.0 / (s * s)) * u * u.transpose()
+  const float inv_s = (float)__ddiv_rn(1.0, s);
+  const float inv_s2 = (float)__ddiv_rn(1.0, __dmul_rn(s, s));
+  for (int aa = 0; aa < dims; ++aa)
+    for (int bb = 0; bb < dims; ++bb)
+      out[aa * dims + bb] = __fsub_rn(__fmul_rn(K[aa * 3 + bb], inv_s),
+                                      __fmul_rn(__fmul_rn(u[aa], inv_s2), u[bb]));
+}
+
+void launch_uncertainty(const SearchGrid& sg, const CellMap& cm_high, const float2* points,
+                        const long long* offsets, const TableSlot* slots, const TableMeta* metas,
+                        const PairWork& pw, const Rotation* rots, const SearchBuffers& sb,
+                        double useless_threshold, double* costs, int dims, float* out,
+                        cudaStream_t stream) {
+  unc_cost_kernel<<<pw.n_rot, 256, 0, stream>>>(sg, cm_high, points, offsets, slots, metas, pw, rots,
+                                                sb, useless_threshold, costs);
+  unc_moments_kernel<<<1, 32, 0, stream>>>(sg, rots + pw.rot_begin, pw.n_rot, costs, dims, out);
+}
+
+}  // namespace csm

@@ -159,6 +159,32 @@ class CorrelativeScanMatcher:
                                              C.byref(lo), C.byref(hi))
         return lo.value, hi.value
 
+    def GetUncertaintyMatrix(self, pointcloud_a, pointcloud_b, rotation: float | None = None):
+        """Olson covariance: 3x3 over all rotations (cc:267-319) or, with `rotation`,
+        2x2 over translations (cc:322-373).  float32 matrix like the Eigen result."""
+        a, b = _cloud(pointcloud_a), _cloud(pointcloud_b)
+        dims = 3 if rotation is None else 2
+        out = np.zeros(dims * dims, np.float32)
+        check(self._L.nautilus_csm_uncertainty(self._h, ptr(a), len(a), ptr(b), len(b), dims,
+                                               0.0 if rotation is None else float(rotation),
+                                               ptr(out)))
+        return out.reshape(dims, dims)
+
+    def GetLocalUncertaintyStats(self, comparison_clouds, target_cloud):
+        """cc:375-398: mean condition number and mean largest eigenvalue of the 2x2
+        covariance of target_cloud matched against every comparison cloud."""
+        cond, scale = 0.0, 0.0
+        for c in comparison_clouds:
+            res = self.GetTransformation(target_cloud, c)
+            u = self.GetUncertaintyMatrix(target_cloud, c, float(res[1][1])).astype(np.float64)
+            tr, det = u[0, 0] + u[1, 1], u[0, 0] * u[1, 1] - u[0, 1] * u[1, 0]
+            root = math.sqrt(max(tr * tr / 4.0 - det, 0.0))
+            ev = np.asarray([tr / 2.0 + root, tr / 2.0 - root], np.float32)
+            cond += float(ev.max() / ev.min())
+            scale += float(ev.max())
+        n = len(comparison_clouds)
+        return cond / n, scale / n
+
     # ---- batch API (new; what a batched SolveAutoLC would call) -------------
     def upload_scans(self, xy, offsets) -> None:
         xy = _cloud(xy)

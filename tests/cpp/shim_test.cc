@@ -74,6 +74,11 @@ int main(int argc, char** argv) {
     double mx = 0;
     for (double v : hi.values.v) mx = v > mx ? v : mx;
     std::printf("TABLEMAX %.17g %llu\n", mx, (unsigned long long)hi.width);
+    Eigen::Matrix2f u2 = matcher.GetUncertaintyMatrix(a, b, 0.125);
+    std::printf("UNC2 %.9g %.9g %.9g %.9g\n", u2(0, 0), u2(0, 1), u2(1, 0), u2(1, 1));
+    std::vector<vector<Vector2f>> clouds(1, b);
+    std::pair<double, double> st = matcher.GetLocalUncertaintyStats(clouds, a);
+    std::printf("STATS %.9g %.9g\n", st.first, st.second);
   }
   std::printf(failures ? "SHIM FAILED %d\n" : "SHIM OK %d\n", failures);
   return failures ? 1 : 0;

@@ -44,10 +44,14 @@ def test_shim_runs_reference_unit_tests_and_matches(tmp_path):
     want = m.GetTransformation(a, b, -0.5, 0.5)
     want5 = m.GetTransformationRestricted(a, b, 0.1, 0.3, np.pi / 2)
     got = {ln.split()[0]: [float(v) for v in ln.split()[1:]] for ln in r.stdout.splitlines()
-           if ln.startswith(("MATCH", "TABLEMAX"))}
+           if ln.startswith(("MATCH", "TABLEMAX", "UNC2", "STATS"))}
     for key, w in (("MATCH", want), ("MATCH5", want5)):
         assert got[key][0] == w[0]
         assert np.float32(got[key][1]) == w[1][0][0] and np.float32(got[key][2]) == w[1][0][1]
         assert np.float32(got[key][3]) == w[1][1]
     assert got["TABLEMAX"] == [1.0, 2000.0]
+    u2 = m.GetUncertaintyMatrix(a, b, 0.125)
+    assert np.array_equal(np.asarray(got["UNC2"], np.float32), u2.ravel())
+    cond, scale = m.GetLocalUncertaintyStats([b], a)
+    assert abs(got["STATS"][0] - cond) <= 1e-4 * abs(cond) and abs(got["STATS"][1] - scale) <= 1e-4 * abs(scale)
     m.close()
