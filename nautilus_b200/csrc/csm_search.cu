@@ -57,12 +57,14 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // The rare sum that lands within float rounding of a cell edge is flagged there
 // and looked up cell by cell (cell_fast) instead.
 //
-// Rotations.  A warp scores LS_R consecutive rotations of one tile together.
-// One degree moves a point 5 m away by 9 cm, a third of a cell, so consecutive
-// rotations mostly address the SAME patch: its 7 values are loaded once and
-// added to each rotation's own sums (the word of rotation k is compared with
-// that of k-1; warp-uniform).  Every sum still runs over the points in point
-// order, one lane per candidate, like cc:66-77 -- only the loads are shared.
+// Runs.  Consecutive beams of a scan land 1-5 cm apart, far less than a 0.3 m
+// cell, so consecutive points mostly address the SAME patch (82 % on the bench
+// scans).  Phase A run-length encodes the patch words of a 32-point chunk
+// (shuffle + ballot); phase B loads the 7 values of a run once and adds them
+// once per point of the run.  Every sum still takes its terms in point order,
+// one lane per candidate, like cc:66-77 -- only the loads are shared -- and the
+// kernel is bound by the fp64 add pipe instead of shared-memory bandwidth.
+// A warp owns a rotation; the warps of a block take rotations round-robin.
 //
 // Table.  The part of the pooled log table above the lookup floor (TableMeta::
 // lx0..ly1) is staged in shared memory once per block with 7 floor columns on
@@ -71,10 +73,8 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // hit 16 different bank pairs.  Tables whose box does not fit the budget are
 // read from global memory (same padded layout) through L1.
 // ---------------------------------------------------------------------------
-constexpr int LS_WARPS = 8;
+constexpr int LS_WARPS = 12;
 constexpr int LS_THREADS = LS_WARPS * 32;
-constexpr int LS_R = 4;              // rotations scored together by a warp
-static_assert(LS_R == 4, "phase B reads the four patch words of a point as one uint4");
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
 constexpr int LS_TJ = 16;            // y translations per tile
 constexpr int LS_IU = 7;             // x translations per lane
@@ -84,8 +84,8 @@ static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding"
 // patch word: bits 0-9 first row + LS_YB, bits 10-20 / 21-31 first column of half 0 / 1
 constexpr int LS_YB = 32;
 constexpr unsigned LS_ODD = 0xffffffffu;  // look every cell up on its own
-// per-warp list: one patch word per (point of the chunk, rotation)
-constexpr int LS_LIST_BYTES = LS_PC * LS_R * 4;
+// per-warp list: one {patch word, run length} per run of the chunk
+constexpr int LS_LIST_BYTES = LS_PC * 8;
 
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
@@ -144,132 +144,100 @@ __device__ __forceinline__ void low_score_rounds(
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
-  const int n_groups = (rot1 - rot0 + LS_R - 1) / LS_R;
-  unsigned* lw = reinterpret_cast<unsigned*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC][LS_R]
+  uint2* runs = reinterpret_cast<uint2*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC]
   const int lj = lane & 15, half = lane >> 4;
   const int xshift = half ? 21 : 10;
   const int ljc = lj - LS_YB + 1;  // row of a patch word = clamp(word row + ljc, floor row above, floor row below)
+  const unsigned below = (1u << lane) - 1u;          // lanes before this one
+  const unsigned above = lane == 31 ? 0u : ~((2u << lane) - 1u);  // lanes after this one
 
   for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
     const int ti = tile % tiles_x, tj = tile / tiles_x;
     const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
     const int jj = tj * LS_TJ + lj;             // this lane's y translation
+    const float ty0 = s_tlow[tj * LS_TJ], tx0 = s_tlow[ti * LS_TI];
+    const bool two = ti * LS_TI + LS_IU < n_t;  // the tile has a second group of x translations
+    const float tx1 = s_tlow[two ? ti * LS_TI + LS_IU : ti * LS_TI];
     double rbest[LS_IU];  // best of this warp's rotations, which ascend: '>' keeps the earliest
     int rbest_rot[LS_IU];
 #pragma unroll
     for (int u = 0; u < LS_IU; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
 
-    for (int grp = warp; grp < n_groups; grp += LS_WARPS) {
-      const int r0 = rot0 + grp * LS_R;
-      const int nr = min(LS_R, rot1 - r0);
-      double acc[LS_R][LS_IU];
+#pragma unroll 1
+    for (int r = rot0 + warp; r < rot1; r += LS_WARPS) {
+      const Rotation rot = rots[r];
+      double acc[LS_IU];
 #pragma unroll
-      for (int k = 0; k < LS_R; ++k)
-#pragma unroll
-        for (int u = 0; u < LS_IU; ++u) acc[k][u] = 0.0;
+      for (int u = 0; u < LS_IU; ++u) acc[u] = 0.0;
 
+#pragma unroll 1
       for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
         const int pc = min(LS_PC, n_pts - p0);
-        // phase A (lane = point): patch word of every rotation of the group.  The
-        // translations step by exactly one cell, so when the first sum of an axis
-        // lies clear of a cell edge (cell_clear, margin SearchGrid::reg_eps proven
-        // on the host) the other translations hit the next cells.
-        bool odd = false;
+        // phase A (lane = point): the patch word of the point.  The translations
+        // step by exactly one cell, so when the first sum of an axis lies clear of a
+        // cell edge (cell_clear, margin SearchGrid::reg_eps proven on the host) the
+        // other translations hit the next cells.
+        unsigned word = LS_ODD;
         if (lane < pc) {
-          const float2 p = a[p0 + lane];
-          unsigned word = LS_ODD;
-#pragma unroll
-          for (int k = 0; k < LS_R; ++k) {
-            if (k < nr) {  // (past the last rotation the previous word repeats: no loads)
-              word = LS_ODD;
-              const Rotation rot = rots[r0 + k];
-              const float2 q = rotate_point(p, rot.c, rot.s);
-              int cy0, cx0, cx1 = 0;
-              bool ok = packable;
-              ok = cell_clear(cm, __fadd_rn(q.y, s_tlow[tj * LS_TJ]), sg.reg_eps, sg.reg_qmax, &cy0) && ok;
-              ok = cell_clear(cm, __fadd_rn(q.x, s_tlow[ti * LS_TI]), sg.reg_eps, sg.reg_qmax, &cx0) && ok;
-              if (ti * LS_TI + LS_IU < n_t)
-                ok = cell_clear(cm, __fadd_rn(q.x, s_tlow[ti * LS_TI + LS_IU]), sg.reg_eps,
-                                sg.reg_qmax, &cx1) && ok;
-              else
-                cx1 = cx0;  // no second group in this tile: any window will do
-              if (ok) {
-                // rows yb + lj are clamped to the floor rows by phase B, so yb only
-                // matters within [-17, th]; columns c .. c+6 relative to the padded
-                // box, a window entirely outside moved onto the floor padding
-                const int yb = max(-LS_TJ - 1, min(cy0 - lt.oy, lt.th)) + LS_YB;
-                const int xa = max(0, min(cx0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
-                const int xb = max(0, min(cx1 - lt.ox + lt.xpad, lt.tw + lt.xpad));
-                word = (unsigned)yb | ((unsigned)xa << 10) | ((unsigned)xb << 21);
-              }
-              odd = odd || word == LS_ODD;
-            }
-            lw[lane * LS_R + k] = word;
+          const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
+          int cy0, cx0, cx1;
+          bool ok = packable;
+          ok = cell_clear(cm, __fadd_rn(q.y, ty0), sg.reg_eps, sg.reg_qmax, &cy0) && ok;
+          ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps, sg.reg_qmax, &cx0) && ok;
+          ok = cell_clear(cm, __fadd_rn(q.x, tx1), sg.reg_eps, sg.reg_qmax, &cx1) && ok;
+          if (ok) {
+            // rows yb + lj are clamped to the floor rows by phase B, so yb only
+            // matters within [-17, th]; columns c .. c+6 relative to the padded
+            // box, a window entirely outside moved onto the floor padding
+            const int yb = max(-LS_TJ - 1, min(cy0 - lt.oy, lt.th)) + LS_YB;
+            const int xa = max(0, min(cx0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+            const int xb = max(0, min(cx1 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+            word = (unsigned)yb | ((unsigned)xa << 10) | ((unsigned)xb << 21);
           }
         }
-        const bool any_odd = __any_sync(0xffffffffu, odd);  // also orders the list writes
+        // run-length encode: a point whose patch equals the previous point's adds
+        // the values already in registers.  run = {word, length | first lane << 8}
+        const unsigned prevw = __shfl_up_sync(0xffffffffu, word, 1);
+        const bool start = lane < pc && (lane == 0 || word != prevw || word == LS_ODD);
+        const unsigned starts = __ballot_sync(0xffffffffu, start);
+        if (start) {
+          const unsigned later = starts & above;
+          const int next = later ? __ffs(later) - 1 : pc;
+          runs[__popc(starts & below)] = make_uint2(word, (unsigned)(next - lane) | ((unsigned)lane << 8));
+        }
         __syncwarp();
-        // phase B (lane = candidate column): per point, per rotation, 7 consecutive
-        // cells; a rotation whose patch word equals the previous one reuses its loads
-        if (!any_odd) {
+        // phase B (lane = candidate column): per run 7 consecutive cells, added once
+        // per point of the run -- each sum still takes its terms in point order
+        const int n_runs = __popc(starts);
 #pragma unroll 1
-          for (int pl = 0; pl < pc; ++pl) {
-            const uint4 w4 = *reinterpret_cast<const uint4*>(lw + pl * LS_R);
-            const unsigned wk[LS_R] = {w4.x, w4.y, w4.z, w4.w};
-            double t[LS_IU];
+        for (int ri = 0; ri < n_runs; ++ri) {
+          const uint2 e = runs[ri];
+          double t[LS_IU];
+          if (e.x == LS_ODD) {
+            double ts[LS_IU];  // (a local array: keeps t itself in registers)
+            low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + (int)(e.y >> 8)], rot.c, rot.s),
+                                 n_t, jj, i0, ts);
 #pragma unroll
-            for (int k = 0; k < LS_R; ++k) {
-              // the words are the same in every lane: a vote makes the branch uniform
-              if (k == 0 || __any_sync(0xffffffffu, wk[k] != wk[k - 1])) {
-                const int row = min(max((int)(wk[k] & 1023u) + ljc, 0), lt.row_below);
-                const double* src = lt.tab + (row * lt.ts + (int)((wk[k] >> xshift) & 2047u));
+            for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
+          } else {
+            const int row = min(max((int)(e.x & 1023u) + ljc, 0), lt.row_below);
+            const double* src = lt.tab + (row * lt.ts + (int)((e.x >> xshift) & 2047u));
 #pragma unroll
-                for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
-              }
-#pragma unroll
-              for (int u = 0; u < LS_IU; ++u) acc[k][u] = __dadd_rn(acc[k][u], t[u]);
-            }
+            for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
           }
-        } else {
+          const int len = (int)(e.y & 255u);
 #pragma unroll 1
-          for (int pl = 0; pl < pc; ++pl) {  // same sums; flagged points cell by cell
-            double t[LS_IU];
-            unsigned prev = LS_ODD;
+          for (int c = 0; c < len; ++c) {
 #pragma unroll
-            for (int k = 0; k < LS_R; ++k) {
-              const unsigned w = lw[pl * LS_R + k];
-              if (k < nr) {
-                if (w == LS_ODD) {
-                  const Rotation rot = rots[r0 + k];
-                  double ts[LS_IU];  // (a local array: keeps t itself in registers)
-                  low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + pl], rot.c, rot.s), n_t,
-                                       jj, i0, ts);
-#pragma unroll
-                  for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
-                } else if (w != prev) {
-                  const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
-                  const double* src = lt.tab + (row * lt.ts + (int)((w >> xshift) & 2047u));
-#pragma unroll
-                  for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
-                }
-                prev = w;
-#pragma unroll
-                for (int u = 0; u < LS_IU; ++u) acc[k][u] = __dadd_rn(acc[k][u], t[u]);
-              }
-            }
+            for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
           }
         }
         __syncwarp();
       }
 #pragma unroll
-      for (int k = 0; k < LS_R; ++k) {
-        if (k < nr) {
-#pragma unroll
-          for (int u = 0; u < LS_IU; ++u) {
-            const double sc = __ddiv_rn(acc[k][u], (double)n_pts);  // probability / size (cc:76)
-            if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r0 + k; }
-          }
-        }
+      for (int u = 0; u < LS_IU; ++u) {
+        const double sc = __ddiv_rn(acc[u], (double)n_pts);  // probability / size (cc:76)
+        if (sc > rbest[u]) { rbest[u] = sc; rbest_rot[u] = r; }
       }
     }
     // merge the warps: higher score wins, equal scores keep the smaller rotation
