@@ -73,7 +73,10 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // hit 16 different bank pairs.  Tables whose box does not fit the budget are
 // read from global memory (same padded layout) through L1.
 // ---------------------------------------------------------------------------
-constexpr int LS_WARPS = 12;
+#ifndef LS_WARPS_N
+#define LS_WARPS_N 10
+#endif
+constexpr int LS_WARPS = LS_WARPS_N;
 constexpr int LS_THREADS = LS_WARPS * 32;
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
 constexpr int LS_TJ = 16;            // y translations per tile
@@ -84,13 +87,10 @@ static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding"
 // patch word: bits 0-9 first row + LS_YB, bits 10-20 / 21-31 first column of half 0 / 1
 constexpr int LS_YB = 32;
 constexpr unsigned LS_ODD = 0xffffffffu;  // look every cell up on its own
-// per-warp list: one {patch word, run length} per run of the chunk
-constexpr int LS_LIST_BYTES = LS_PC * 8;
 
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
   b += sizeof(double) * (((size_t)n_t * n_t + 1) & ~(size_t)1);      // best score
-  b += (size_t)LS_WARPS * LS_LIST_BYTES;                             // lists
   b += sizeof(int) * (size_t)n_t * n_t;                              // best rotation
   b += sizeof(float) * ((size_t)wl + 2 + n_t);                       // thresholds, translations
   return b;
@@ -140,16 +140,13 @@ template <bool SMEM>
 __device__ __forceinline__ void low_score_rounds(
     const SearchGrid& sg, const CellMap& cm, const float* s_tlow, const LowTab lt,
     const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
-    int rot1, unsigned char* s_lists, double* s_best, int* s_best_rot, bool packable) {
+    int rot1, double* s_best, int* s_best_rot, bool packable) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
-  uint2* runs = reinterpret_cast<uint2*>(s_lists + warp * LS_LIST_BYTES);  // [LS_PC]
   const int lj = lane & 15, half = lane >> 4;
   const int xshift = half ? 21 : 10;
   const int ljc = lj - LS_YB + 1;  // row of a patch word = clamp(word row + ljc, floor row above, floor row below)
-  const unsigned below = (1u << lane) - 1u;          // lanes before this one
-  const unsigned above = lane == 31 ? 0u : ~((2u << lane) - 1u);  // lanes after this one
 
   for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
     const int ti = tile % tiles_x, tj = tile / tiles_x;
@@ -196,43 +193,49 @@ __device__ __forceinline__ void low_score_rounds(
           }
         }
         // run-length encode: a point whose patch equals the previous point's adds
-        // the values already in registers.  run = {word, length | first lane << 8}
+        // the values already in registers.  Run starts as a ballot; the word of a
+        // run is fetched from its first lane by shuffle.
         const unsigned prevw = __shfl_up_sync(0xffffffffu, word, 1);
-        const bool start = lane < pc && (lane == 0 || word != prevw || word == LS_ODD);
-        const unsigned starts = __ballot_sync(0xffffffffu, start);
-        if (start) {
-          const unsigned later = starts & above;
-          const int next = later ? __ffs(later) - 1 : pc;
-          runs[__popc(starts & below)] = make_uint2(word, (unsigned)(next - lane) | ((unsigned)lane << 8));
-        }
-        __syncwarp();
+        unsigned m = __ballot_sync(0xffffffffu,
+                                   lane < pc && (lane == 0 || word != prevw || word == LS_ODD));
         // phase B (lane = candidate column): per run 7 consecutive cells, added once
         // per point of the run -- each sum still takes its terms in point order
-        const int n_runs = __popc(starts);
 #pragma unroll 1
-        for (int ri = 0; ri < n_runs; ++ri) {
-          const uint2 e = runs[ri];
+        while (m) {
+          const int pl = __ffs(m) - 1;
+          m &= m - 1;
+          int c = (m ? __ffs(m) - 1 : pc) - pl;  // points in the run
+          const unsigned w = __shfl_sync(0xffffffffu, word, pl);
           double t[LS_IU];
-          if (e.x == LS_ODD) {
+          if (w == LS_ODD) {
             double ts[LS_IU];  // (a local array: keeps t itself in registers)
-            low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + (int)(e.y >> 8)], rot.c, rot.s),
-                                 n_t, jj, i0, ts);
+            low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + pl], rot.c, rot.s), n_t, jj, i0, ts);
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
           } else {
-            const int row = min(max((int)(e.x & 1023u) + ljc, 0), lt.row_below);
-            const double* src = lt.tab + (row * lt.ts + (int)((e.x >> xshift) & 2047u));
+            const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
+            const double* src = lt.tab + (row * lt.ts + (int)((w >> xshift) & 2047u));
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
           }
-          const int len = (int)(e.y & 255u);
 #pragma unroll 1
-          for (int c = 0; c < len; ++c) {
+          for (; c >= 4; c -= 4) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+              for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
+          }
+          if (c & 2) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+              for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
+          }
+          if (c & 1) {
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
           }
         }
-        __syncwarp();
       }
 #pragma unroll
       for (int u = 0; u < LS_IU; ++u) {
@@ -275,8 +278,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
   extern __shared__ __align__(16) unsigned char s_raw[];
   double* s_tab = reinterpret_cast<double*>(s_raw);                  // [table_cells]
   double* s_best = s_tab + table_cells;                              // [n_tr]
-  unsigned char* s_lists = reinterpret_cast<unsigned char*>(s_best + ((n_tr + 1) & ~1));  // 16 B aligned
-  int* s_best_rot = reinterpret_cast<int*>(s_lists + LS_WARPS * LS_LIST_BYTES);  // [n_tr]
+  int* s_best_rot = reinterpret_cast<int*>(s_best + ((n_tr + 1) & ~1));  // [n_tr]
   float* s_thr = reinterpret_cast<float*>(s_best_rot + n_tr);
   float* s_tlow = s_thr + (g.wl + 2);                                // [n_t]
 
@@ -313,14 +315,14 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
                      ? lowlog[(size_t)(lt.oy + r + 1) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
     }
     __syncthreads();
-    low_score_rounds<true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
+    low_score_rounds<true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
                            s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
   } else {
     // whole table from global memory: lowlog has the same padded layout
     lt.tab = lowlog; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
     lt.xpad = CSM_LOW_PAD; lt.row_below = g.wl + 1;
     __syncthreads();
-    low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1, s_lists,
+    low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
                             s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
   }
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
