@@ -74,7 +74,7 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // read from global memory (same padded layout) through L1.
 // ---------------------------------------------------------------------------
 #ifndef LS_WARPS_N
-#define LS_WARPS_N 10
+#define LS_WARPS_N 12
 #endif
 constexpr int LS_WARPS = LS_WARPS_N;
 constexpr int LS_THREADS = LS_WARPS * 32;
@@ -87,6 +87,11 @@ static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding"
 // patch word: bits 0-9 first row + LS_YB, bits 10-20 / 21-31 first column of half 0 / 1
 constexpr int LS_YB = 32;
 constexpr unsigned LS_ODD = 0xffffffffu;  // look every cell up on its own
+// run info: bits 0-23 first cell of the patch (inner runs), 24-29 points in the run, 30-31 kind
+constexpr unsigned LS_INNER = 0u;       // the 16 x 14 patch lies inside the staged rows / columns: no clamps
+constexpr unsigned LS_FLOOR = 1u << 30; // the patch lies outside the box: every value is the lookup floor
+constexpr unsigned LS_EDGE = 2u << 30;  // rows / columns clamped onto the floor padding (the patch word)
+constexpr unsigned LS_SLOW = 3u << 30;  // LS_ODD
 
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
@@ -99,6 +104,7 @@ size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
 // Geometry of the table a block scores against (staged box or the whole table).
 struct LowTab {
   const double* tab;  // shared (staged) or global (lowlog)
+  unsigned tab_s;     // shared-window address of tab when it is staged
   int ox, oy;         // low-res cell of box column / row 0
   int tw, th;         // box width / height in cells
   int ts;             // row stride in doubles
@@ -111,6 +117,38 @@ template <bool SMEM>
 __device__ __forceinline__ double tab_load(const double* p) {
   if (SMEM) return *p;
   return __ldg(p);
+}
+
+// The 7 consecutive values at cell index `cell` of the table.  Shared memory is
+// addressed by its 32-bit window address (tab_s), which spares the generic ->
+// shared conversion per access.
+template <int OFF>
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+  double v;
+  asm("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+
+// `base` = shared-window byte address (staged table) or unused; `cell` = index of
+// the first of the 7 cells.
+template <bool SMEM>
+__device__ __forceinline__ void tab_load7(const double* tab, unsigned base, int cell, double* t) {
+  static_assert(LS_IU == 7, "seven loads below");
+  if (SMEM) {
+    const unsigned ad = base + (unsigned)cell * 8u;
+    t[0] = lds_f64<0>(ad);  t[1] = lds_f64<8>(ad);  t[2] = lds_f64<16>(ad); t[3] = lds_f64<24>(ad);
+    t[4] = lds_f64<32>(ad); t[5] = lds_f64<40>(ad); t[6] = lds_f64<48>(ad);
+  } else {
+#pragma unroll
+    for (int u = 0; u < LS_IU; ++u) t[u] = __ldg(tab + cell + u);
+  }
+}
+
+// Keeps a loop-invariant value in its register: without this the compiler
+// re-derives shared-window addresses (3 uniform instructions) at every use.
+__device__ __forceinline__ unsigned pinned(unsigned v) {
+  asm volatile("mov.u32 %0, %0;" : "+r"(v));
+  return v;
 }
 
 // The 7 table values of one lane for one (rotation, point), every cell looked up
@@ -147,6 +185,7 @@ __device__ __forceinline__ void low_score_rounds(
   const int lj = lane & 15, half = lane >> 4;
   const int xshift = half ? 21 : 10;
   const int ljc = lj - LS_YB + 1;  // row of a patch word = clamp(word row + ljc, floor row above, floor row below)
+  const unsigned above = lane == 31 ? 0u : ~((2u << lane) - 1u);  // lanes after this one
 
   for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
     const int ti = tile % tiles_x, tj = tile / tiles_x;
@@ -155,6 +194,8 @@ __device__ __forceinline__ void low_score_rounds(
     const float ty0 = s_tlow[tj * LS_TJ], tx0 = s_tlow[ti * LS_TI];
     const bool two = ti * LS_TI + LS_IU < n_t;  // the tile has a second group of x translations
     const float tx1 = s_tlow[two ? ti * LS_TI + LS_IU : ti * LS_TI];
+    const int lane_cell = lj * lt.ts + (two ? half * LS_IU : 0);  // this lane's cell within an inner patch
+    const unsigned tab_s = pinned(lt.tab_s), lane_s = pinned(lt.tab_s + 8u * (unsigned)lane_cell);
     double rbest[LS_IU];  // best of this warp's rotations, which ascend: '>' keeps the earliest
     int rbest_rot[LS_IU];
 #pragma unroll
@@ -174,7 +215,7 @@ __device__ __forceinline__ void low_score_rounds(
         // step by exactly one cell, so when the first sum of an axis lies clear of a
         // cell edge (cell_clear, margin SearchGrid::reg_eps proven on the host) the
         // other translations hit the next cells.
-        unsigned word = LS_ODD;
+        unsigned word = LS_ODD, info = LS_SLOW;
         if (lane < pc) {
           const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
           int cy0, cx0, cx1;
@@ -183,41 +224,57 @@ __device__ __forceinline__ void low_score_rounds(
           ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps, sg.reg_qmax, &cx0) && ok;
           ok = cell_clear(cm, __fadd_rn(q.x, tx1), sg.reg_eps, sg.reg_qmax, &cx1) && ok;
           if (ok) {
-            // rows yb + lj are clamped to the floor rows by phase B, so yb only
-            // matters within [-17, th]; columns c .. c+6 relative to the padded
-            // box, a window entirely outside moved onto the floor padding
-            const int yb = max(-LS_TJ - 1, min(cy0 - lt.oy, lt.th)) + LS_YB;
-            const int xa = max(0, min(cx0 - lt.ox + lt.xpad, lt.tw + lt.xpad));
-            const int xb = max(0, min(cx1 - lt.ox + lt.xpad, lt.tw + lt.xpad));
+            // lane lj reads staged row r0 + lj clamped to the floor rows, so r0 only
+            // matters within [-16, th + 1]; columns c .. c+6 of the padded box, a
+            // window entirely outside moved onto the floor padding
+            const int r0 = cy0 - lt.oy + 1, ca = cx0 - lt.ox + lt.xpad, cb = cx1 - lt.ox + lt.xpad;
+            const int xmax = lt.tw + lt.xpad;
+            const int yb = max(-LS_TJ, min(r0, lt.row_below)) + LS_YB - 1;
+            const int xa = max(0, min(ca, xmax)), xb = max(0, min(cb, xmax));
             word = (unsigned)yb | ((unsigned)xa << 10) | ((unsigned)xb << 21);
+            const bool rows_out = r0 + LS_TJ - 1 <= 0 || r0 >= lt.row_below;
+            const bool a_out = xa + LS_IU <= lt.xpad || xa >= xmax;
+            const bool b_out = xb + LS_IU <= lt.xpad || xb >= xmax;
+            const bool inner = r0 >= 0 && r0 + LS_TJ - 1 <= lt.row_below && ca == xa &&
+                               (two ? cb == ca + LS_IU && cb <= xmax : true);
+            info = rows_out || (a_out && b_out) ? LS_FLOOR
+                   : inner ? LS_INNER | (unsigned)(r0 * lt.ts + ca) : LS_EDGE;
           }
         }
         // run-length encode: a point whose patch equals the previous point's adds
-        // the values already in registers.  Run starts as a ballot; the word of a
-        // run is fetched from its first lane by shuffle.
+        // the values already in registers.  Run starts come from a ballot; each start
+        // lane works out the length of its run; phase B fetches {kind, cell, length}
+        // of a run from its first lane by shuffle and steps from start to start.
         const unsigned prevw = __shfl_up_sync(0xffffffffu, word, 1);
-        unsigned m = __ballot_sync(0xffffffffu,
-                                   lane < pc && (lane == 0 || word != prevw || word == LS_ODD));
+        const unsigned starts = __ballot_sync(
+            0xffffffffu, lane < pc && (lane == 0 || word != prevw || word == LS_ODD));
+        {
+          const unsigned later = starts & above;
+          info |= (unsigned)((later ? __ffs(later) - 1 : pc) - lane) << 24;
+        }
         // phase B (lane = candidate column): per run 7 consecutive cells, added once
         // per point of the run -- each sum still takes its terms in point order
 #pragma unroll 1
-        while (m) {
-          const int pl = __ffs(m) - 1;
-          m &= m - 1;
-          int c = (m ? __ffs(m) - 1 : pc) - pl;  // points in the run
-          const unsigned w = __shfl_sync(0xffffffffu, word, pl);
+        for (int pl = 0; pl < pc;) {
+          const unsigned inf = __shfl_sync(0xffffffffu, info, pl);
+          int c = (int)((inf >> 24) & 63u);  // points in the run
           double t[LS_IU];
-          if (w == LS_ODD) {
+          if (inf < LS_FLOOR) {
+            tab_load7<SMEM>(lt.tab + lane_cell, lane_s, (int)(inf & 0xffffffu), t);
+          } else if (inf < LS_EDGE) {
+#pragma unroll
+            for (int u = 0; u < LS_IU; ++u) t[u] = CSM_FLOOR_LOG;
+          } else if (inf < LS_SLOW) {
+            const unsigned w = __shfl_sync(0xffffffffu, word, pl);
+            const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
+            tab_load7<SMEM>(lt.tab, tab_s, row * lt.ts + (int)((w >> xshift) & 2047u), t);
+          } else {
             double ts[LS_IU];  // (a local array: keeps t itself in registers)
             low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + pl], rot.c, rot.s), n_t, jj, i0, ts);
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
-          } else {
-            const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
-            const double* src = lt.tab + (row * lt.ts + (int)((w >> xshift) & 2047u));
-#pragma unroll
-            for (int u = 0; u < LS_IU; ++u) t[u] = tab_load<SMEM>(src + u);
           }
+          pl += c;
 #pragma unroll 1
           for (; c >= 4; c -= 4) {
 #pragma unroll
@@ -309,6 +366,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
   if (fits) {
     // staged rows: 0 = floor, 1 .. th = box, th + 1 = floor
     lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD; lt.row_below = lt.th + 1;
+    lt.tab_s = (unsigned)__cvta_generic_to_shared(s_tab);
     for (int k = threadIdx.x; k < ts * (lt.th + 2); k += LS_THREADS) {
       const int r = k / ts - 1, c = k - (r + 1) * ts - LS_XPAD;
       s_tab[k] = ((unsigned)r < (unsigned)lt.th && (unsigned)c < (unsigned)lt.tw)
@@ -319,7 +377,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
                            s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
   } else {
     // whole table from global memory: lowlog has the same padded layout
-    lt.tab = lowlog; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
+    lt.tab = lowlog; lt.tab_s = 0; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
     lt.xpad = CSM_LOW_PAD; lt.row_below = g.wl + 1;
     __syncthreads();
     low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
