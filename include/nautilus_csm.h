@@ -104,6 +104,16 @@ int64_t nautilus_csm_cell(double resolution, uint64_t dim, float v);
  * returns -1 outside [0, dim).  Host twin of the kernels' cell_fast, for tests. */
 int64_t nautilus_csm_cell_fast(double resolution, uint64_t dim, float v);
 
+/* Test hook for the kernels' "regular cells" shortcut (host code, no launches): the
+ * search kernels derive the cells of consecutive translations from the first one
+ * when its float quotient lies clear of a cell edge (margins proven at create time
+ * from the actual translation lists).  Replays that rule on n_samples random and
+ * cell-edge-hugging coordinates against the exact cell map for the low-res grid
+ * (MemoizeLowRes, cc:96-99) and every hi-res window (cc:126-129); writes how many
+ * predictions were made and how many disagreed (must be 0). */
+int nautilus_csm_regular_check(NautilusCsm* h, int64_t n_samples, uint64_t seed,
+                               int64_t* n_checked, int64_t* n_bad_low, int64_t* n_bad_high);
+
 /* --- scan residency -------------------------------------------------------
  * Copies n_scans clouds to the device (one H2D); scan ids are 0..n_scans-1 and
  * replace any previous set.  offsets has n_scans+1 entries, in points. */

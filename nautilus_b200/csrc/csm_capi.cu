@@ -263,6 +263,15 @@ int build_search_grid(NautilusCsm* h) {
     h->grid.reg_eps = (float)std::min(eps, 0.49);  // >= 0.5 never passes: always cell_fast
     if (eps >= 0.49) h->grid.reg_eps = 0.5f;
     h->grid.reg_qmax = (float)qmax;
+    // hi-res windows: step k of a window against its first step
+    const double qmax_h = vmax / rh + 2.0;
+    double dev_h = 0.0;
+    for (int i = 0; i < n_t; ++i)
+      for (size_t k = 0; k < steps[i].size(); ++k)
+        dev_h = std::max(dev_h, fabs((double)steps[i][k] - (double)steps[i][0] - (double)k * rh));
+    const double eps_h = 4.0 * (qmax_h * ldexp(1.0, -22) + (ulp + dev_h) / rh) + 1e-6;
+    h->grid.reg_eps_h = eps_h >= 0.49 ? 0.5f : (float)eps_h;
+    h->grid.reg_qmax_h = (float)qmax_h;
   }
   // exact cell maps for the two grids
   int rc2;
@@ -346,6 +355,68 @@ int64_t nautilus_csm_cell_fast(double resolution, uint64_t dim, float v) {
   }
   c_map.lowf = c_thr.data();
   return cell_fast(c_map, v);
+}
+
+static bool host_cell_clear(const CellMap& m, float v, float eps, float qmax, int* cell) {
+  const volatile float e = v * m.inv_res;  // one rounded float product, like __fmul_rn
+  const float ev = e, fl = floorf(ev), fr = ev - fl;
+  *cell = (int)fl + m.half;
+  return fabsf(ev) < qmax && fr > eps && fr < 1.0f - eps;
+}
+
+int nautilus_csm_regular_check(NautilusCsm* h, int64_t n_samples, uint64_t seed,
+                               int64_t* n_checked, int64_t* n_bad_low, int64_t* n_bad_high) {
+  if (!h || !n_checked || !n_bad_low || !n_bad_high) return fail(NAUTILUS_EINVAL, "null argument");
+  CellMap ml = h->cm_low, mh = h->cm_high;
+  ml.lowf = h->thr_low_host.data();
+  mh.lowf = h->thr_high_host.data();
+  const SearchGrid& sg = h->grid;
+  const int n_t = sg.n_t, nh_max = sg.n_h_max;
+  const double vmax = h->params.scanner_range;
+  uint64_t st = seed * 6364136223846793005ull + 1442695040888963407ull;
+  auto rnd = [&]() {  // uniform in [0, 1)
+    st = st * 6364136223846793005ull + 1442695040888963407ull;
+    return (double)(st >> 11) * (1.0 / 9007199254740992.0);
+  };
+  int64_t checked = 0, bad_l = 0, bad_h = 0;
+  for (int64_t s = 0; s < n_samples; ++s) {
+    // a rotated point coordinate: uniform, or hugging a cell edge of either grid
+    const int mode = (int)(s % 3);
+    const int k0 = (int)(rnd() * n_t) % n_t;
+    const int wi = (int)(rnd() * n_t) % n_t;
+    float p;
+    if (mode == 0) {
+      p = (float)((2.0 * rnd() - 1.0) * vmax);
+    } else {
+      const double res = mode == 1 ? h->params.low_res : h->params.high_res;
+      const float t0 = mode == 1 ? h->t_low_host[k0] : h->t_high_host[(size_t)wi * nh_max];
+      const double edge = floor((2.0 * rnd() - 1.0) * vmax / res) * res;
+      p = (float)(edge - (double)t0 + (2.0 * rnd() - 1.0) * 0.01 * res);
+      if (rnd() < 0.25) p = nextafterf((float)(edge - (double)t0), rnd() < 0.5 ? -INFINITY : INFINITY);
+    }
+    int c0;
+    if (host_cell_clear(ml, p + h->t_low_host[k0], sg.reg_eps, sg.reg_qmax, &c0)) {
+      for (int k = k0; k < std::min(n_t, k0 + 16); ++k) {
+        const int want = cell_fast(ml, p + h->t_low_host[k]);
+        const int got = c0 + (k - k0);
+        const int got_in = got >= 0 && got < h->geo.wl ? got : -1;
+        ++checked;
+        if (want != got_in) ++bad_l;
+      }
+    }
+    const float* th = h->t_high_host.data() + (size_t)wi * nh_max;
+    if (host_cell_clear(mh, p + th[0], sg.reg_eps_h, sg.reg_qmax_h, &c0)) {
+      for (int k = 0; k < h->n_h_host[wi]; ++k) {
+        const int want = cell_fast(mh, p + th[k]);
+        const int got = c0 + k;
+        const int got_in = got >= 0 && got < h->geo.w ? got : -1;
+        ++checked;
+        if (want != got_in) ++bad_h;
+      }
+    }
+  }
+  *n_checked = checked; *n_bad_low = bad_l; *n_bad_high = bad_h;
+  return NAUTILUS_OK;
 }
 
 void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,

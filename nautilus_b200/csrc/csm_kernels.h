@@ -44,6 +44,9 @@ struct SearchGrid {
   // cells of t_low[k0 + k], k < 16, are floor(e) + k (proved on the host from the
   // actual t_low values and float error bounds, build_search_grid).
   float reg_eps, reg_qmax;
+  // The same for the hi-res windows (refine): cells of t_high[i*n_h_max + k] are
+  // floor(e) + k for the estimate e of (p + t_high[i*n_h_max]) / high_res.
+  float reg_eps_h, reg_qmax_h;
 };
 
 // Per-pair work item.

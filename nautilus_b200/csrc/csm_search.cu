@@ -414,8 +414,13 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
 //   the hi-res window it opens and keep a strictly better result.
 // ---------------------------------------------------------------------------
 constexpr int RF_THREADS = 128;
-constexpr int RF_POINT_CHUNK = 128;
-constexpr int RF_STRIDE = RF_POINT_CHUNK + 1;  // odd: list rows start on different banks
+constexpr int RF_POINT_CHUNK = 1024;  // points whose window words are staged at a time
+#ifndef RF_DEPTH_N
+#define RF_DEPTH_N 2
+#endif
+constexpr int RF_DEPTH = RF_DEPTH_N;  // groups of 8 gathers in flight per thread
+constexpr int RF_SLOW = -1;           // window word of a point that is looked up cell by cell
+static_assert(RF_POINT_CHUNK % 64 == 0, "flags end on an 8-byte boundary");
 
 struct ArgBest {
   double score;
@@ -454,11 +459,11 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
   const int nh_max = sg.n_h_max;
 
   extern __shared__ __align__(16) unsigned char s_raw[];
-  double* memo = reinterpret_cast<double*>(s_raw);                 // [n_tr]
+  int* s_word = reinterpret_cast<int*>(s_raw);                     // [RF_POINT_CHUNK], 16 B aligned
+  unsigned char* s_flag = reinterpret_cast<unsigned char*>(s_word + RF_POINT_CHUNK);  // [RF_POINT_CHUNK / 8]
+  double* memo = reinterpret_cast<double*>(s_flag + RF_POINT_CHUNK / 8);  // [n_tr]
   double* hacc = memo + n_tr;                                      // [nh_max^2]
   int* memo_rot = reinterpret_cast<int*>(hacc + nh_max * nh_max);  // [n_tr]
-  int* cxh = memo_rot + n_tr;                                      // [nh_max][RF_POINT_CHUNK]
-  int* cyh = cxh + nh_max * RF_STRIDE;                        // row offset or -1
   __shared__ ArgBest s_red[RF_THREADS / 32];
   __shared__ int s_ctl[4];
 
@@ -512,20 +517,29 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
     const float* thy = sg.t_high + j * nh_max;
 
     for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) hacc[c] = 0.0;
+    const float tx0 = thx[0], ty0 = thy[0];
     for (int p0 = 0; p0 < n_pts; p0 += RF_POINT_CHUNK) {
       const int pc = min(RF_POINT_CHUNK, n_pts - p0);
       __syncthreads();
-      for (int pl = threadIdx.x; pl < pc; pl += RF_THREADS) {
-        const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
-        for (int k = 0; k < nhx; ++k) {
-          const int cx = cell_fast(cm, __fadd_rn(q.x, thx[k]));
-          cxh[k * RF_STRIDE + pl] = (cx >= tm.ax0 && cx <= tm.ax1) ? cx - tm.ax0 : -1;
+      // Window words (thread = point).  The hi-res steps advance by exactly one
+      // cell, so when the first sum of an axis lies clear of a cell edge (margin
+      // SearchGrid::reg_eps_h, proven on the host) step k hits cell + k: a point
+      // whose whole nhx x nhy window lies inside the table's rectangle is one
+      // word = index of the window's first cell.  Other points are flagged.
+      for (int pl = threadIdx.x; pl < ((pc + 31) & ~31); pl += RF_THREADS) {
+        int word = RF_SLOW;
+        if (pl < pc) {
+          const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
+          int cx0, cy0;
+          bool ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps_h, sg.reg_qmax_h, &cx0);
+          ok = cell_clear(cm, __fadd_rn(q.y, ty0), sg.reg_eps_h, sg.reg_qmax_h, &cy0) && ok;
+          ok = ok && cx0 >= tm.ax0 && cx0 + nhx - 1 <= tm.ax1 && cy0 >= tm.ay0 && cy0 + nhy - 1 <= tm.ay1;
+          if (ok) word = (cy0 - tm.ay0) * tm.stride + (cx0 - tm.ax0);
+          s_word[pl] = word;
         }
-        for (int k = 0; k < nhy; ++k) {
-          const int cy = cell_fast(cm, __fadd_rn(q.y, thy[k]));
-          cyh[k * RF_STRIDE + pl] =
-              (cy >= tm.ay0 && cy <= tm.ay1) ? (cy - tm.ay0) * tm.stride : -1;
-        }
+        // one flag per group of 8 points: does any of them need the slow path
+        const unsigned slow = __ballot_sync(0xffffffffu, pl < pc && word == RF_SLOW);
+        if ((threadIdx.x & 7) == 0) s_flag[pl >> 3] = (unsigned char)((slow >> (threadIdx.x & 31)) & 0xffu);
       }
       __syncthreads();
       // lanes run along x (consecutive cells of one table row => coalesced
@@ -533,25 +547,60 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
       for (int w = threadIdx.x; w < n_cand; w += RF_THREADS) {
         const int kx = w % nhx, ky = w / nhx;
         const int c = kx * nhy + ky;            // x outer, y inner (cc:126-129)
-        const int* px = cxh + kx * RF_STRIDE;
-        const int* py = cyh + ky * RF_STRIDE;
+        const double* __restrict__ hp = hi + ((size_t)ky * tm.stride + kx);
         double s = hacc[c];
-        int pl = 0;
         // the table holds lookup_log of every cell (normalize_pool_kernel); eight
         // independent gathers in flight, added in point order
-        for (; pl + 8 <= pc; pl += 8) {
-          double t[8];
+        auto slow_value = [&](int p) -> double {
+          const float2 q = rotate_point(a[p], rot.c, rot.s);
+          const int cx = cell_fast(cm, __fadd_rn(q.x, thx[kx]));
+          const int cy = cell_fast(cm, __fadd_rn(q.y, thy[ky]));
+          if (cx < tm.ax0 || cx > tm.ax1 || cy < tm.ay0 || cy > tm.ay1) return CSM_FLOOR_LOG;
+          return __ldg(hi + ((size_t)(cy - tm.ay0) * tm.stride + (cx - tm.ax0)));
+        };
+        // groups of 8 points; the loads of the next RF_DEPTH - 1 groups are issued
+        // before the adds of the current one (the sum itself is a serial chain)
+        const int ng = pc >> 3;
+        double buf[RF_DEPTH][8];
+        bool fast[RF_DEPTH];
+        auto load8 = [&](int g, double* t) {
+          const int4 w0 = *reinterpret_cast<const int4*>(s_word + 8 * g);
+          const int4 w1 = *reinterpret_cast<const int4*>(s_word + 8 * g + 4);
+          t[0] = __ldg(hp + w0.x); t[1] = __ldg(hp + w0.y); t[2] = __ldg(hp + w0.z); t[3] = __ldg(hp + w0.w);
+          t[4] = __ldg(hp + w1.x); t[5] = __ldg(hp + w1.y); t[6] = __ldg(hp + w1.z); t[7] = __ldg(hp + w1.w);
+        };
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int ox = px[pl + u], oy = py[pl + u];
-            t[u] = ((ox | oy) >= 0) ? __ldg(hi + oy + ox) : CSM_FLOOR_LOG;
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) s = __dadd_rn(s, t[u]);
+        for (int d = 0; d < RF_DEPTH - 1; ++d) {
+          fast[d] = d < ng && s_flag[d] == 0;
+          if (fast[d]) load8(d, buf[d]);
         }
-        for (; pl < pc; ++pl) {
-          const int ox = px[pl], oy = py[pl];
-          s = __dadd_rn(s, ((ox | oy) >= 0) ? __ldg(hi + oy + ox) : CSM_FLOOR_LOG);
+#pragma unroll 1
+        for (int g0 = 0; g0 < ng; g0 += RF_DEPTH) {
+#pragma unroll
+          for (int d = 0; d < RF_DEPTH; ++d) {
+            const int g = g0 + d;
+            if (g < ng) {
+              constexpr int ahead = RF_DEPTH - 1;
+              const int dn = (d + ahead) % RF_DEPTH;
+              fast[dn] = g + ahead < ng && s_flag[g + ahead] == 0;
+              if (fast[dn]) load8(g + ahead, buf[dn]);
+              if (fast[d]) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s = __dadd_rn(s, buf[d][u]);
+              } else {
+#pragma unroll 1
+                for (int u = 0; u < 8; ++u) {
+                  const int wd = s_word[8 * g + u];
+                  s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + 8 * g + u));
+                }
+              }
+            }
+          }
+        }
+#pragma unroll 1
+        for (int pl = 8 * ng; pl < pc; ++pl) {
+          const int wd = s_word[pl];
+          s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + pl));
         }
         hacc[c] = s;
       }
@@ -586,9 +635,8 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
 }
 
 static size_t refine_smem_bytes(int n_t, int nh_max) {
-  return (size_t)n_t * n_t * (sizeof(double) + sizeof(int)) +
-         (size_t)nh_max * nh_max * sizeof(double) +
-         (size_t)2 * nh_max * RF_STRIDE * sizeof(int);
+  return (size_t)n_t * n_t * sizeof(double) + (size_t)nh_max * nh_max * sizeof(double) +
+         (size_t)n_t * n_t * sizeof(int) + (size_t)RF_POINT_CHUNK * sizeof(int) + RF_POINT_CHUNK / 8;
 }
 
 void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,

@@ -159,6 +159,14 @@ class CorrelativeScanMatcher:
                                              C.byref(lo), C.byref(hi))
         return lo.value, hi.value
 
+    def regular_check(self, n_samples: int = 200000, seed: int = 1):
+        """Test hook: replay the kernels' regular-cell rule on the host against the
+        exact cell map; returns (predictions checked, low-res misses, hi-res misses)."""
+        n, bl, bh = C.c_int64(), C.c_int64(), C.c_int64()
+        check(self._L.nautilus_csm_regular_check(self._h, n_samples, seed, C.byref(n), C.byref(bl),
+                                                 C.byref(bh)))
+        return n.value, bl.value, bh.value
+
     def GetUncertaintyMatrix(self, pointcloud_a, pointcloud_b, rotation: float | None = None):
         """Olson covariance: 3x3 over all rotations (cc:267-319) or, with `rotation`,
         2x2 over translations (cc:322-373).  float32 matrix like the Eigen result."""

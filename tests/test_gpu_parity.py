@@ -81,6 +81,18 @@ def test_ref_unit_low_res_inexpressible():
     assert low.GetPointValue((0.0, -0.03)) == 0.56
 
 
+@pytest.mark.parametrize("cfg", [(30, 2, 0.3, 0.03), (30, 10, 0.3, 0.03), (4, 0.45, 0.3, 0.03),
+                                 (30, 2, 0.5, 0.05), (10, 1, 0.2, 0.01)])
+def test_regular_cell_rule_matches_exact_cells(cfg):
+    """K5 / K6 take the cells of consecutive translations from the first one when its
+    float quotient lies clear of a cell edge; the rule must agree with the exact map
+    (floor((double)v / res), h:98-101) on random and edge-hugging coordinates."""
+    m = CorrelativeScanMatcher(*cfg)
+    n, bad_low, bad_high = m.regular_check(300000, seed=7)
+    m.close()
+    assert n > 1000000 and bad_low == 0 and bad_high == 0
+
+
 def test_low_res_from_random_tables_vs_oracle():
     rng = np.random.default_rng(3)
     for (rg, lo, hi) in [(4, 1, 0.5), (0.3, 0.3, 0.03), (6, 0.3, 0.03), (5, 0.7, 0.1)]:
