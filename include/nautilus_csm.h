@@ -57,8 +57,9 @@ typedef struct NautilusCsmParams {
   int32_t margin_cells; /* table crop margin in hi-res cells around the scan's
                            occupied box.  <0 => never crop (every table is
                            computed over the full grid, bit-identical to the
-                           reference); 0 => default (160: truncated tails are
-                           below 1e-20 of the table maximum)                   */
+                           reference); 0 => default (128: cells above the lookup
+                           floor differ from the uncropped table by at most
+                           5e-14 relative, scripts/margin_study.py)            */
   int32_t max_tables;   /* resident hi-res table slots per wave; 0 => auto     */
   int32_t stage_cells;  /* shared-memory budget of the low-res scorer's staged table,
                            in doubles; 0 => default                             */

@@ -463,7 +463,7 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
   h->geo.res_h = p->high_res;
   h->geo.res_l = p->low_res;
   h->geo.bm_stride = (h->geo.w + 31) / 32;
-  h->geo.margin = p->margin_cells < 0 ? -1 : (p->margin_cells == 0 ? 160 : p->margin_cells);
+  h->geo.margin = p->margin_cells < 0 ? -1 : (p->margin_cells == 0 ? 128 : p->margin_cells);
   // blur(sigma, sigma, 0, true, true): sigma is a float parameter there
   const float sigma_f = (float)(p->blur_sigma > 0 ? p->blur_sigma : 4.0);
   if (sigma_f < 0.5f) { delete h; return fail(NAUTILUS_EINVAL, "blur_sigma < 0.5 is a no-op in CImg; unsupported"); }

@@ -466,6 +466,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
   int* memo_rot = reinterpret_cast<int*>(hacc + nh_max * nh_max);  // [n_tr]
   __shared__ ArgBest s_red[RF_THREADS / 32];
   __shared__ int s_ctl[4];
+  __shared__ double s_bound;
 
   const float2* a = points + offsets[pw.a_scan];
   const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
@@ -506,6 +507,12 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
       else if (top.score == -INFINITY && best_prob == -INFINITY) { stop = 1; status = 1; }
       if (!stop) { memo[top.idx] = -INFINITY; ++n_pops; }
       s_ctl[0] = stop;
+      // Every table value is log(v <= 1) <= 0, so a candidate's running sum only
+      // falls: once it is below best_prob * n_pts (taken a few ulps low, so that the
+      // rounded quotient cannot come out above best_prob) the candidate cannot win
+      // the strict '>' of cc:225 and its remaining points are skipped.
+      s_bound = best_prob == -INFINITY ? -INFINITY
+                                       : __dmul_rn(__dmul_rn(best_prob, (double)n_pts), 1.0 + 0x1p-50);
     }
     __syncthreads();
     if (s_ctl[0]) break;
@@ -549,6 +556,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
         const int c = kx * nhy + ky;            // x outer, y inner (cc:126-129)
         const double* __restrict__ hp = hi + ((size_t)ky * tm.stride + kx);
         double s = hacc[c];
+        const double bound = s_bound;
         // the table holds lookup_log of every cell (normalize_pool_kernel); eight
         // independent gathers in flight, added in point order
         auto slow_value = [&](int p) -> double {
@@ -574,8 +582,9 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
           fast[d] = d < ng && s_flag[d] == 0;
           if (fast[d]) load8(d, buf[d]);
         }
+        bool dead = false;  // every candidate of this warp has fallen below the bound
 #pragma unroll 1
-        for (int g0 = 0; g0 < ng; g0 += RF_DEPTH) {
+        for (int g0 = 0; g0 < ng && !dead; g0 += RF_DEPTH) {
 #pragma unroll
           for (int d = 0; d < RF_DEPTH; ++d) {
             const int g = g0 + d;
@@ -596,11 +605,16 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
               }
             }
           }
+          dead = !__any_sync(__activemask(), s >= bound);
         }
+        if (dead) {
+          s = -INFINITY;  // (below the bound: any value that cannot win will do)
+        } else {
 #pragma unroll 1
-        for (int pl = 8 * ng; pl < pc; ++pl) {
-          const int wd = s_word[pl];
-          s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + pl));
+          for (int pl = 8 * ng; pl < pc; ++pl) {
+            const int wd = s_word[pl];
+            s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + pl));
+          }
         }
         hacc[c] = s;
       }
