@@ -322,6 +322,8 @@ def run_ours(args):
     props = torch.cuda.get_device_properties(local)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
     smem_peak = props.multi_processor_count * 128 * sm_mhz * 1e6 / 1e9
+    fp64_peak = props.multi_processor_count * 64 * sm_mhz * 1e6 / 1e9       # Gadd/s
+    fp64_achieved = low_bytes / 8.0 / (acc["low"] * 1e-3) / 1e9             # one add per table read
     table_bytes = 8.0 * (m.w_high ** 2 + m.w_low ** 2) * args.scans * args.steps
     kernels = {
         "low_score_kernel": {"ms_per_step": acc["low"] / args.steps,
@@ -352,12 +354,16 @@ def run_ours(args):
                      "traffic": ncu_traffic_bytes("low_score_kernel"),
                      "peak_source": peak_kind, "launches": waves * args.steps,
                      "smem_peak": smem_peak, "smem_frac": achieved / smem_peak,
+                     "fp64_add_peak": fp64_peak, "fp64_add_achieved": fp64_achieved,
+                     "fp64_add_frac": fp64_achieved / fp64_peak,
                      "note": "algorithmic 8 B per (candidate, point), SURVEY 8(d).  The kernel "
-                             "stages its table in shared memory, so its HBM traffic is ~0 and "
-                             "frac > 1 against the HBM copy peak is expected; the binding "
-                             "resource is shared-memory bandwidth: smem_peak = SMs x 128 B/clk x "
-                             "SM clock (derived, GB/s), smem_frac = achieved / smem_peak "
-                             "(see DESIGN.md section 3)"},
+                             "stages its table in shared memory and loads a patch once per run "
+                             "of points that share it, so neither HBM (traffic ~0, frac > 1 "
+                             "expected) nor shared memory (smem_peak = SMs x 128 B/clk x SM "
+                             "clock) binds it: what remains is one fp64 add per (candidate, "
+                             "point) in point order.  fp64_add_peak = SMs x 64 adds/clk x SM "
+                             "clock (measured: scripts/micro/dadd_bench.cu, 2 warp-DADD/clk/SM), "
+                             "in Gadd/s; fp64_add_frac is the binding fraction (DESIGN.md 3)"},
         "kernels": kernels,
     }
     if not args.no_cpu_baseline:
