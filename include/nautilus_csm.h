@@ -81,6 +81,7 @@ typedef struct NautilusCsmTimings {
   float ms_refine;   /* memo reduction + best-first hi-res refinement          */
   int32_t launches;  /* kernels launched by the call                           */
   int32_t waves;     /* table waves the call was split into                    */
+  int32_t spec_windows; /* hi-res windows scored speculatively (K6 queue length) */
 } NautilusCsmTimings;
 
 const char* nautilus_csm_last_error(void);

@@ -43,7 +43,8 @@ class Stats(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("ms_tables", C.c_float), ("ms_low", C.c_float),
-                ("ms_refine", C.c_float), ("launches", C.c_int32), ("waves", C.c_int32)]
+                ("ms_refine", C.c_float), ("launches", C.c_int32), ("waves", C.c_int32),
+                ("spec_windows", C.c_int32)]
 
 
 EXPORTS = [
@@ -93,7 +94,8 @@ def lib():
     if not os.path.exists(LIB_PATH):
         raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
                            "g.build()'` (there is no CPU fallback)")
-    L = C.CDLL(LIB_PATH)
+    # NAUTILUS_CSM_LIB: a tuning variant built by scripts/ab_build.sh (A/B runs only)
+    L = C.CDLL(os.environ.get("NAUTILUS_CSM_LIB") or LIB_PATH)
     vp, d, f = C.c_void_p, C.c_double, C.c_float
     i32, i64, u64 = C.c_int32, C.c_int64, C.c_uint64
     L.nautilus_csm_last_error.restype = C.c_char_p

@@ -511,6 +511,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->user_scans.release(); h->tmp_scans.release();
   h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();
   h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
+  h->spec_pairs_dev.release(); h->spec_items_dev.release(); h->spec_out_dev.release(); h->spec_counters_dev.release();
   for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
   if (h->table_stream) cudaStreamDestroy(h->table_stream);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -670,6 +671,17 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if ((rc = h->chunk_rot_dev.reserve((size_t)max_wave_pairs * chunks * n_tr))) return rc;
   sb.chunk_best = h->chunk_best_dev.p;
   sb.chunk_rot = h->chunk_rot_dev.p;
+  const char* rf_env = getenv("NAUTILUS_CSM_REFINE");
+  const bool rf_serial = rf_env && !strcmp(rf_env, "serial");
+  sb.spec_pairs = nullptr; sb.spec_items = nullptr; sb.spec_out = nullptr; sb.spec_counters = nullptr;
+  if (!rf_serial) {
+    if ((rc = h->spec_pairs_dev.reserve(max_wave_pairs))) return rc;
+    if ((rc = h->spec_items_dev.reserve((size_t)max_wave_pairs * RF_SPEC_CAP))) return rc;
+    if ((rc = h->spec_out_dev.reserve((size_t)max_wave_pairs * RF_SPEC_CAP))) return rc;
+    if ((rc = h->spec_counters_dev.reserve(2 * (size_t)n_waves))) return rc;
+    sb.spec_pairs = h->spec_pairs_dev.p; sb.spec_items = h->spec_items_dev.p;
+    sb.spec_out = h->spec_out_dev.p; sb.spec_counters = h->spec_counters_dev.p;
+  }
 
   if (h->geo.wl + 1 > 65535)
     return fail(NAUTILUS_EINVAL, "low-res grid too large for the 16-bit row lists of the search");
@@ -723,11 +735,12 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
                      h->metas_dev.p + base, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
                      table_cells, st);
     CU_TRY(cudaEventRecord(evt(w, 3), st));
-    launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p + base,
-                  h->metas_dev.p + base, h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
-                  h->results_dev.p, st);
+    if (!rf_serial) sb.spec_counters = h->spec_counters_dev.p + 2 * w;  // the wave's queue counters
+    launches += 1 + launch_refine(h->geo, h->grid, h->cm_high, ss.points, ss.offsets,
+                                  h->slots_dev.p + base, h->metas_dev.p + base, h->pairs_dev.p + k0,
+                                  h->rots_dev.p, k1 - k0, sb, h->results_dev.p, rf_serial,
+                                  h->sm_count, st);
     CU_TRY(cudaEventRecord(evt(w, 4), st));
-    launches += 2;
     const int next = ring ? w + 1 : w + 2;  // issued after the event it may wait on is recorded
     if (next < n_waves && (rc = issue_tables(next))) return rc;
   }
@@ -735,10 +748,15 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   std::vector<PairResult> res(n_pairs);
   CU_TRY(cudaMemcpyAsync(res.data(), h->results_dev.p, sizeof(PairResult) * n_pairs,
                          cudaMemcpyDeviceToHost, st));
+  std::vector<int> spec_counts(2 * (size_t)n_waves, 0);
+  if (!rf_serial)
+    CU_TRY(cudaMemcpyAsync(spec_counts.data(), h->spec_counters_dev.p, sizeof(int) * 2 * n_waves,
+                           cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
 
   h->timings.launches = launches;
   h->timings.waves = n_waves;
+  for (int w = 0; w < n_waves; ++w) h->timings.spec_windows += spec_counts[2 * w];
   for (int w = 0; w < n_waves; ++w) {
     float a = 0, b = 0, c = 0;
     cudaEventElapsedTime(&a, evt(w, 0), evt(w, 1));

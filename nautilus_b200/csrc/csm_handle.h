@@ -144,6 +144,10 @@ struct NautilusCsm {
   DevBuf<PairResult> results_dev;
   DevBuf<double> chunk_best_dev;
   DevBuf<int> chunk_rot_dev;
+  DevBuf<SpecPair> spec_pairs_dev;
+  DevBuf<SpecItem> spec_items_dev;
+  DevBuf<SpecOut> spec_out_dev;
+  DevBuf<int> spec_counters_dev;
   std::vector<cudaEvent_t> events;
   NautilusCsmTimings timings{};
   int last_n_pairs = 0;

@@ -71,22 +71,54 @@ struct Rotation {
   float theta, c, s, pad;
 };
 
+// Speculative refinement (csm_search.cu, K6): state of a pair after its first
+// pop, one queue entry per hi-res window that the reference may still open, and
+// the window's result.
+#ifndef RF_SPEC_CAP_N
+#define RF_SPEC_CAP_N 96
+#endif
+constexpr int RF_SPEC_CAP = RF_SPEC_CAP_N;  // listed windows per pair; beyond it the pair finishes serially
+struct SpecPair {
+  double best_prob;   // best1: result of the first pop
+  float x, y, theta;
+  int status;         // 1: nothing to score
+  int n_list;         // windows listed (<= RF_SPEC_CAP)
+  int n_more;         // slots with bound >= best1 beyond the list
+  int item_base;      // first queue entry of the pair
+  int first_tr;       // slot of the first pop (-1: none)
+  long long n_high;   // candidates of the first pop
+};
+struct SpecItem {
+  int pair, tr, rot, pad;  // pair (wave-relative), slot i*n_t+j, rotation index within the pair
+  double memo;             // the slot's low-res bound
+};
+struct SpecOut {
+  double score;
+  int idx, pad;
+};
+
 struct SearchBuffers {
   double* chunk_best;   // [n_pairs][n_chunks_max][n_t*n_t] best score per theta chunk
   int* chunk_rot;       // same shape: rotation index (within the pair) of that best
   int chunks_per_pair;  // theta chunks per pair (uniform upper bound)
   int rot_per_chunk;
+  SpecPair* spec_pairs;  // [n_pairs]
+  SpecItem* spec_items;  // [n_pairs * RF_SPEC_CAP]
+  SpecOut* spec_out;     // [n_pairs * RF_SPEC_CAP]
+  int* spec_counters;    // [0] queue entries written, [1] next entry to fetch
 };
 
 void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm_low,
                       const float2* points, const long long* offsets, const TableSlot* slots,
                       const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
                       int n_pairs, const SearchBuffers& sb, int table_cells, cudaStream_t stream);
-void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
-                   const float2* points, const long long* offsets, const TableSlot* slots,
-                   const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
-                   int n_pairs, const SearchBuffers& sb, PairResult* results,
-                   cudaStream_t stream);
+// Returns the number of kernels launched.  serial: one block per pair runs the
+// whole best-first loop; otherwise first pop / speculative windows / replay.
+int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
+                  const float2* points, const long long* offsets, const TableSlot* slots,
+                  const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                  int n_pairs, const SearchBuffers& sb, PairResult* results, bool serial,
+                  int sm_count, cudaStream_t stream);
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells);
 // GetUncertaintyMatrix (cc:267-373) after launch_low_score filled sb for the pair:
 // costs[n_rot][n_t*n_t] scratch, out = dims x dims floats (row-major).

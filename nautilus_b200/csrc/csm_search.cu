@@ -407,11 +407,31 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
 }
 
 // ---------------------------------------------------------------------------
-// K6  memo reduction + best-first hi-res refinement, one block per pair.
+// K6  memo reduction + best-first hi-res refinement.
 // Follows GetTransformation's loop (CorrelativeScanMatcher.cc:170-243):
 //   pop the first maximum of the memo in slot (AbsCoords) order, invalidate
 //   it, stop when it is below the best hi-res score so far, otherwise score
 //   the hi-res window it opens and keep a strictly better result.
+//
+// The loop is a serial chain per pair (mean 3.6 windows, maximum 76 on the bench
+// batch), so one block per pair leaves the GPU waiting for the longest chain.
+// The default path therefore runs it in three kernels:
+//   refine_first_kernel   block per pair: memo, first pop -> best1, and the list
+//                         of slots the reference can still pop: every later pop
+//                         needs bound >= best >= best1, and pops go in (bound
+//                         descending, slot order) -- so they are a PREFIX of the
+//                         slots with bound >= best1 in that order;
+//   refine_spec_kernel    persistent blocks fetch (pair, slot) windows from one
+//                         queue and score them independently (early exit against
+//                         best1, which is never above the reference's bound);
+//   refine_finish_kernel  block per pair: replays the reference's decisions over
+//                         the list in order (stop / count / strictly better) and
+//                         writes the result; a pair whose list was cut at
+//                         RF_SPEC_CAP carries on with the serial loop.
+// Windows scored beyond the reference's stopping point are discarded by the
+// replay and not counted, so pose, score and the n_high / n_pops counters are
+// those of the sequential loop.  launch_refine(serial=true) keeps the
+// one-kernel form.
 // ---------------------------------------------------------------------------
 constexpr int RF_THREADS = 128;
 constexpr int RF_POINT_CHUNK = 1024;  // points whose window words are staged at a time
@@ -449,21 +469,252 @@ __device__ ArgBest block_argmax(ArgBest v, ArgBest* s_red) {
   return r;
 }
 
+// Shared-memory carve-up of the refine kernels (dynamic part).
+struct RefineShared {
+  int* word;            // [RF_POINT_CHUNK], 16 B aligned
+  unsigned char* flag;  // [RF_POINT_CHUNK / 8]
+  double* hacc;         // [nh_max^2]
+  double* memo;         // [n_tr]   (first / finish / serial kernels)
+  int* memo_rot;        // [n_tr]
+};
+
+__device__ __forceinline__ RefineShared carve_refine(unsigned char* raw, int nh_max, int n_tr) {
+  RefineShared sh;
+  sh.word = reinterpret_cast<int*>(raw);
+  sh.flag = reinterpret_cast<unsigned char*>(sh.word + RF_POINT_CHUNK);
+  sh.hacc = reinterpret_cast<double*>(sh.flag + RF_POINT_CHUNK / 8);
+  sh.memo = sh.hacc + nh_max * nh_max;
+  sh.memo_rot = reinterpret_cast<int*>(sh.memo + n_tr);
+  return sh;
+}
+
+// Every table value is log(v <= 1) <= 0, so a candidate's running sum only
+// falls: once it is below best_prob * n_pts (taken a few ulps low, so that the
+// rounded quotient cannot come out above best_prob) the candidate cannot win
+// the strict '>' of cc:225 and its remaining points are skipped.
+__device__ __forceinline__ double dead_bound(double best_prob, int n_pts) {
+  return best_prob == -INFINITY ? -INFINITY
+                                : __dmul_rn(__dmul_rn(best_prob, (double)n_pts), 1.0 + 0x1p-50);
+}
+
+// memo[slot] = max over theta, earliest theta on ties (chunks ascend in theta)
+__device__ __forceinline__ void reduce_memo(const SearchBuffers& sb, int pair, int n_rot, int n_tr,
+                                            double* memo, int* memo_rot) {
+  const int n_chunks = (n_rot + sb.rot_per_chunk - 1) / sb.rot_per_chunk;
+  for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) {
+    double b = -INFINITY;
+    int br = 0;
+    for (int ch = 0; ch < n_chunks; ++ch) {
+      const size_t at = ((size_t)pair * sb.chunks_per_pair + ch) * n_tr + tr;
+      const double s = sb.chunk_best[at];
+      if (s > b) { b = s; br = sb.chunk_rot[at]; }
+    }
+    memo[tr] = b;
+    memo_rot[tr] = br;
+  }
+}
+
+// std::max_element over the memo: first maximum in slot order (cc:172-174)
+__device__ __forceinline__ ArgBest memo_top(const SearchGrid& sg, const double* memo, int n_tr,
+                                            ArgBest* s_red) {
+  ArgBest mine = {-INFINITY, INT_MAX, -1};
+  for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) {
+    ArgBest c = {memo[tr], sg.slot_rank[tr], tr};
+    mine = arg_better(mine, c);
+  }
+  return block_argmax(mine, s_red);
+}
+
+// GetProbAndTransformation (cc:117-143) over the hi-res window of low-res slot
+// (i, j) at one rotation, by the whole block: the best candidate (score already
+// divided by n_pts; idx = kx * nhy + ky, the reference's x-outer / y-inner rank;
+// idx < 0 when no candidate can beat `bound`).  Candidates whose running sum
+// falls below `bound` (see dead_bound) are dropped.
+__device__ ArgBest score_window(const SearchGrid& sg, const CellMap& cm, const float2* __restrict__ a,
+                                int n_pts, const TableMeta& tm, const double* __restrict__ hi,
+                                const Rotation rot, int i, int j, double bound,
+                                const RefineShared& sh, ArgBest* s_red) {
+  const int nh_max = sg.n_h_max;
+  const int nhx = sg.n_h[i], nhy = sg.n_h[j], n_cand = nhx * nhy;
+  const float* thx = sg.t_high + i * nh_max;
+  const float* thy = sg.t_high + j * nh_max;
+  int* s_word = sh.word;
+  unsigned char* s_flag = sh.flag;
+  double* hacc = sh.hacc;
+
+  for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) hacc[c] = 0.0;
+  const float tx0 = thx[0], ty0 = thy[0];
+  for (int p0 = 0; p0 < n_pts; p0 += RF_POINT_CHUNK) {
+    const int pc = min(RF_POINT_CHUNK, n_pts - p0);
+    __syncthreads();
+    // Window words (thread = point).  The hi-res steps advance by exactly one
+    // cell, so when the first sum of an axis lies clear of a cell edge (margin
+    // SearchGrid::reg_eps_h, proven on the host) step k hits cell + k: a point
+    // whose whole nhx x nhy window lies inside the table's rectangle is one
+    // word = index of the window's first cell.  Other points are flagged.
+    for (int pl = threadIdx.x; pl < ((pc + 31) & ~31); pl += RF_THREADS) {
+      int word = RF_SLOW;
+      if (pl < pc) {
+        const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
+        int cx0, cy0;
+        bool ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps_h, sg.reg_qmax_h, &cx0);
+        ok = cell_clear(cm, __fadd_rn(q.y, ty0), sg.reg_eps_h, sg.reg_qmax_h, &cy0) && ok;
+        ok = ok && cx0 >= tm.ax0 && cx0 + nhx - 1 <= tm.ax1 && cy0 >= tm.ay0 && cy0 + nhy - 1 <= tm.ay1;
+        if (ok) word = (cy0 - tm.ay0) * tm.stride + (cx0 - tm.ax0);
+        s_word[pl] = word;
+      }
+      // one flag per group of 8 points: does any of them need the slow path
+      const unsigned slow = __ballot_sync(0xffffffffu, pl < pc && word == RF_SLOW);
+      if ((threadIdx.x & 7) == 0) s_flag[pl >> 3] = (unsigned char)((slow >> (threadIdx.x & 31)) & 0xffu);
+    }
+    __syncthreads();
+    // lanes run along x (consecutive cells of one table row => coalesced
+    // gathers); the candidate's rank in the reference's loop is kx*nhy + ky
+    for (int w = threadIdx.x; w < n_cand; w += RF_THREADS) {
+      const int kx = w % nhx, ky = w / nhx;
+      const int c = kx * nhy + ky;            // x outer, y inner (cc:126-129)
+      const double* __restrict__ hp = hi + ((size_t)ky * tm.stride + kx);
+      double s = hacc[c];
+      // the table holds lookup_log of every cell (normalize_pool_kernel); eight
+      // independent gathers in flight, added in point order
+      auto slow_value = [&](int p) -> double {
+        const float2 q = rotate_point(a[p], rot.c, rot.s);
+        const int cx = cell_fast(cm, __fadd_rn(q.x, thx[kx]));
+        const int cy = cell_fast(cm, __fadd_rn(q.y, thy[ky]));
+        if (cx < tm.ax0 || cx > tm.ax1 || cy < tm.ay0 || cy > tm.ay1) return CSM_FLOOR_LOG;
+        return __ldg(hi + ((size_t)(cy - tm.ay0) * tm.stride + (cx - tm.ax0)));
+      };
+      // groups of 8 points; the loads of the next RF_DEPTH - 1 groups are issued
+      // before the adds of the current one (the sum itself is a serial chain)
+      const int ng = pc >> 3;
+      double buf[RF_DEPTH][8];
+      bool fast[RF_DEPTH];
+      auto load8 = [&](int g, double* t) {
+        const int4 w0 = *reinterpret_cast<const int4*>(s_word + 8 * g);
+        const int4 w1 = *reinterpret_cast<const int4*>(s_word + 8 * g + 4);
+        t[0] = __ldg(hp + w0.x); t[1] = __ldg(hp + w0.y); t[2] = __ldg(hp + w0.z); t[3] = __ldg(hp + w0.w);
+        t[4] = __ldg(hp + w1.x); t[5] = __ldg(hp + w1.y); t[6] = __ldg(hp + w1.z); t[7] = __ldg(hp + w1.w);
+      };
+#pragma unroll
+      for (int d = 0; d < RF_DEPTH - 1; ++d) {
+        fast[d] = d < ng && s_flag[d] == 0;
+        if (fast[d]) load8(d, buf[d]);
+      }
+      bool dead = false;  // every candidate of this warp has fallen below the bound
+#pragma unroll 1
+      for (int g0 = 0; g0 < ng && !dead; g0 += RF_DEPTH) {
+#pragma unroll
+        for (int d = 0; d < RF_DEPTH; ++d) {
+          const int g = g0 + d;
+          if (g < ng) {
+            constexpr int ahead = RF_DEPTH - 1;
+            const int dn = (d + ahead) % RF_DEPTH;
+            fast[dn] = g + ahead < ng && s_flag[g + ahead] == 0;
+            if (fast[dn]) load8(g + ahead, buf[dn]);
+            if (fast[d]) {
+#pragma unroll
+              for (int u = 0; u < 8; ++u) s = __dadd_rn(s, buf[d][u]);
+            } else {
+#pragma unroll 1
+              for (int u = 0; u < 8; ++u) {
+                const int wd = s_word[8 * g + u];
+                s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + 8 * g + u));
+              }
+            }
+          }
+        }
+        dead = !__any_sync(__activemask(), s >= bound);
+      }
+      if (dead) {
+        s = -INFINITY;  // (below the bound: any value that cannot win will do)
+      } else {
+#pragma unroll 1
+        for (int pl = 8 * ng; pl < pc; ++pl) {
+          const int wd = s_word[pl];
+          s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + pl));
+        }
+      }
+      hacc[c] = s;
+    }
+  }
+  __syncthreads();
+  // strict '>' in x-outer / y-inner order == max score, smallest index on ties
+  ArgBest hb = {-INFINITY, INT_MAX, -1};
+  for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) {
+    ArgBest cnd = {__ddiv_rn(hacc[c], (double)n_pts), c, c};
+    hb = arg_better(hb, cnd);
+  }
+  return block_argmax(hb, s_red);
+}
+
+// State of one pair's best-first loop (meaningful in thread 0).
+struct BestState {
+  double prob;
+  float x, y, theta;
+  long long n_high, n_pops;
+  int status;
+};
+
+__device__ __forceinline__ void take_if_better(BestState& st, const ArgBest& htop, const SearchGrid& sg,
+                                               int i, int j, float theta) {
+  if (htop.idx >= 0 && htop.score > st.prob) {
+    const int nhy = sg.n_h[j];
+    st.prob = htop.score;
+    st.x = sg.t_high[i * sg.n_h_max + htop.idx / nhy];
+    st.y = sg.t_high[j * sg.n_h_max + htop.idx % nhy];
+    st.theta = theta;
+  }
+}
+
+// The serial loop of cc:170-243 from the state `st` and the (partly invalidated) memo.
+__device__ void best_first_loop(const SearchGrid& sg, const CellMap& cm, const float2* a, int n_pts,
+                                const TableMeta& tm, const double* hi, const Rotation* rots,
+                                const PairWork& pw, const RefineShared& sh, ArgBest* s_red,
+                                int* s_ctl, double* s_bound, BestState& st) {
+  const int n_t = sg.n_t, n_tr = n_t * n_t;
+  for (;;) {
+    const ArgBest top = memo_top(sg, sh.memo, n_tr, s_red);
+    if (threadIdx.x == 0) {
+      int stop = 0;
+      if (top.idx < 0 || top.score < st.prob) stop = 1;
+      else if (top.score == -INFINITY && st.prob == -INFINITY) { stop = 1; st.status = 1; }
+      if (!stop) { sh.memo[top.idx] = -INFINITY; ++st.n_pops; }
+      s_ctl[0] = stop;
+      *s_bound = dead_bound(st.prob, n_pts);
+    }
+    __syncthreads();
+    if (s_ctl[0]) break;
+    const int i = top.idx / n_t, j = top.idx - i * n_t;  // tr = i*n_t + j, x outer
+    const Rotation rot = rots[pw.rot_begin + sh.memo_rot[top.idx]];
+    const ArgBest htop = score_window(sg, cm, a, n_pts, tm, hi, rot, i, j, *s_bound, sh, s_red);
+    if (threadIdx.x == 0) {
+      st.n_high += sg.n_h[i] * sg.n_h[j];
+      take_if_better(st, htop, sg, i, j, rot.theta);
+    }
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ void write_result(PairResult* results, const PairWork& pw, int n_tr,
+                                             const BestState& st) {
+  PairResult r;
+  r.score = st.prob; r.x = st.x; r.y = st.y; r.theta = st.theta;
+  r.pad = st.status;
+  r.n_low = (long long)pw.n_rot * n_tr;
+  r.n_high = st.n_high; r.n_pops = st.n_pops;
+  results[pw.out_index] = r;
+}
+
+// One kernel, one block per pair: the whole loop in sequence.
 __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
     Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
     const Rotation* __restrict__ rots, SearchBuffers sb, PairResult* __restrict__ results) {
   const PairWork pw = pairs[blockIdx.x];
-  const int n_t = sg.n_t, n_tr = n_t * n_t;
-  const int nh_max = sg.n_h_max;
-
+  const int n_tr = sg.n_t * sg.n_t;
   extern __shared__ __align__(16) unsigned char s_raw[];
-  int* s_word = reinterpret_cast<int*>(s_raw);                     // [RF_POINT_CHUNK], 16 B aligned
-  unsigned char* s_flag = reinterpret_cast<unsigned char*>(s_word + RF_POINT_CHUNK);  // [RF_POINT_CHUNK / 8]
-  double* memo = reinterpret_cast<double*>(s_flag + RF_POINT_CHUNK / 8);  // [n_tr]
-  double* hacc = memo + n_tr;                                      // [nh_max^2]
-  int* memo_rot = reinterpret_cast<int*>(hacc + nh_max * nh_max);  // [n_tr]
+  const RefineShared sh = carve_refine(s_raw, sg.n_h_max, n_tr);
   __shared__ ArgBest s_red[RF_THREADS / 32];
   __shared__ int s_ctl[4];
   __shared__ double s_bound;
@@ -472,201 +723,226 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
   const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
   const TableMeta tm = metas[pw.table];
   const double* __restrict__ hi = slots[pw.table].values;
-  const int n_chunks = (pw.n_rot + sb.rot_per_chunk - 1) / sb.rot_per_chunk;
+  reduce_memo(sb, blockIdx.x, pw.n_rot, n_tr, sh.memo, sh.memo_rot);
+  __syncthreads();
+  BestState st = {-INFINITY, 0.f, 0.f, 0.f, 0, 0, 0};
+  best_first_loop(sg, cm, a, n_pts, tm, hi, rots, pw, sh, s_red, s_ctl, &s_bound, st);
+  if (threadIdx.x == 0) write_result(results, pw, n_tr, st);
+}
 
-  // memo[slot] = max over theta, earliest theta on ties (chunks ascend in theta)
-  for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) {
-    double b = -INFINITY;
-    int br = 0;
-    for (int ch = 0; ch < n_chunks; ++ch) {
-      const size_t at = ((size_t)blockIdx.x * sb.chunks_per_pair + ch) * n_tr + tr;
-      const double s = sb.chunk_best[at];
-      if (s > b) { b = s; br = sb.chunk_rot[at]; }
-    }
-    memo[tr] = b;
-    memo_rot[tr] = br;
-  }
+// --- speculative form --------------------------------------------------------
+
+__global__ void __launch_bounds__(RF_THREADS) refine_first_kernel(
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb) {
+  const PairWork pw = pairs[blockIdx.x];
+  const int n_t = sg.n_t, n_tr = n_t * n_t;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const RefineShared sh = carve_refine(s_raw, sg.n_h_max, n_tr);
+  __shared__ ArgBest s_red[RF_THREADS / 32];
+  __shared__ int s_ctl[4];
+  __shared__ double s_best;
+
+  const float2* a = points + offsets[pw.a_scan];
+  const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
+  const TableMeta tm = metas[pw.table];
+  const double* __restrict__ hi = slots[pw.table].values;
+  reduce_memo(sb, blockIdx.x, pw.n_rot, n_tr, sh.memo, sh.memo_rot);
   __syncthreads();
 
-  double best_prob = -INFINITY;   // meaningful in thread 0 only
-  float best_x = 0.f, best_y = 0.f, best_theta = 0.f;
-  long long n_high = 0, n_pops = 0;
-  int status = 0;
-
-  for (;;) {
-    // std::max_element over the memo: first maximum in slot order (cc:172-174)
-    ArgBest mine = {-INFINITY, INT_MAX, -1};
-    for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) {
-      ArgBest c = {memo[tr], sg.slot_rank[tr], tr};
-      mine = arg_better(mine, c);
-    }
-    const ArgBest top = block_argmax(mine, s_red);
-    if (threadIdx.x == 0) {
-      int stop = 0;
-      if (top.idx < 0 || top.score < best_prob) stop = 1;
-      else if (top.score == -INFINITY && best_prob == -INFINITY) { stop = 1; status = 1; }
-      if (!stop) { memo[top.idx] = -INFINITY; ++n_pops; }
-      s_ctl[0] = stop;
-      // Every table value is log(v <= 1) <= 0, so a candidate's running sum only
-      // falls: once it is below best_prob * n_pts (taken a few ulps low, so that the
-      // rounded quotient cannot come out above best_prob) the candidate cannot win
-      // the strict '>' of cc:225 and its remaining points are skipped.
-      s_bound = best_prob == -INFINITY ? -INFINITY
-                                       : __dmul_rn(__dmul_rn(best_prob, (double)n_pts), 1.0 + 0x1p-50);
-    }
-    __syncthreads();
-    if (s_ctl[0]) break;
-
-    const int i = top.idx / n_t, j = top.idx - i * n_t;  // tr = i*n_t + j, x outer
-    const Rotation rot = rots[pw.rot_begin + memo_rot[top.idx]];
-    const int nhx = sg.n_h[i], nhy = sg.n_h[j], n_cand = nhx * nhy;
-    const float* thx = sg.t_high + i * nh_max;
-    const float* thy = sg.t_high + j * nh_max;
-
-    for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) hacc[c] = 0.0;
-    const float tx0 = thx[0], ty0 = thy[0];
-    for (int p0 = 0; p0 < n_pts; p0 += RF_POINT_CHUNK) {
-      const int pc = min(RF_POINT_CHUNK, n_pts - p0);
-      __syncthreads();
-      // Window words (thread = point).  The hi-res steps advance by exactly one
-      // cell, so when the first sum of an axis lies clear of a cell edge (margin
-      // SearchGrid::reg_eps_h, proven on the host) step k hits cell + k: a point
-      // whose whole nhx x nhy window lies inside the table's rectangle is one
-      // word = index of the window's first cell.  Other points are flagged.
-      for (int pl = threadIdx.x; pl < ((pc + 31) & ~31); pl += RF_THREADS) {
-        int word = RF_SLOW;
-        if (pl < pc) {
-          const float2 q = rotate_point(a[p0 + pl], rot.c, rot.s);
-          int cx0, cy0;
-          bool ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps_h, sg.reg_qmax_h, &cx0);
-          ok = cell_clear(cm, __fadd_rn(q.y, ty0), sg.reg_eps_h, sg.reg_qmax_h, &cy0) && ok;
-          ok = ok && cx0 >= tm.ax0 && cx0 + nhx - 1 <= tm.ax1 && cy0 >= tm.ay0 && cy0 + nhy - 1 <= tm.ay1;
-          if (ok) word = (cy0 - tm.ay0) * tm.stride + (cx0 - tm.ax0);
-          s_word[pl] = word;
-        }
-        // one flag per group of 8 points: does any of them need the slow path
-        const unsigned slow = __ballot_sync(0xffffffffu, pl < pc && word == RF_SLOW);
-        if ((threadIdx.x & 7) == 0) s_flag[pl >> 3] = (unsigned char)((slow >> (threadIdx.x & 31)) & 0xffu);
-      }
-      __syncthreads();
-      // lanes run along x (consecutive cells of one table row => coalesced
-      // gathers); the candidate's rank in the reference's loop is kx*nhy + ky
-      for (int w = threadIdx.x; w < n_cand; w += RF_THREADS) {
-        const int kx = w % nhx, ky = w / nhx;
-        const int c = kx * nhy + ky;            // x outer, y inner (cc:126-129)
-        const double* __restrict__ hp = hi + ((size_t)ky * tm.stride + kx);
-        double s = hacc[c];
-        const double bound = s_bound;
-        // the table holds lookup_log of every cell (normalize_pool_kernel); eight
-        // independent gathers in flight, added in point order
-        auto slow_value = [&](int p) -> double {
-          const float2 q = rotate_point(a[p], rot.c, rot.s);
-          const int cx = cell_fast(cm, __fadd_rn(q.x, thx[kx]));
-          const int cy = cell_fast(cm, __fadd_rn(q.y, thy[ky]));
-          if (cx < tm.ax0 || cx > tm.ax1 || cy < tm.ay0 || cy > tm.ay1) return CSM_FLOOR_LOG;
-          return __ldg(hi + ((size_t)(cy - tm.ay0) * tm.stride + (cx - tm.ax0)));
-        };
-        // groups of 8 points; the loads of the next RF_DEPTH - 1 groups are issued
-        // before the adds of the current one (the sum itself is a serial chain)
-        const int ng = pc >> 3;
-        double buf[RF_DEPTH][8];
-        bool fast[RF_DEPTH];
-        auto load8 = [&](int g, double* t) {
-          const int4 w0 = *reinterpret_cast<const int4*>(s_word + 8 * g);
-          const int4 w1 = *reinterpret_cast<const int4*>(s_word + 8 * g + 4);
-          t[0] = __ldg(hp + w0.x); t[1] = __ldg(hp + w0.y); t[2] = __ldg(hp + w0.z); t[3] = __ldg(hp + w0.w);
-          t[4] = __ldg(hp + w1.x); t[5] = __ldg(hp + w1.y); t[6] = __ldg(hp + w1.z); t[7] = __ldg(hp + w1.w);
-        };
-#pragma unroll
-        for (int d = 0; d < RF_DEPTH - 1; ++d) {
-          fast[d] = d < ng && s_flag[d] == 0;
-          if (fast[d]) load8(d, buf[d]);
-        }
-        bool dead = false;  // every candidate of this warp has fallen below the bound
-#pragma unroll 1
-        for (int g0 = 0; g0 < ng && !dead; g0 += RF_DEPTH) {
-#pragma unroll
-          for (int d = 0; d < RF_DEPTH; ++d) {
-            const int g = g0 + d;
-            if (g < ng) {
-              constexpr int ahead = RF_DEPTH - 1;
-              const int dn = (d + ahead) % RF_DEPTH;
-              fast[dn] = g + ahead < ng && s_flag[g + ahead] == 0;
-              if (fast[dn]) load8(g + ahead, buf[dn]);
-              if (fast[d]) {
-#pragma unroll
-                for (int u = 0; u < 8; ++u) s = __dadd_rn(s, buf[d][u]);
-              } else {
-#pragma unroll 1
-                for (int u = 0; u < 8; ++u) {
-                  const int wd = s_word[8 * g + u];
-                  s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + 8 * g + u));
-                }
-              }
-            }
-          }
-          dead = !__any_sync(__activemask(), s >= bound);
-        }
-        if (dead) {
-          s = -INFINITY;  // (below the bound: any value that cannot win will do)
-        } else {
-#pragma unroll 1
-          for (int pl = 8 * ng; pl < pc; ++pl) {
-            const int wd = s_word[pl];
-            s = __dadd_rn(s, wd != RF_SLOW ? __ldg(hp + wd) : slow_value(p0 + pl));
-          }
-        }
-        hacc[c] = s;
-      }
-    }
-    __syncthreads();
-    // strict '>' in x-outer / y-inner order == max score, smallest index on ties
-    ArgBest hb = {-INFINITY, INT_MAX, -1};
-    for (int c = threadIdx.x; c < n_cand; c += RF_THREADS) {
-      ArgBest cnd = {__ddiv_rn(hacc[c], (double)n_pts), c, c};
-      hb = arg_better(hb, cnd);
-    }
-    const ArgBest htop = block_argmax(hb, s_red);
-    if (threadIdx.x == 0) {
-      n_high += n_cand;
-      if (htop.idx >= 0 && htop.score > best_prob) {
-        best_prob = htop.score;
-        best_x = thx[htop.idx / nhy];
-        best_y = thy[htop.idx % nhy];
-        best_theta = rot.theta;
-      }
-    }
-    __syncthreads();
+  SpecPair sp;
+  sp.best_prob = -INFINITY; sp.x = sp.y = sp.theta = 0.f;
+  sp.status = 0; sp.n_list = 0; sp.n_more = 0; sp.item_base = 0; sp.first_tr = -1; sp.n_high = 0;
+  const ArgBest top = memo_top(sg, sh.memo, n_tr, s_red);
+  if (top.idx < 0 || top.score == -INFINITY) {  // nothing to score (cc:209-212 would abort)
+    sp.status = top.idx < 0 ? 0 : 1;
+    if (threadIdx.x == 0) sb.spec_pairs[blockIdx.x] = sp;
+    return;
   }
+  const int i = top.idx / n_t, j = top.idx - i * n_t;
+  const Rotation rot = rots[pw.rot_begin + sh.memo_rot[top.idx]];
+  const ArgBest htop = score_window(sg, cm, a, n_pts, tm, hi, rot, i, j, -INFINITY, sh, s_red);
   if (threadIdx.x == 0) {
-    PairResult r;
-    r.score = best_prob; r.x = best_x; r.y = best_y; r.theta = best_theta;
-    r.pad = status;
-    r.n_low = (long long)pw.n_rot * n_tr;
-    r.n_high = n_high; r.n_pops = n_pops;
-    results[pw.out_index] = r;
+    BestState st = {-INFINITY, 0.f, 0.f, 0.f, 0, 0, 0};
+    take_if_better(st, htop, sg, i, j, rot.theta);
+    s_best = st.prob;
+    sp.best_prob = st.prob; sp.x = st.x; sp.y = st.y; sp.theta = st.theta;
+    sp.n_high = sg.n_h[i] * sg.n_h[j];
+    sp.first_tr = top.idx;
+    s_ctl[1] = 0;
+  }
+  __syncthreads();
+  // slots the reference may still pop: bound >= best1 (and not the one just popped)
+  const double b1 = s_best;
+  int q = 0;
+  for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) q += (tr != top.idx && sh.memo[tr] >= b1);
+  if (q) atomicAdd(&s_ctl[1], q);
+  __syncthreads();
+  const int n_q = s_ctl[1];
+  const int n_list = min(n_q, RF_SPEC_CAP);
+  if (threadIdx.x == 0) {
+    sp.n_list = n_list;
+    sp.n_more = n_q - n_list;
+    sp.item_base = n_list ? atomicAdd(&sb.spec_counters[0], n_list) : 0;
+    s_ctl[2] = sp.item_base;
+    sb.spec_pairs[blockIdx.x] = sp;
+  }
+  __syncthreads();
+  if (n_list == 0) return;
+  const int base = s_ctl[2];
+  // position in pop order: bound descending, slot rank ascending on ties
+  for (int tr = threadIdx.x; tr < n_tr; tr += RF_THREADS) {
+    const double m = sh.memo[tr];
+    if (tr == top.idx || !(m >= b1)) continue;
+    const int rk = sg.slot_rank[tr];
+    int pos = 0;
+    for (int o = 0; o < n_tr; ++o) {
+      const double mo = sh.memo[o];
+      pos += (o != top.idx) && (mo > m || (mo == m && sg.slot_rank[o] < rk));
+    }
+    if (pos < n_list) {
+      SpecItem it;
+      it.pair = blockIdx.x; it.tr = tr; it.rot = sh.memo_rot[tr]; it.pad = 0; it.memo = m;
+      sb.spec_items[base + pos] = it;
+    }
   }
 }
 
-static size_t refine_smem_bytes(int n_t, int nh_max) {
-  return (size_t)n_t * n_t * sizeof(double) + (size_t)nh_max * nh_max * sizeof(double) +
-         (size_t)n_t * n_t * sizeof(int) + (size_t)RF_POINT_CHUNK * sizeof(int) + RF_POINT_CHUNK / 8;
+__global__ void __launch_bounds__(RF_THREADS) refine_spec_kernel(
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const RefineShared sh = carve_refine(s_raw, sg.n_h_max, 0);
+  __shared__ ArgBest s_red[RF_THREADS / 32];
+  __shared__ int s_item;
+  const int n_items = sb.spec_counters[0];
+  const int n_t = sg.n_t;
+  for (;;) {
+    if (threadIdx.x == 0) s_item = atomicAdd(&sb.spec_counters[1], 1);
+    __syncthreads();
+    const int item = s_item;
+    if (item >= n_items) break;
+    const SpecItem it = sb.spec_items[item];
+    const PairWork pw = pairs[it.pair];
+    const float2* a = points + offsets[pw.a_scan];
+    const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
+    const TableMeta tm = metas[pw.table];
+    const double* __restrict__ hi = slots[pw.table].values;
+    const int i = it.tr / n_t, j = it.tr - i * n_t;
+    const Rotation rot = rots[pw.rot_begin + it.rot];
+    const double bound = dead_bound(sb.spec_pairs[it.pair].best_prob, n_pts);
+    const ArgBest htop = score_window(sg, cm, a, n_pts, tm, hi, rot, i, j, bound, sh, s_red);
+    if (threadIdx.x == 0) {
+      SpecOut o;
+      o.score = htop.score; o.idx = htop.idx; o.pad = 0;
+      sb.spec_out[item] = o;
+    }
+    __syncthreads();  // s_item is rewritten next turn
+  }
 }
 
-void launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
-                   const float2* points, const long long* offsets, const TableSlot* slots,
-                   const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
-                   int n_pairs, const SearchBuffers& sb, PairResult* results,
-                   cudaStream_t stream) {
-  if (n_pairs <= 0) return;
-  const size_t smem = refine_smem_bytes(sg.n_t, sg.n_h_max);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
+__global__ void __launch_bounds__(RF_THREADS) refine_finish_kernel(
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb, PairResult* __restrict__ results) {
+  const PairWork pw = pairs[blockIdx.x];
+  const int n_t = sg.n_t, n_tr = n_t * n_t;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const RefineShared sh = carve_refine(s_raw, sg.n_h_max, n_tr);
+  __shared__ ArgBest s_red[RF_THREADS / 32];
+  __shared__ int s_ctl[4];
+  __shared__ double s_bound;
+
+  const SpecPair sp = sb.spec_pairs[blockIdx.x];
+  BestState st = {sp.best_prob, sp.x, sp.y, sp.theta, sp.n_high, sp.first_tr >= 0 ? 1 : 0, sp.status};
+  if (threadIdx.x == 0) {
+    // the reference's decisions over the listed slots, in pop order
+    bool stopped = sp.first_tr < 0;
+    for (int k = 0; k < sp.n_list && !stopped; ++k) {
+      const SpecItem it = sb.spec_items[sp.item_base + k];
+      if (it.memo < st.prob) { stopped = true; break; }
+      if (it.memo == -INFINITY && st.prob == -INFINITY) { stopped = true; st.status = 1; break; }
+      const int i = it.tr / n_t, j = it.tr - i * n_t;
+      ++st.n_pops;
+      st.n_high += sg.n_h[i] * sg.n_h[j];
+      const SpecOut o = sb.spec_out[sp.item_base + k];
+      ArgBest htop = {o.score, o.idx, o.idx};
+      take_if_better(st, htop, sg, i, j, rots[pw.rot_begin + it.rot].theta);
+    }
+    // the list holds every slot with bound >= best1 unless it was cut
+    s_ctl[1] = (!stopped && sp.n_more > 0) ? 1 : 0;
   }
-  refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots, metas,
-                                                       pairs, rots, sb, results);
+  __syncthreads();
+  if (s_ctl[1]) {
+    const float2* a = points + offsets[pw.a_scan];
+    const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
+    const TableMeta tm = metas[pw.table];
+    const double* __restrict__ hi = slots[pw.table].values;
+    reduce_memo(sb, blockIdx.x, pw.n_rot, n_tr, sh.memo, sh.memo_rot);
+    __syncthreads();
+    if (threadIdx.x == 0) sh.memo[sp.first_tr] = -INFINITY;
+    for (int k = threadIdx.x; k < sp.n_list; k += RF_THREADS)
+      sh.memo[sb.spec_items[sp.item_base + k].tr] = -INFINITY;
+    __syncthreads();
+    best_first_loop(sg, cm, a, n_pts, tm, hi, rots, pw, sh, s_red, s_ctl, &s_bound, st);
+  }
+  if (threadIdx.x == 0) write_result(results, pw, n_tr, st);
+}
+
+static size_t refine_smem_bytes(int n_t, int nh_max, bool with_memo) {
+  size_t b = (size_t)RF_POINT_CHUNK * sizeof(int) + RF_POINT_CHUNK / 8 +
+             (size_t)nh_max * nh_max * sizeof(double);
+  if (with_memo) b += (size_t)n_t * n_t * (sizeof(double) + sizeof(int));
+  return b;
+}
+
+template <typename K>
+static void allow_smem(K kernel, size_t smem, size_t* configured) {
+  if (smem > 48 * 1024 && smem > *configured) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    *configured = smem;
+  }
+}
+
+int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
+                  const float2* points, const long long* offsets, const TableSlot* slots,
+                  const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                  int n_pairs, const SearchBuffers& sb, PairResult* results, bool serial,
+                  int sm_count, cudaStream_t stream) {
+  if (n_pairs <= 0) return 0;
+  const size_t smem = refine_smem_bytes(sg.n_t, sg.n_h_max, true);
+  static size_t conf_serial = 0, conf_first = 0, conf_spec = 0, conf_finish = 0;
+  if (serial) {
+    allow_smem(refine_kernel, smem, &conf_serial);
+    refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots, metas,
+                                                         pairs, rots, sb, results);
+    return 1;
+  }
+  const size_t smem_spec = refine_smem_bytes(sg.n_t, sg.n_h_max, false);
+  allow_smem(refine_first_kernel, smem, &conf_first);
+  allow_smem(refine_spec_kernel, smem_spec, &conf_spec);
+  allow_smem(refine_finish_kernel, smem, &conf_finish);
+  cudaMemsetAsync(sb.spec_counters, 0, 2 * sizeof(int), stream);
+  refine_first_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots,
+                                                             metas, pairs, rots, sb);
+  // persistent: as many blocks as stay resident, each fetching windows from the queue
+  static int per_sm = 0;
+  if (!per_sm) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, refine_spec_kernel, RF_THREADS, smem_spec);
+    if (per_sm < 1) per_sm = 1;
+  }
+  const long long max_items = (long long)n_pairs * RF_SPEC_CAP;
+  const int grid = (int)std::min<long long>((long long)sm_count * per_sm, std::max<long long>(max_items, 1));
+  refine_spec_kernel<<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets, slots,
+                                                              metas, pairs, rots, sb);
+  refine_finish_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots,
+                                                              metas, pairs, rots, sb, results);
+  return 3;
 }
 
 }  // namespace csm
