@@ -175,6 +175,38 @@ void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction
 
 int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out);
 
+/* --- front end ----------------------------------------------------------------
+ * Range -> point conversion and keyframe scoring on the device, so that a bag's
+ * scans cross PCIe once as ranges (4 B per beam):
+ *   nautilus::LaserScanToPointCloud            (src/input/pointcloud_helpers.cc:28-48)   variant 0
+ *   pointcloud_helpers::LaserScanToPointCloud  (third_party/csm/src/pointcloud_helpers.cc:44-66,
+ *                                               with FilterGlancing :21-42)              variant 1
+ *   ComputeScatterMatrixScore / GetLCCandidates (src/loop_closure/lc_candidate_filter.cc:23-81) */
+typedef struct NautilusLaserSpec {
+  float angle_min, angle_max, angle_increment, range_min; /* sensor_msgs/LaserScan fields */
+  double max_range;       /* the functions' max_range argument                      */
+  int32_t variant;        /* 0: nautilus (angle = min + inc * index); 1: csm
+                             (angle accumulated in float, glancing filter)           */
+  int32_t truncate_ends;  /* csm variant: drop pi/12 at either end                   */
+} NautilusLaserSpec;
+
+/* Converts n_scans scans of n_beams ranges each (row-major) and makes the
+ * resulting clouds the handle's scan set, exactly as if they had been passed to
+ * nautilus_csm_upload_scans (scan ids 0..n_scans-1). */
+int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_scans,
+                               int32_t n_beams, const NautilusLaserSpec* spec);
+/* Reads the resident scan set back: offsets[n_scans + 1] and, when xy is not NULL,
+ * the points (cap_points >= offsets[n_scans]). */
+int nautilus_csm_download_scans(NautilusCsm* h, float* xy, int64_t cap_points, int64_t* offsets);
+/* ComputeScatterMatrixScore of every resident scan (min / max eigenvalue of the
+ * scatter matrix; float sums in point order like the reference). */
+int nautilus_lc_scatter_scores(NautilusCsm* h, double* score);
+/* GetLCCandidates: sequential keyframe selection over the scores (host; the
+ * reference's constants are min_dist = 5, min_score = 0.70).  pose_xy = n x 2
+ * floats (GetPoseTranslation).  out has room for n indices. */
+int nautilus_lc_candidates(const double* score, const float* pose_xy, int32_t n, double min_dist,
+                           double min_score, int64_t* out, int32_t* n_out);
+
 /* --- point-to-point matching -------------------------------------------------
  * The nearest-neighbour correspondence search that feeds the Ceres residuals:
  *   Solver::GetPointToPointMatching   (src/optimization/solver.cc:132-172)

@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
-SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu"]
+SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu"]
 HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
@@ -35,6 +35,12 @@ class Params(C.Structure):
                 ("rot_step", C.c_double), ("blur_sigma", C.c_double),
                 ("device", C.c_int32), ("margin_cells", C.c_int32),
                 ("max_tables", C.c_int32), ("stage_cells", C.c_int32)]
+
+
+class LaserSpec(C.Structure):
+    _fields_ = [("angle_min", C.c_float), ("angle_max", C.c_float), ("angle_increment", C.c_float),
+                ("range_min", C.c_float), ("max_range", C.c_double), ("variant", C.c_int32),
+                ("truncate_ends", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -56,6 +62,8 @@ EXPORTS = [
     "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_regular_check",
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
+    "nautilus_csm_upload_ranges", "nautilus_csm_download_scans", "nautilus_lc_scatter_scores",
+    "nautilus_lc_candidates",
 ]
 
 
@@ -128,6 +136,10 @@ def lib():
     L.nautilus_nn_match_batch.argtypes = [vp, vp, vp, vp, d, i32, vp, vp, vp]
     L.nautilus_nn_self_index.argtypes = [vp, vp]
     L.nautilus_nn_last_stats.argtypes = [vp, C.POINTER(f), C.POINTER(u64)]
+    L.nautilus_csm_upload_ranges.argtypes = [vp, vp, i32, i32, C.POINTER(LaserSpec)]
+    L.nautilus_csm_download_scans.argtypes = [vp, vp, i64, vp]
+    L.nautilus_lc_scatter_scores.argtypes = [vp, vp]
+    L.nautilus_lc_candidates.argtypes = [vp, vp, i32, d, d, vp, C.POINTER(i32)]
     _lib = L
     return L
 

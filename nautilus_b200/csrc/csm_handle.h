@@ -94,6 +94,11 @@ struct DevBuf {
 
 }  // namespace csmh
 
+struct NautilusCsm;
+// frontend.cu: makes ScanSet::host_xy of the user scans valid (D2H when the clouds
+// were produced on the device)
+int nautilus_internal_host_xy(NautilusCsm* h);
+
 // internal header: the handle is written in terms of the two namespaces above
 using namespace csm;
 using namespace csmh;

@@ -186,6 +186,10 @@ int nautilus_nn_build(NautilusCsm* h, double cell_size) {
   NnState& nn = h->nn;
   nn.release();
   const long long total = ss.host_offsets[ss.n];
+  {  // clouds converted on the device (nautilus_csm_upload_ranges) are fetched once
+    const int rc_xy = nautilus_internal_host_xy(h);
+    if (rc_xy) return rc_xy;
+  }
   const float* xy_host = ss.host_xy.data();
   int max_pts = 0;
   for (int s = 0; s < ss.n; ++s)

@@ -201,6 +201,53 @@ class CorrelativeScanMatcher:
         self.n_scans = len(offsets) - 1
         self._scan_sizes = (offsets[1:] - offsets[:-1]).astype(np.int64)
 
+    # ---- front end (include/nautilus_csm.h, "front end") -----------------------
+    def upload_ranges(self, ranges, angle_min: float, angle_max: float, angle_increment: float,
+                      range_min: float, max_range: float, *, variant: int = 0,
+                      truncate_ends: bool = False) -> None:
+        """LaserScanToPointCloud for a batch of scans (rows of `ranges`) on the device;
+        the clouds become the resident scan set.  variant 0:
+        src/input/pointcloud_helpers.cc:28-48, variant 1 (csm, glancing filter):
+        third_party/csm/src/pointcloud_helpers.cc:21-66."""
+        r = np.ascontiguousarray(ranges, dtype=np.float32)
+        if r.ndim != 2:
+            raise ValueError("ranges must be [n_scans, n_beams]")
+        spec = _lib.LaserSpec(angle_min, angle_max, angle_increment, range_min, max_range,
+                              int(variant), int(bool(truncate_ends)))
+        check(self._L.nautilus_csm_upload_ranges(self._h, ptr(r), r.shape[0], r.shape[1],
+                                                 C.byref(spec)))
+        self.n_scans = r.shape[0]
+        offs = np.zeros(self.n_scans + 1, np.int64)
+        check(self._L.nautilus_csm_download_scans(self._h, None, 0, ptr(offs)))
+        self._scan_sizes = (offs[1:] - offs[:-1]).astype(np.int64)
+
+    def download_scans(self):
+        """(xy float32 [n, 2], offsets int64 [n_scans + 1]) of the resident scan set."""
+        offs = np.zeros(self.n_scans + 1, np.int64)
+        check(self._L.nautilus_csm_download_scans(self._h, None, 0, ptr(offs)))
+        xy = np.empty((int(offs[-1]), 2), np.float32)
+        check(self._L.nautilus_csm_download_scans(self._h, ptr(xy), len(xy), ptr(offs)))
+        return xy, offs
+
+    def scatter_scores(self) -> np.ndarray:
+        """ComputeScatterMatrixScore (lc_candidate_filter.cc:34-52) of every resident scan."""
+        out = np.empty(self.n_scans, np.float64)
+        check(self._L.nautilus_lc_scatter_scores(self._h, ptr(out)))
+        return out
+
+    def GetLCCandidates(self, pose_xy, *, min_dist: float = 5.0, min_score: float = 0.70):
+        """LCCandidateFilter::GetLCCandidates (lc_candidate_filter.cc:66-81) over the
+        resident scans: device scatter scores + the reference's sequential selection."""
+        pose_xy = np.ascontiguousarray(pose_xy, np.float32).reshape(-1, 2)
+        if len(pose_xy) != self.n_scans:
+            raise ValueError("one pose per resident scan")
+        score = self.scatter_scores()
+        out = np.empty(self.n_scans, np.int64)
+        n = C.c_int32()
+        check(self._L.nautilus_lc_candidates(ptr(score), ptr(pose_xy), self.n_scans, min_dist,
+                                             min_score, ptr(out), C.byref(n)))
+        return out[:n.value].copy()
+
     def match_batch(self, a_ids, b_ids, rot_min, rot_max, *, with_stats: bool = False):
         a_ids = np.ascontiguousarray(a_ids, dtype=np.int32)
         b_ids = np.ascontiguousarray(b_ids, dtype=np.int32)

@@ -56,6 +56,9 @@ def lib():
     L.ref_lowres_from_table.argtypes = [d, d, d, d, vp]
     L.ref_highres_table.restype = vp
     L.ref_highres_table.argtypes = [d, d, d, d, _f32p, i64]
+    if hasattr(L, "ref_csm_laser_to_points"):  # front end (ref_frontend_wrap.cc)
+        L.ref_csm_laser_to_points.restype = i64
+        L.ref_csm_laser_to_points.argtypes = [_f32p, i64, f, f, f, f, d, C.c_int, _f32p]
     if hasattr(L, "ref_kd_new"):  # KD-tree part (ref_nn_wrap.cc)
         L.ref_kd_new.restype = vp
         L.ref_kd_new.argtypes = [_f32p, i64]
@@ -248,3 +251,14 @@ def nn_match_batch(xy, offsets, src_ids, tgt_ids, transforms, threshold, threads
                                 dist.ctypes.data_as(C.c_void_p) if with_dist else None,
                                 threads or max_threads())
     return (secs, idx, out_off, dist) if with_dist else (secs, idx, out_off)
+
+
+def csm_laser_to_points(ranges, angle_min, angle_max, angle_increment, range_min, max_range,
+                        truncate_ends=False):
+    """The reference's pointcloud_helpers::LaserScanToPointCloud
+    (third_party/csm/src/pointcloud_helpers.cc:44-66), compiled unchanged."""
+    r = np.ascontiguousarray(ranges, np.float32)
+    out = np.zeros((len(r), 2), np.float32)
+    n = lib().ref_csm_laser_to_points(r, len(r), angle_min, angle_max, angle_increment, range_min,
+                                      max_range, int(bool(truncate_ends)), out.reshape(-1))
+    return out[:n].copy()
