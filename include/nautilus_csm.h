@@ -207,6 +207,27 @@ int nautilus_lc_scatter_scores(NautilusCsm* h, double* score);
 int nautilus_lc_candidates(const double* score, const float* pose_xy, int32_t n, double min_dist,
                            double min_score, int64_t* out, int32_t* n_out);
 
+/* --- residual blocks ------------------------------------------------------------
+ * The step after the point-to-point matching: the lidar residual functors that
+ * Solver::AddLidarResiduals hands to Ceres (src/optimization/solver.cc:275-296),
+ *   LIDARPointResidual  (src/optimization/slam_residuals.h:123-145)  kind 0
+ *   LIDARNormalResidual (src/optimization/slam_residuals.h:64-90)    kind 1
+ * evaluated for a batch of residual blocks with analytic Jacobians -- the values
+ * ceres::AutoDiffCostFunction<..., DYNAMIC, 3, 3> computes by automatic
+ * differentiation.  Block b owns correspondences [offsets[b], offsets[b+1]) of the
+ * four parallel float (x, y) arrays (PointCorrespondences, data_structures.h:62-100)
+ * and the poses source_poses[3b..], target_poses[3b..] = (x, y, theta).
+ * residuals: 2 doubles per correspondence.  jac_source / jac_target (optional):
+ * per correspondence 2 rows x 3 columns, row-major, i.e. a block's slice is Ceres'
+ * jacobians[0] / jacobians[1] of that block. */
+int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const double* source_poses,
+                            const double* target_poses, const int64_t* offsets, int32_t n_blocks,
+                            const float* source_points, const float* target_points,
+                            const float* source_normals, const float* target_normals,
+                            double* residuals, double* jac_source, double* jac_target);
+/* Device time of the last nautilus_residuals_eval kernel (CUDA events). */
+int nautilus_residuals_last_ms(const NautilusCsm* h, float* kernel_ms);
+
 /* --- point-to-point matching -------------------------------------------------
  * The nearest-neighbour correspondence search that feeds the Ceres residuals:
  *   Solver::GetPointToPointMatching   (src/optimization/solver.cc:132-172)

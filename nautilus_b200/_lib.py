@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
-SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu"]
+SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu", "residuals.cu"]
 HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
@@ -63,7 +63,7 @@ EXPORTS = [
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_csm_upload_ranges", "nautilus_csm_download_scans", "nautilus_lc_scatter_scores",
-    "nautilus_lc_candidates",
+    "nautilus_lc_candidates", "nautilus_residuals_eval", "nautilus_residuals_last_ms",
 ]
 
 
@@ -140,6 +140,8 @@ def lib():
     L.nautilus_csm_download_scans.argtypes = [vp, vp, i64, vp]
     L.nautilus_lc_scatter_scores.argtypes = [vp, vp]
     L.nautilus_lc_candidates.argtypes = [vp, vp, i32, d, d, vp, C.POINTER(i32)]
+    L.nautilus_residuals_eval.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp]
+    L.nautilus_residuals_last_ms.argtypes = [vp, C.POINTER(f)]
     _lib = L
     return L
 

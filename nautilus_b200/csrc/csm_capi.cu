@@ -511,6 +511,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->user_scans.release(); h->tmp_scans.release();
   h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();
   h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
+  h->residual_arena.release();
   h->spec_pairs_dev.release(); h->spec_items_dev.release(); h->spec_out_dev.release(); h->spec_counters_dev.release();
   for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
   if (h->table_stream) cudaStreamDestroy(h->table_stream);

@@ -157,6 +157,10 @@ struct NautilusCsm {
   NautilusCsmTimings timings{};
   int last_n_pairs = 0;
 
+  // residual evaluation (residuals.cu)
+  DevBuf<unsigned char> residual_arena;
+  float residual_kernel_ms = 0.f;
+
   // nearest-neighbour matching (nn_capi.cu)
   csmh::NnState nn;
 };

@@ -1,0 +1,163 @@
+// Batched evaluation of the lidar residual blocks that follow the point-to-point
+// matching, with analytic Jacobians, on sm_100a.  Replaces
+//   LIDARNormalResidual::operator()  src/optimization/slam_residuals.h:64-90
+//   LIDARPointResidual::operator()   src/optimization/slam_residuals.h:123-145
+//   PoseArrayToAffine                src/util/slam_util.h:20-28
+// evaluated by ceres::AutoDiffCostFunction<..., DYNAMIC, 3, 3> (slam_residuals.h:104-113,
+// 159-168): residuals[2k], residuals[2k+1] per correspondence k, jacobians[0] /
+// jacobians[1] row-major [2 n][3] with respect to the source / target pose (x, y, theta).
+//
+//   source_to_target = (T(t_t) R(th_t))^-1 * (T(t_s) R(th_s))
+//   p' = R(th_t)^T (R(th_s) p + t_s - t_t)
+//   dp'/dt_s = R(th_t)^T      dp'/dth_s = R(th_t)^T J R(th_s) p      (J = [[0,-1],[1,0]])
+//   dp'/dt_t = -R(th_t)^T     dp'/dth_t = -J p'
+// One thread per correspondence; HBM-bound streaming (32 B in, 16 + 96 B out).
+#include "csm_handle.h"
+
+namespace csm {
+
+struct ResidualArgs {
+  const double* src_pose;   // [n_blocks][3]
+  const double* tgt_pose;   // [n_blocks][3]
+  const long long* offsets; // [n_blocks + 1]
+  int n_blocks;
+  const float2 *sp, *tp, *sn, *tn;  // [n_corr]
+  double* res;              // [n_corr][2]
+  double* jac_s;            // [n_corr][2][3] or null
+  double* jac_t;
+  int kind;                 // 0: point residual, 1: normal residual
+};
+
+__global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long n_corr) {
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_corr) return;
+  // residual block of this correspondence: last b with offsets[b] <= k
+  int lo = 0, hi = a.n_blocks;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (a.offsets[mid] <= k) lo = mid; else hi = mid;
+  }
+  const double xs = a.src_pose[3 * lo], ys = a.src_pose[3 * lo + 1], ths = a.src_pose[3 * lo + 2];
+  const double xt = a.tgt_pose[3 * lo], yt = a.tgt_pose[3 * lo + 1], tht = a.tgt_pose[3 * lo + 2];
+  double ss, cs, st, ct;
+  sincos(ths, &ss, &cs);
+  sincos(tht, &st, &ct);
+  const float2 pf = a.sp[k], qf = a.tp[k];
+  const double px = pf.x, py = pf.y, qx = qf.x, qy = qf.y;
+  // w = R(th_s) p + t_s - t_t (world frame, relative to the target origin)
+  const double rx = cs * px - ss * py, ry = ss * px + cs * py;
+  const double wx = rx + xs - xt, wy = ry + ys - yt;
+  // p' = R(th_t)^T w
+  const double ppx = ct * wx + st * wy, ppy = -st * wx + ct * wy;
+  // d p' / d (x_s, y_s, th_s, x_t, y_t, th_t), rows = p'_x, p'_y
+  const double jrx = -ry, jry = rx;  // J R(th_s) p
+  double dx[6], dy[6];
+  dx[0] = ct;  dy[0] = -st;
+  dx[1] = st;  dy[1] = ct;
+  dx[2] = ct * jrx + st * jry;  dy[2] = -st * jrx + ct * jry;
+  dx[3] = -ct; dy[3] = st;
+  dx[4] = -st; dy[4] = -ct;
+  dx[5] = ppy; dy[5] = -ppx;      // -J p'
+  double r0, r1, g0[6], g1[6];
+  if (a.kind == 0) {              // difference_in_target = target - source'
+    r0 = qx - ppx; r1 = qy - ppy;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) { g0[c] = -dx[c]; g1[c] = -dy[c]; }
+  } else {                        // n_t . (p' - q),  n_s . (q - p')
+    const float2 nsf = a.sn[k], ntf = a.tn[k];
+    const double nsx = nsf.x, nsy = nsf.y, ntx = ntf.x, nty = ntf.y;
+    r0 = ntx * (ppx - qx) + nty * (ppy - qy);
+    r1 = nsx * (qx - ppx) + nsy * (qy - ppy);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      g0[c] = ntx * dx[c] + nty * dy[c];
+      g1[c] = -(nsx * dx[c] + nsy * dy[c]);
+    }
+  }
+  reinterpret_cast<double2*>(a.res)[k] = make_double2(r0, r1);
+  if (a.jac_s) {
+    double* j = a.jac_s + 6 * k;
+    j[0] = g0[0]; j[1] = g0[1]; j[2] = g0[2]; j[3] = g1[0]; j[4] = g1[1]; j[5] = g1[2];
+  }
+  if (a.jac_t) {
+    double* j = a.jac_t + 6 * k;
+    j[0] = g0[3]; j[1] = g0[4]; j[2] = g0[5]; j[3] = g1[3]; j[4] = g1[4]; j[5] = g1[5];
+  }
+}
+
+}  // namespace csm
+
+extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const double* source_poses,
+                                       const double* target_poses, const int64_t* offsets,
+                                       int32_t n_blocks, const float* source_points,
+                                       const float* target_points, const float* source_normals,
+                                       const float* target_normals, double* residuals,
+                                       double* jac_source, double* jac_target) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  if (kind != 0 && kind != 1) return fail(NAUTILUS_EINVAL, "kind must be 0 (point) or 1 (normal)");
+  if (n_blocks < 0) return fail(NAUTILUS_EINVAL, "n_blocks < 0");
+  if (n_blocks == 0) return NAUTILUS_OK;
+  if (!source_poses || !target_poses || !offsets || !residuals)
+    return fail(NAUTILUS_EINVAL, "null argument");
+  if (offsets[0] != 0) return fail(NAUTILUS_EINVAL, "offsets[0] must be 0");
+  for (int b = 0; b < n_blocks; ++b)
+    if (offsets[b + 1] < offsets[b]) return fail(NAUTILUS_EINVAL, "offsets must be non-decreasing");
+  const long long n = offsets[n_blocks];
+  if (n == 0) return NAUTILUS_OK;
+  if (!source_points || !target_points || (kind == 1 && (!source_normals || !target_normals)))
+    return fail(NAUTILUS_EINVAL, "null correspondence array");
+  CU_TRY(cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  // one device arena per call: poses | offsets | 4 float2 arrays | residuals | jacobians
+  const size_t b_pose = sizeof(double) * 3 * (size_t)n_blocks;
+  const size_t b_off = sizeof(long long) * ((size_t)n_blocks + 1);
+  const size_t b_pts = sizeof(float2) * (size_t)n;
+  const size_t b_res = sizeof(double) * 2 * (size_t)n;
+  const size_t b_jac = sizeof(double) * 6 * (size_t)n;
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const size_t total = 2 * up(b_pose) + up(b_off) + 4 * up(b_pts) + up(b_res) + 2 * up(b_jac);
+  int rc = h->residual_arena.reserve(total);
+  if (rc) return rc;
+  unsigned char* base = h->residual_arena.p;
+  size_t at = 0;
+  auto take = [&](size_t bytes) { unsigned char* p = base + at; at += up(bytes); return p; };
+  csm::ResidualArgs a;
+  double* d_sp = (double*)take(b_pose); double* d_tp = (double*)take(b_pose);
+  long long* d_off = (long long*)take(b_off);
+  float2* d_p = (float2*)take(b_pts); float2* d_q = (float2*)take(b_pts);
+  float2* d_ns = (float2*)take(b_pts); float2* d_nt = (float2*)take(b_pts);
+  double* d_res = (double*)take(b_res);
+  double* d_js = (double*)take(b_jac); double* d_jt = (double*)take(b_jac);
+  CU_TRY(cudaMemcpyAsync(d_sp, source_poses, b_pose, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_tp, target_poses, b_pose, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_off, offsets, b_off, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_p, source_points, b_pts, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_q, target_points, b_pts, cudaMemcpyHostToDevice, st));
+  if (kind == 1) {
+    CU_TRY(cudaMemcpyAsync(d_ns, source_normals, b_pts, cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(d_nt, target_normals, b_pts, cudaMemcpyHostToDevice, st));
+  }
+  a.src_pose = d_sp; a.tgt_pose = d_tp; a.offsets = d_off; a.n_blocks = n_blocks;
+  a.sp = d_p; a.tp = d_q; a.sn = d_ns; a.tn = d_nt;
+  a.res = d_res; a.jac_s = jac_source ? d_js : nullptr; a.jac_t = jac_target ? d_jt : nullptr;
+  a.kind = kind;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  csm::residual_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, n);
+  cudaEventRecord(e1, st);
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(residuals, d_res, b_res, cudaMemcpyDeviceToHost, st));
+  if (jac_source) CU_TRY(cudaMemcpyAsync(jac_source, d_js, b_jac, cudaMemcpyDeviceToHost, st));
+  if (jac_target) CU_TRY(cudaMemcpyAsync(jac_target, d_jt, b_jac, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&h->residual_kernel_ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return NAUTILUS_OK;
+}
+
+extern "C" int nautilus_residuals_last_ms(const NautilusCsm* h, float* kernel_ms) {
+  if (!h || !kernel_ms) return fail(NAUTILUS_EINVAL, "null argument");
+  *kernel_ms = h->residual_kernel_ms;
+  return NAUTILUS_OK;
+}
