@@ -328,8 +328,10 @@ def run_ours(args):
     kernels = {
         "low_score_kernel": {"ms_per_step": acc["low"] / args.steps,
                              "share": acc["low"] / (acc["tables"] + acc["low"] + acc["refine"])},
-        "refine_kernel": {"ms_per_step": acc["refine"] / args.steps,
-                          "share": acc["refine"] / (acc["tables"] + acc["low"] + acc["refine"])},
+        "refine_kernels": {"ms_per_step": acc["refine"] / args.steps,
+                           "share": acc["refine"] / (acc["tables"] + acc["low"] + acc["refine"]),
+                           "kernels": "refine_first + refine_spec + refine_finish",
+                           "speculative_windows_per_step": m.last_timings()["spec_windows"]},
         "table_kernels": {"ms_per_step": acc["tables"] / args.steps,
                           "share": acc["tables"] / (acc["tables"] + acc["low"] + acc["refine"]),
                           "algorithmic_GBps": table_bytes / (acc["tables"] * 1e-3) / 1e9,

@@ -195,6 +195,9 @@ typedef struct NautilusLaserSpec {
  * nautilus_csm_upload_scans (scan ids 0..n_scans-1). */
 int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_scans,
                                int32_t n_beams, const NautilusLaserSpec* spec);
+/* Device time of the kernels of the last nautilus_csm_upload_ranges (CUDA events:
+ * count pass + offsets + write pass). */
+int nautilus_csm_frontend_last_ms(const NautilusCsm* h, float* kernel_ms);
 /* Reads the resident scan set back: offsets[n_scans + 1] and, when xy is not NULL,
  * the points (cap_points >= offsets[n_scans]). */
 int nautilus_csm_download_scans(NautilusCsm* h, float* xy, int64_t cap_points, int64_t* offsets);

@@ -63,7 +63,7 @@ EXPORTS = [
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_csm_upload_ranges", "nautilus_csm_download_scans", "nautilus_lc_scatter_scores",
-    "nautilus_lc_candidates", "nautilus_residuals_eval", "nautilus_residuals_last_ms",
+    "nautilus_lc_candidates", "nautilus_csm_frontend_last_ms", "nautilus_residuals_eval", "nautilus_residuals_last_ms",
 ]
 
 
@@ -142,6 +142,7 @@ def lib():
     L.nautilus_lc_candidates.argtypes = [vp, vp, i32, d, d, vp, C.POINTER(i32)]
     L.nautilus_residuals_eval.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp]
     L.nautilus_residuals_last_ms.argtypes = [vp, C.POINTER(f)]
+    L.nautilus_csm_frontend_last_ms.argtypes = [vp, C.POINTER(f)]
     _lib = L
     return L
 

@@ -160,6 +160,7 @@ struct NautilusCsm {
   // residual evaluation (residuals.cu)
   DevBuf<unsigned char> residual_arena;
   float residual_kernel_ms = 0.f;
+  float frontend_kernel_ms = 0.f;  // last nautilus_csm_upload_ranges: count + write passes
 
   // nearest-neighbour matching (nn_capi.cu)
   csmh::NnState nn;

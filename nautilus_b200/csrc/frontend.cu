@@ -273,20 +273,31 @@ int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_sc
       cudaFuncSetAttribute(ranges_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       cudaFuncSetAttribute(ranges_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     }
+    cudaEvent_t e0, e1, e2, e3;
+    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2); cudaEventCreate(&e3);
+    cudaEventRecord(e0, st);
     ranges_kernel<false><<<n_scans, FE_THREADS, smem, st>>>(ranges_dev, n_beams, beams_dev,
                                                             spec->range_min, spec->max_range,
                                                             spec->variant, counts_dev, nullptr, nullptr);
     offsets_kernel<<<1, 1024, 0, st>>>(counts_dev, n_scans, ss.offsets);
+    cudaEventRecord(e1, st);
     FE_TRY(cudaMemcpyAsync(ss.host_offsets.data(), ss.offsets, sizeof(long long) * (n_scans + 1),
                            cudaMemcpyDeviceToHost, st));
     FE_TRY(cudaStreamSynchronize(st));
     const long long total = ss.host_offsets[n_scans];
     if ((rc = ensure_scan_capacity(ss, (size_t)total, n_scans))) { cleanup(); return rc; }
+    cudaEventRecord(e2, st);
     ranges_kernel<true><<<n_scans, FE_THREADS, smem, st>>>(ranges_dev, n_beams, beams_dev,
                                                            spec->range_min, spec->max_range,
                                                            spec->variant, nullptr, ss.offsets, ss.points);
+    cudaEventRecord(e3, st);
     FE_TRY(cudaGetLastError());
     FE_TRY(cudaStreamSynchronize(st));
+    float ta = 0.f, tb = 0.f;
+    cudaEventElapsedTime(&ta, e0, e1);
+    cudaEventElapsedTime(&tb, e2, e3);
+    h->frontend_kernel_ms = ta + tb;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
   } else {
     FE_TRY(cudaMemsetAsync(ss.offsets, 0, sizeof(long long), st));
     FE_TRY(cudaStreamSynchronize(st));
@@ -294,6 +305,12 @@ int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_sc
 #undef FE_TRY
   cleanup();
   ss.n = n_scans;
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_frontend_last_ms(const NautilusCsm* h, float* kernel_ms) {
+  if (!h || !kernel_ms) return fail(NAUTILUS_EINVAL, "null argument");
+  *kernel_ms = h->frontend_kernel_ms;
   return NAUTILUS_OK;
 }
 

@@ -221,6 +221,11 @@ class CorrelativeScanMatcher:
         check(self._L.nautilus_csm_download_scans(self._h, None, 0, ptr(offs)))
         self._scan_sizes = (offs[1:] - offs[:-1]).astype(np.int64)
 
+    def frontend_last_ms(self) -> float:
+        ms = C.c_float()
+        check(self._L.nautilus_csm_frontend_last_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
     def download_scans(self):
         """(xy float32 [n, 2], offsets int64 [n_scans + 1]) of the resident scan set."""
         offs = np.zeros(self.n_scans + 1, np.int64)

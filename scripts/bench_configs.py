@@ -4,7 +4,7 @@ point-to-point NN path (configs[4]).  One JSON line per config, CUDA-event times
 from the library, the reference's CPU code (oracle/_ref) timed beside it on a
 bounded sample.  Usage (on a B200):
 
-  python scripts/bench_configs.py [tables] [wide] [nn] [--cpu]
+  python scripts/bench_configs.py [tables] [wide] [nn] [frontend] [residuals] [--cpu]
 """
 import json
 import os
@@ -148,12 +148,103 @@ def bench_nn(cpu):
     return line
 
 
+def bench_frontend(cpu):
+    from nautilus_b200 import synth_ranges as sr
+    n = 20000                                        # BASELINE configs[4]: a 20k-pose trajectory
+    r = sr.make_ranges(n, seed=1)
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    lines = []
+    for variant, name in ((0, "nautilus::LaserScanToPointCloud"), (1, "csm LaserScanToPointCloud + FilterGlancing")):
+        ms, walls = [], []
+        for _ in range(4):
+            t0 = time.perf_counter()
+            m.upload_ranges(r, sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC, sr.RANGE_MIN, sr.MAX_RANGE,
+                            variant=variant)
+            walls.append(time.perf_counter() - t0)
+            ms.append(m.frontend_last_ms())
+        t = float(np.median(ms[1:])) * 1e-3
+        n_pts = int(m._scan_sizes.sum())
+        # count pass reads the ranges, write pass reads them again and writes the points
+        alg = 4.0 * r.size + 8.0 * n_pts
+        line = {"config": f"front end: {name}, {n} scans x {r.shape[1]} beams",
+                "metric": "scans_per_sec", "value": n / t, "ms_kernels": t * 1e3,
+                "ms_wall_with_h2d": float(np.median(walls[1:])) * 1e3, "points_out": n_pts,
+                "roofline": {"bound": "hbm", "algorithmic_bytes_per_scan": alg / n,
+                             "achieved": alg / t / 1e9, "peak": PEAK, "unit": "GB/s",
+                             "frac": alg / t / 1e9 / PEAK}}
+        if cpu and variant == 1:
+            from oracle import ref
+            k = 2000
+            t0 = time.perf_counter()
+            tot = 0
+            for s in range(k):
+                tot += len(ref.csm_laser_to_points(r[s], sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC,
+                                                   sr.RANGE_MIN, sr.MAX_RANGE, False))
+            secs = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": k / secs, "unit": "scans/s", "cores": 1, "kind": "reference",
+                                    "sample": f"{k} scans, one thread, {secs:.2f} s",
+                                    "counts_identical_to_gpu": bool(tot == int(m._scan_sizes[:k].sum()))}
+        lines.append(line)
+    t0 = time.perf_counter()
+    sc = m.scatter_scores()
+    lines.append({"config": f"LC candidate filter: scatter score of {n} scans", "metric": "scans_per_sec",
+                  "value": n / (time.perf_counter() - t0), "note": "wall time incl. D2H of the scores",
+                  "frac_above_0.70": float((sc >= 0.70).mean())})
+    m.close()
+    return lines
+
+
+def bench_residuals(cpu):
+    from nautilus_b200.residuals import evaluate_residual_blocks, last_kernel_ms
+    rng = np.random.default_rng(0)
+    nb, per = 20000, 800                              # 1.6e7 correspondences
+    offs = np.arange(nb + 1, dtype=np.int64) * per
+    sp = rng.uniform(-20, 20, size=(nb, 3))
+    tp = sp + rng.normal(0, 0.2, size=(nb, 3))
+    p = rng.uniform(-25, 25, size=(nb * per, 2)).astype(np.float32)
+    q = (p + rng.normal(0, 0.1, size=p.shape)).astype(np.float32)
+    a = rng.uniform(-np.pi, np.pi, size=(2, nb * per))
+    ns = np.stack([np.cos(a[0]), np.sin(a[0])], 1).astype(np.float32)
+    nt = np.stack([np.cos(a[1]), np.sin(a[1])], 1).astype(np.float32)
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    lines = []
+    for kind, name in ((0, "LIDARPointResidual"), (1, "LIDARNormalResidual")):
+        ms, walls = [], []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            evaluate_residual_blocks(m, kind, sp, tp, offs, p, q, ns, nt)
+            walls.append(time.perf_counter() - t0)
+            ms.append(last_kernel_ms(m))
+        t = float(np.median(ms)) * 1e-3
+        n = nb * per
+        alg = n * ((16 if kind == 0 else 32) + 16 + 96.0)
+        line = {"config": f"residual blocks: {name}, {nb} blocks x {per} correspondences, residuals + both Jacobians",
+                "metric": "correspondences_per_sec", "value": n / t, "ms_kernel": t * 1e3,
+                "ms_wall_with_copies": float(np.median(walls)) * 1e3,
+                "roofline": {"bound": "hbm", "algorithmic_bytes_per_correspondence": alg / n,
+                             "achieved": alg / t / 1e9, "peak": PEAK, "unit": "GB/s",
+                             "frac": alg / t / 1e9 / PEAK}}
+        if cpu:
+            from oracle import residual_port as rp
+            k = 200
+            t0 = time.perf_counter()
+            rp.evaluate(kind, sp[:k], tp[:k], offs[:k + 1], p[:k * per], q[:k * per], ns[:k * per], nt[:k * per])
+            secs = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": k * per / secs, "unit": "correspondences/s", "cores": 1,
+                                    "kind": "port", "sample": f"{k} blocks, numpy dual numbers, {secs:.2f} s"}
+        lines.append(line)
+    m.close()
+    return lines
+
+
 def main():
-    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "nn"]
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "nn", "frontend", "residuals"]
     cpu = "--cpu" in sys.argv
     for w in which:
-        line = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn}[w](cpu)
-        print(json.dumps(line), flush=True)
+        out = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn,
+               "frontend": bench_frontend, "residuals": bench_residuals}[w](cpu)
+        for line in (out if isinstance(out, list) else [out]):
+            print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
