@@ -36,7 +36,7 @@ UNIT = "candidates/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scans", type=int, default=N_SCANS)
@@ -64,55 +64,68 @@ def make_batch(n_scans, seed):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region (NVML in a
+    thread, every 20 ms; NVML is initialised before the warm-up so that its start-up
+    does not fall into the timed region).  Falls back to one nvidia-smi query."""
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+               "sw_power_cap": 0x4}
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.samples, self.run, self.t, self.h = index, [], False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+
+    def _loop(self):
+        nv = self.nv
+        while self.run:
+            try:
+                self.samples.append((float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)),
+                                     int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                                     if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons")
+                                     else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))))
+            except Exception:
+                pass
+            time.sleep(0.02)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+        if self.h is None:
+            return
+        self.samples, self.run = [], True
+        self.t = threading.Thread(target=self._loop, daemon=True)
+        self.t.start()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
+        if self.h is None:
+            return self._smi_once()
+        self.run = False
+        self.t.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_sm, "reasons": ["no samples"]}
+        sm = sorted(v for v, _ in self.samples)
+        bits = 0
+        for _, r in self.samples:
+            bits |= r
+        reasons = sorted(k for k, b in self.REASONS.items() if bits & b)
+        busy = sm[len(sm) // 2:]  # upper half = samples under load
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": self.max_sm, "reasons": reasons,
+                "samples": len(sm), "source": "nvml"}
+
+    def _smi_once(self):
         try:
-            self.proc.wait(timeout=5)
+            out = subprocess.run(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
+                 "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=20).stdout
+            f = [float(v) for v in out.strip().split(",")]
+            return {"sm_mhz": f[0], "sm_max_mhz": f[1], "reasons": [], "samples": 1,
+                    "source": "nvidia-smi after the timed region (NVML unavailable)"}
         except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [v.strip() for v in ln.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        busy = sorted(sm)[len(sm) // 2:]  # upper half = samples under load
-        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)),
-                "reasons": sorted(reasons), "samples": len(sm)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
 
 
 def ncu_traffic_bytes(kernel):
@@ -293,9 +306,9 @@ def run_ours(args):
         return ms, wall_ms, acc, (score, x, y, th, st)
 
     m.upload_scans(xy_host, offs)
+    sampler = ClockSampler(local)   # NVML start-up happens before the warm-up
     for _ in range(args.warmup):
         step(False)
-    sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms, _, acc, last = timed(False, args.steps)          # inputs resident in HBM

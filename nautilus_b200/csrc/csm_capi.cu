@@ -539,8 +539,9 @@ int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* of
   h->nn.built = false;  // the NN index belongs to the previous scan set
   int rc = upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
   if (rc) return rc;
-  const long long total = n_scans > 0 ? offsets[n_scans] : 0;
-  h->user_scans.host_xy.assign(xy, xy + 2 * total);
+  // the host copy the NN path needs for its KD-tree layout is fetched from the
+  // device when nautilus_nn_build asks for it (nautilus_internal_host_xy)
+  h->user_scans.host_xy.clear();
   return NAUTILUS_OK;
 }
 
