@@ -293,30 +293,54 @@ __global__ void __launch_bounds__(NM_THREADS) nn_match_kernel(
     q.x = __fadd_rn(__fadd_rn(__fmul_rn(pr.m[0], p.x), __fmul_rn(pr.m[1], p.y)), pr.m[2]);
     q.y = __fadd_rn(__fadd_rn(__fmul_rn(pr.m[3], p.x), __fmul_rn(pr.m[4], p.y)), pr.m[5]);
     int best_i = -1;
-    float best = FLT_MAX, best_ax = 0.f, best_ay = 0.f;
-    bool tie = false;
+    float best2 = FLT_MAX, second2 = FLT_MAX, best_ax = 0.f, best_ay = 0.f;
     if (n_tgt > 0) {
       const int cx = nn_cell(q.x, ix.inv_cell), cy = nn_cell(q.y, ix.inv_cell);
+      // Squared distances in the loop (sqrt is monotone: the smallest square has the
+      // smallest float distance; only the runner-up can tie with it after rounding).
+      // Cells are probed centre first; a neighbour cell whose nearest edge is farther
+      // than min(best, threshold) cannot hold the answer or a tie and is skipped
+      // (margin 3e-6 relative on the squares: float rounding of dx, dy and the sum is
+      // below 3e-7).  r2 = that radius squared, in double.
+      const double cell = 1.0 / ix.inv_cell;
+      const double gx0 = (double)q.x - (double)cx * cell, gx1 = (double)(cx + 1) * cell - (double)q.x;
+      const double gy0 = (double)q.y - (double)cy * cell, gy1 = (double)(cy + 1) * cell - (double)q.y;
+      double r2 = (double)thr_f * (double)thr_f;
       // (rolled on purpose: the unrolled 3 x 3 probe overflows the instruction cache)
+      // probe order: centre, edge neighbours, corners; 2-bit fields hold ox + 1 / oy + 1
+      constexpr unsigned OX = 1u | (0u << 2) | (2u << 4) | (1u << 6) | (1u << 8) | (0u << 10) | (2u << 12) | (0u << 14) | (2u << 16);
+      constexpr unsigned OY = 1u | (1u << 2) | (1u << 4) | (0u << 6) | (2u << 8) | (0u << 10) | (0u << 12) | (2u << 14) | (2u << 16);
 #pragma unroll 1
-      for (int oy = -1; oy <= 1; ++oy) {
-#pragma unroll 1
-        for (int ox = -1; ox <= 1; ++ox) {
-          const int b = nn_bucket(cx + ox, cy + oy, mask);
-          const int k1 = bs[b + 1];
-          for (int k = bs[b]; k < k1; ++k) {
-            const GridPoint g = tp[k];
-            const int dim = (unsigned)g.idx_dim >> 30, id = g.idx_dim & 0x3fffffff;
-            // a leaf the walk never reaches from this side of its parent
-            if (dim != 0 && (dim == 1 ? q.x : q.y) > g.skip_val) continue;
-            float ax, ay;
-            const float d = nn_dist(g.x, g.y, q, &ax, &ay);
-            if (d < best) { best = d; best_i = id; best_ax = ax; best_ay = ay; tie = false; }
-            else if (d == best && id != best_i) tie = true;
+      for (int pk = 0; pk < 9; ++pk) {
+        const int ox = (int)((OX >> (2 * pk)) & 3u) - 1, oy = (int)((OY >> (2 * pk)) & 3u) - 1;
+        if (pk > 0) {
+          const double gx = ox < 0 ? gx0 : ox > 0 ? gx1 : 0.0;
+          const double gy = oy < 0 ? gy0 : oy > 0 ? gy1 : 0.0;
+          const double g = fmax(gx, gy);
+          if (g > 0.0 && g * g > r2 * 1.000003) continue;
+        }
+        const int b = nn_bucket(cx + ox, cy + oy, mask);
+        const int k1 = bs[b + 1];
+        for (int k = bs[b]; k < k1; ++k) {
+          const GridPoint g = tp[k];
+          const int dim = (unsigned)g.idx_dim >> 30, id = g.idx_dim & 0x3fffffff;
+          // a leaf the walk never reaches from this side of its parent
+          if (dim != 0 && (dim == 1 ? q.x : q.y) > g.skip_val) continue;
+          const float dx = __fsub_rn(g.x, q.x), dy = __fsub_rn(g.y, q.y);
+          const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+          if (d2 < best2) {
+            second2 = best2; best2 = d2; best_i = id;
+            best_ax = fabsf(dx); best_ay = fabsf(dy);
+            r2 = fmin(r2, (double)d2);
+          } else if (id != best_i && d2 < second2) {
+            second2 = d2;
           }
         }
       }
     }
+    // the reference's float distance of the winner, and whether the runner-up ties with it
+    const float best = best_i >= 0 ? __fsqrt_rn(best2) : FLT_MAX;
+    const bool tie = best_i >= 0 && second2 < FLT_MAX && __fsqrt_rn(second2) == best;
     int out = -1;
     float out_d = best;
     if (best_i >= 0) {
