@@ -144,7 +144,10 @@ def main():
         cand = int(res[4][:, 0].sum() + res[4][:, 1].sum())
         st["csm_all_candidates"] = {"pairs": int(len(a_ids)), "ms_wall": 1e3 * wall, "ms_device": tm["ms_total"],
                                     "candidates_per_sec": cand / (tm["ms_total"] * 1e-3),
-                                    "pairs_per_sec": len(a_ids) / (tm["ms_total"] * 1e-3)}
+                                    "pairs_per_sec": len(a_ids) / (tm["ms_total"] * 1e-3),
+                                    "ms_tables": tm["ms_tables"], "ms_low": tm["ms_low"], "ms_refine": tm["ms_refine"],
+                                    "speculative_windows": tm["spec_windows"], "mean_pops": float(res[4][:, 2].mean()),
+                                    "max_pops": int(res[4][:, 2].max())}
     else:
         st["csm_all_candidates"] = {"pairs": 0}
 
