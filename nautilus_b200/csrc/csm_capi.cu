@@ -675,11 +675,12 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   sb.chunk_rot = h->chunk_rot_dev.p;
   const char* rf_env = getenv("NAUTILUS_CSM_REFINE");
   const bool rf_serial = rf_env && !strcmp(rf_env, "serial");
+  sb.spec_cap = spec_cap_for(n_tr);
   sb.spec_pairs = nullptr; sb.spec_items = nullptr; sb.spec_out = nullptr; sb.spec_counters = nullptr;
   if (!rf_serial) {
     if ((rc = h->spec_pairs_dev.reserve(max_wave_pairs))) return rc;
-    if ((rc = h->spec_items_dev.reserve((size_t)max_wave_pairs * RF_SPEC_CAP))) return rc;
-    if ((rc = h->spec_out_dev.reserve((size_t)max_wave_pairs * RF_SPEC_CAP))) return rc;
+    if ((rc = h->spec_items_dev.reserve((size_t)max_wave_pairs * spec_cap_for(n_tr)))) return rc;
+    if ((rc = h->spec_out_dev.reserve((size_t)max_wave_pairs * spec_cap_for(n_tr)))) return rc;
     if ((rc = h->spec_counters_dev.reserve(2 * (size_t)n_waves))) return rc;
     sb.spec_pairs = h->spec_pairs_dev.p; sb.spec_items = h->spec_items_dev.p;
     sb.spec_out = h->spec_out_dev.p; sb.spec_counters = h->spec_counters_dev.p;

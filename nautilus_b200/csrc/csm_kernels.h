@@ -74,15 +74,19 @@ struct Rotation {
 // Speculative refinement (csm_search.cu, K6): state of a pair after its first
 // pop, one queue entry per hi-res window that the reference may still open, and
 // the window's result.
-#ifndef RF_SPEC_CAP_N
-#define RF_SPEC_CAP_N 96
+// Listed windows per pair: every slot but the first pop when the translation grid has
+// at most RF_SPEC_CAP_MAX + 1 slots (the reference's 14 x 14 grid: 195), else the pair
+// finishes serially beyond the cap.
+#ifndef RF_SPEC_CAP_MAX_N
+#define RF_SPEC_CAP_MAX_N 255
 #endif
-constexpr int RF_SPEC_CAP = RF_SPEC_CAP_N;  // listed windows per pair; beyond it the pair finishes serially
+constexpr int RF_SPEC_CAP_MAX = RF_SPEC_CAP_MAX_N;
+inline int spec_cap_for(int n_tr) { return n_tr - 1 < 1 ? 1 : (n_tr - 1 < RF_SPEC_CAP_MAX ? n_tr - 1 : RF_SPEC_CAP_MAX); }
 struct SpecPair {
   double best_prob;   // best1: result of the first pop
   float x, y, theta;
   int status;         // 1: nothing to score
-  int n_list;         // windows listed (<= RF_SPEC_CAP)
+  int n_list;         // windows listed (<= SearchBuffers::spec_cap)
   int n_more;         // slots with bound >= best1 beyond the list
   int item_base;      // first queue entry of the pair
   int first_tr;       // slot of the first pop (-1: none)
@@ -103,8 +107,9 @@ struct SearchBuffers {
   int chunks_per_pair;  // theta chunks per pair (uniform upper bound)
   int rot_per_chunk;
   SpecPair* spec_pairs;  // [n_pairs]
-  SpecItem* spec_items;  // [n_pairs * RF_SPEC_CAP]
-  SpecOut* spec_out;     // [n_pairs * RF_SPEC_CAP]
+  SpecItem* spec_items;  // [n_pairs * spec_cap]
+  SpecOut* spec_out;     // [n_pairs * spec_cap]
+  int spec_cap;          // listed windows per pair (spec_cap_for(n_t * n_t))
   int* spec_counters;    // [0] queue entries written, [1] next entry to fetch
 };
 

@@ -427,7 +427,7 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
 //   refine_finish_kernel  block per pair: replays the reference's decisions over
 //                         the list in order (stop / count / strictly better) and
 //                         writes the result; a pair whose list was cut at
-//                         RF_SPEC_CAP carries on with the serial loop.
+//                         SearchBuffers::spec_cap carries on with the serial loop.
 // Windows scored beyond the reference's stopping point are discarded by the
 // replay and not counted, so pose, score and the n_high / n_pops counters are
 // those of the sequential loop.  launch_refine(serial=true) keeps the
@@ -781,7 +781,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_first_kernel(
   if (q) atomicAdd(&s_ctl[1], q);
   __syncthreads();
   const int n_q = s_ctl[1];
-  const int n_list = min(n_q, RF_SPEC_CAP);
+  const int n_list = min(n_q, sb.spec_cap);
   if (threadIdx.x == 0) {
     sp.n_list = n_list;
     sp.n_more = n_q - n_list;
@@ -936,7 +936,7 @@ int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hig
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, refine_spec_kernel, RF_THREADS, smem_spec);
     if (per_sm < 1) per_sm = 1;
   }
-  const long long max_items = (long long)n_pairs * RF_SPEC_CAP;
+  const long long max_items = (long long)n_pairs * sb.spec_cap;
   const int grid = (int)std::min<long long>((long long)sm_count * per_sm, std::max<long long>(max_items, 1));
   refine_spec_kernel<<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets, slots,
                                                               metas, pairs, rots, sb);

@@ -104,6 +104,8 @@ def main():
     ap.add_argument("--poses", type=int, default=5000, help="poses per robot")
     ap.add_argument("--robots", type=int, default=4)
     ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--stage-cells", type=int, default=0, help="tuning: staged low-res table budget")
+    ap.add_argument("--only-csm", action="store_true")
     args = ap.parse_args()
     plan = make_plan()
     poses = make_trajectories(args.robots, args.poses)
@@ -116,7 +118,7 @@ def main():
                       "(BASELINE configs[4]), 1080 beams, default_config.lua parameters",
             "n_poses": n, "stages": {}}
     st = line["stages"]
-    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03, stage_cells=args.stage_cells)
     m.upload_ranges(ranges[:64], sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC, sr.RANGE_MIN, sr.MAX_RANGE)
 
     t0 = time.perf_counter()
@@ -151,6 +153,9 @@ def main():
     else:
         st["csm_all_candidates"] = {"pairs": 0}
 
+    if args.only_csm:
+        print(json.dumps(line), flush=True)
+        return
     # growing window 1..10 (OptimizeOverGrowingWindow): sum_w w = 55 pair matchings per node
     t0 = time.perf_counter()
     m.nn_build(0.25)
