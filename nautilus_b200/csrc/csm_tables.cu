@@ -18,6 +18,7 @@
 // All kernels take a wave of tables: blockIdx.y = table slot in the wave.
 #include "csm_common.cuh"
 #include "csm_kernels.h"
+#include <cstdlib>
 
 namespace csm {
 
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(256) raster_kernel(
 // ---------------------------------------------------------------------------
 constexpr int XP_WARPS = 4;
 
-__global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
+__global__ void __launch_bounds__(XP_WARPS * 32) xpass_stored_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas) {
   const int t = blockIdx.y;
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
 constexpr int YP_THREADS = 128;
 constexpr int YP_B = 8;  // rows loaded ahead of the recursion
 
-__global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
+__global__ void __launch_bounds__(YP_THREADS) ypass_stored_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
     TableMeta* __restrict__ metas) {
   const int t = blockIdx.y;
@@ -340,6 +341,230 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
 }
 
 // ---------------------------------------------------------------------------
+// K2a' / K2b'  the same two passes WITHOUT the round trip of the causal outputs
+// through HBM.  A line's causal pass is a serial recursion whose outputs the
+// anti-causal pass consumes in reverse order; the stored variants above write
+// them out and read them back (8 + 8 B per cell and pass).  Here the causal pass
+// keeps only its state (the last three outputs) at every 32nd sample - a
+// checkpoint list in thread-local memory, 24 B per 32 cells - and the
+// anti-causal pass rebuilds each 32-sample chunk from its checkpoint just
+// before it walks it backwards.  The rebuilt values are the same operations on
+// the same operands, hence the same bits.  x-pass: write-only (its input is the
+// bitmap); y-pass: reads the x-pass output twice, writes once.  Lines of up to
+// 32 * RC_MAXCH = 2048 samples; longer grids take the stored variants.
+// ---------------------------------------------------------------------------
+constexpr int RC_MAXCH = 64;
+
+__global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
+    Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas) {
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int group = blockIdx.x * XP_WARPS + warp;
+  const int rows = m.cy1 - m.cy0 + 1;
+  if (group * 32 >= rows) return;
+  const TableSlot slot = slots[t];
+  const int row_local = group * 32 + lane;
+  const bool has_row = row_local < rows && slot.rowflag[row_local] != 0;
+  const unsigned mask = __ballot_sync(0xffffffffu, has_row);
+  if (mask == 0u) return;
+
+  __shared__ double s_tile[XP_WARPS][32][33];
+  double (*tile)[33] = s_tile[warp];
+  double ck[3 * RC_MAXCH];
+  double* base = slot.values + (size_t)(m.cy0 + group * 32 - m.ay0) * m.stride;
+  const unsigned* bm = slot.bitmap + (size_t)row_local * g.bm_stride;
+  const int words = ((m.cx1 - m.cx0) >> 5) + 1;
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
+  const double sum = __dmul_rn(f.B, f.B);
+
+  double v1 = 0.0, v2 = 0.0, v3 = 0.0;  // Neumann seed, CImg.h:49088-49090
+  if (m.cx0 == 0 && has_row && (bm[0] & 1u)) v1 = v2 = v3 = __ddiv_rn(1.0, f.B);
+  double iplus = 0.0;                   // data[N-1] before the causal pass, CImg.h:49085
+  if (m.cx1 == g.w - 1 && has_row) {
+    const int b = g.w - 1 - m.cx0;
+    if ((bm[b >> 5] >> (b & 31)) & 1u) iplus = 1.0;
+  }
+
+  // ---- causal pass, columns cx0 .. ax1: states only
+  const int n_fwd = m.ax1 - m.cx0 + 1;
+  for (int c0 = 0, ci = 0; c0 < n_fwd; c0 += 32, ++ci) {
+    ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
+    const int nk = min(32, n_fwd - c0);
+    const unsigned word = (has_row && ci < words) ? bm[ci] : 0u;
+#pragma unroll 8
+    for (int k = 0; k < nk; ++k) {
+      const double x = ((word >> k) & 1u) ? 1.0 : 0.0;
+      const double v0 = vv_step(x, v1, v2, v3, a1, a2, a3);
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+  }
+
+  const bool at_edge = (m.ax1 == g.w - 1);
+  double w0 = 0.0;
+  if (at_edge) {
+    double w1, w2;
+    vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+    v1 = w0; v2 = w1; v3 = w2;
+  } else {
+    v1 = v2 = v3 = 0.0;
+  }
+
+  // ---- anti-causal pass, columns ax1 .. ax0, chunks aligned to cx0
+  const int rel_hi = m.ax1 - m.cx0;
+  const int rel_lo = m.ax0 - m.cx0;
+  const int ch_hi = rel_hi >> 5;
+  const int ch_lo = (rel_lo >= 0) ? (rel_lo >> 5) : -((-rel_lo + 31) >> 5);
+  for (int ch = ch_hi; ch >= ch_lo; --ch) {
+    const int r0 = ch * 32;
+    const int k_lo = max(0, rel_lo - r0), k_hi = min(31, rel_hi - r0);
+    if (ch >= 0) {  // rebuild the chunk's causal outputs (k_lo == 0 here)
+      double f1 = ck[3 * ch], f2 = ck[3 * ch + 1], f3 = ck[3 * ch + 2];
+      const unsigned word = (has_row && ch < words) ? bm[ch] : 0u;
+#pragma unroll 8
+      for (int k = 0; k <= k_hi; ++k) {
+        const double x = ((word >> k) & 1u) ? 1.0 : 0.0;
+        const double v0 = vv_step(x, f1, f2, f3, a1, a2, a3);
+        tile[lane][k] = v0;
+        f3 = f2; f2 = f1; f1 = v0;
+      }
+    }
+    for (int k = k_hi; k >= k_lo; --k) {
+      if (at_edge && r0 + k == rel_hi) {  // data[N-1] = val[0] of the Triggs step
+        tile[lane][k] = w0;
+        continue;
+      }
+      const double y = (ch >= 0) ? tile[lane][k] : 0.0;  // exact zeros left of the box
+      const double v0 = vv_step(__dmul_rn(y, sum), v1, v2, v3, a1, a2, a3);
+      tile[lane][k] = v0;
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+    __syncwarp();
+    if (lane >= k_lo && lane <= k_hi) {
+      double* dst = base + (m.cx0 + r0 + lane - m.ax0);
+      for (int rr = 0; rr < 32; ++rr)
+        if ((mask >> rr) & 1u) dst[(size_t)rr * m.stride] = tile[rr][lane];
+    }
+    __syncwarp();
+  }
+}
+
+// YC = rows per checkpointed chunk (32: 64 loads in flight per thread and 150
+// registers; 16: 3 KB of checkpoints per thread, ~90 registers)
+template <int YC, int MINB>
+__global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
+    Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
+    TableMeta* __restrict__ metas) {
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int aw = m.ax1 - m.ax0 + 1;
+  if ((int)(blockIdx.x * YP_THREADS) >= aw) return;
+  const int col = blockIdx.x * YP_THREADS + threadIdx.x;
+  const bool live = col < aw;
+  const TableSlot slot = slots[t];
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
+  const double sum = __dmul_rn(f.B, f.B);
+  double* colp = slot.values + (live ? col : 0);
+  const unsigned char* flag = slot.rowflag;
+  const size_t stride = (size_t)m.stride;
+
+  double vmax = -INFINITY, vmin = INFINITY;
+  if (live) {
+    double ck[3 * RC_MAXCH * 32 / YC];
+    double v1 = 0.0, v2 = 0.0, v3 = 0.0;  // Neumann seed from grid row 0
+    if (m.cy0 == 0 && flag[0]) {
+      const double x0 = colp[(size_t)(0 - m.ay0) * stride];
+      v1 = v2 = v3 = __ddiv_rn(x0, f.B);
+    }
+    double iplus = 0.0;  // x-pass output on the grid's last row
+    if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
+      iplus = colp[(size_t)(g.w - 1 - m.ay0) * stride];
+
+    // causal pass, rows cy0 .. ay1: states only
+    const int n_fwd = m.ay1 - m.cy0 + 1;
+    const int nch = (n_fwd + YC - 1) / YC;
+    for (int ci = 0; ci < nch; ++ci) {
+      const int r0 = m.cy0 + ci * YC;
+      ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
+      double a[YC];
+#pragma unroll
+      for (int u = 0; u < YC; ++u) {
+        const int r = r0 + u;
+        a[u] = (r <= m.cy1 && flag[r - m.cy0]) ? colp[(size_t)(r - m.ay0) * stride] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < YC; ++u) {
+        if (r0 + u <= m.ay1) {
+          const double v0 = vv_step(a[u], v1, v2, v3, a1, a2, a3);
+          v3 = v2; v2 = v1; v1 = v0;
+        }
+      }
+    }
+    const bool at_edge = (m.ay1 == g.w - 1);
+    double w0 = 0.0;
+    if (at_edge) {  // Triggs boundary at the grid edge
+      double w1, w2;
+      vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+      v1 = w0; v2 = w1; v3 = w2;
+    } else {
+      v1 = v2 = v3 = 0.0;
+    }
+    // anti-causal pass down to the rectangle's first row, chunk by chunk
+    const int rel_lo = m.ay0 - m.cy0;  // <= 0
+    const int ch_lo = -((-rel_lo + YC - 1) / YC);
+    for (int ch = nch - 1; ch >= ch_lo; --ch) {
+      const int r0 = m.cy0 + ch * YC;
+      double a[YC];
+      if (ch >= 0) {  // rebuild the chunk's causal outputs from its checkpoint
+#pragma unroll
+        for (int u = 0; u < YC; ++u) {
+          const int r = r0 + u;
+          a[u] = (r <= m.cy1 && flag[r - m.cy0]) ? colp[(size_t)(r - m.ay0) * stride] : 0.0;
+        }
+        double f1 = ck[3 * ch], f2 = ck[3 * ch + 1], f3 = ck[3 * ch + 2];
+#pragma unroll
+        for (int u = 0; u < YC; ++u) {
+          if (r0 + u <= m.ay1) {
+            const double v0 = vv_step(a[u], f1, f2, f3, a1, a2, a3);
+            a[u] = v0;
+            f3 = f2; f2 = f1; f1 = v0;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < YC; ++u) a[u] = 0.0;  // exact zeros above the box
+      }
+#pragma unroll
+      for (int u = YC - 1; u >= 0; --u) {
+        const int r = r0 + u;
+        if (r <= m.ay1 && r >= m.ay0) {
+          double v0;
+          if (at_edge && r == m.ay1) {
+            v0 = w0;  // data[N-1] = val[0] of the Triggs step; the state is already set
+          } else {
+            v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
+            v3 = v2; v2 = v1; v1 = v0;
+          }
+          colp[(size_t)(r - m.ay0) * stride] = v0;
+          vmax = fmax(vmax, v0); vmin = fmin(vmin, v0);
+        }
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+  }
+  if ((threadIdx.x & 31) == 0 && vmax >= vmin) {
+    atomicMax(&metas[t].max_key, order_key(vmax));
+    atomicMin(&metas[t].min_key, order_key(vmin));
+  }
+}
+
+// ---------------------------------------------------------------------------
 // K3+K4  normalise (CImg::normalize(0,1), CImg.h:39499-39517) fused with
 // GetLookupTableLowRes (CorrelativeScanMatcher.cc:32-48).
 //
@@ -354,10 +579,8 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_kernel(
 // ---------------------------------------------------------------------------
 constexpr int NP_B = 6;  // rows of a pooling window loaded ahead (windows are 9-11 rows)
 
-__device__ __forceinline__ double normalise_value(double v, double mn, double range) {
-  // (v - m) / (M - m) * (1 - 0) + 0 ; the last two operations are exact no-ops
-  return __ddiv_rn(__dsub_rn(v, mn), range);
-}
+// normalised value = (v - m) / (M - m) * (1 - 0) + 0 ; the last two operations
+// are exact no-ops
 
 __global__ void __launch_bounds__(256) normalize_pool_kernel(
     Geometry g, const TableSlot* __restrict__ slots, TableMeta* __restrict__ metas,
@@ -377,8 +600,14 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
   const bool constant = (M == mn);  // CImg fills with min_value (0) in that case
   const double range = __dsub_rn(M, mn);
   const int aw = m.ax1 - m.ax0 + 1;
+  // v -> (v - mn) / range is monotone (subtraction and division by a positive
+  // number round monotonically), so the window maximum is normalised once per
+  // column instead of once per cell, and a cell whose difference lies clearly
+  // below range * 1e-10 reads as the lookup floor without the division and the
+  // log: d < range * 1e-10 * (1 - 1e-9) => d / range rounds to <= 1e-10.
+  const double sub_floor = __dmul_rn(range, CSM_MIN_VALUE_FOR_LOOKUP * (1.0 - 1e-9));
   for (int c = threadIdx.x; c < aw; c += blockDim.x) {
-    double cm = -INFINITY;
+    double dm = -INFINITY;
     double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
     for (int r0 = rs; r0 <= re; r0 += NP_B, p += (size_t)NP_B * m.stride) {
       double v[NP_B];  // the rows of a window are independent: all loads first
@@ -387,15 +616,18 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
 #pragma unroll
       for (int u = 0; u < NP_B; ++u) {
         if (r0 + u <= re) {
-          const double nv = constant ? 0.0 : normalise_value(v[u], mn, range);
+          const double d = __dsub_rn(v[u], mn);
+          dm = fmax(dm, d);
           // matching only ever needs log(GetPointValue): take it once per cell here
           // instead of once per (candidate, point) in the search
-          p[(size_t)u * m.stride] = store_log ? lookup_log(nv) : nv;
-          cm = fmax(cm, nv);
+          double out;
+          if (store_log) out = (constant || d < sub_floor) ? CSM_FLOOR_LOG : lookup_log(__ddiv_rn(d, range));
+          else out = constant ? 0.0 : __ddiv_rn(d, range);
+          p[(size_t)u * m.stride] = out;
         }
       }
     }
-    s_colmax[c] = cm;
+    s_colmax[c] = constant ? 0.0 : __ddiv_rn(dm, range);
   }
   __syncthreads();
   const int dy = pool_dst[ky];
@@ -486,9 +718,20 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   if (n_tables <= 0) return;
   raster_kernel<<<n_tables, 256, 0, stream>>>(g, points, offsets, scan_ids, slots, metas);
   dim3 gx((g.w + XP_WARPS * 32 - 1) / (XP_WARPS * 32), n_tables);
-  xpass_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
   dim3 gy((g.w + YP_THREADS - 1) / YP_THREADS, n_tables);
-  ypass_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  static const bool stored = getenv("NAUTILUS_CSM_TABLE_STORED") != nullptr;  // A/B knob
+  if (g.w <= 32 * RC_MAXCH && !stored) {
+    xpass_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+    static const int yc = getenv("NAUTILUS_CSM_YC") ? atoi(getenv("NAUTILUS_CSM_YC")) : 16;
+    static const int minb = getenv("NAUTILUS_CSM_YMINB") ? atoi(getenv("NAUTILUS_CSM_YMINB")) : 5;
+    if (yc == 32) ypass_kernel<32, 3><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+    else if (minb == 6) ypass_kernel<16, 6><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+    else if (minb == 8) ypass_kernel<16, 8><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+    else ypass_kernel<16, 5><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  } else {
+    xpass_stored_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+    ypass_stored_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  }
   dim3 gn(g.n_pool, n_tables);
   normalize_pool_kernel<<<gn, 256, sizeof(double) * g.w, stream>>>(
       g, slots, metas, pool.s, pool.e, pool.dst, pool.win, store_log ? 1 : 0);
