@@ -367,6 +367,7 @@ static bool host_cell_clear(const CellMap& m, float v, float eps, float qmax, in
 int nautilus_csm_regular_check(NautilusCsm* h, int64_t n_samples, uint64_t seed,
                                int64_t* n_checked, int64_t* n_bad_low, int64_t* n_bad_high) {
   if (!h || !n_checked || !n_bad_low || !n_bad_high) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   CellMap ml = h->cm_low, mh = h->cm_high;
   ml.lowf = h->thr_low_host.data();
   mh.lowf = h->thr_high_host.data();
@@ -521,12 +522,14 @@ void nautilus_csm_destroy(NautilusCsm* h) {
 
 int nautilus_csm_set_stream(NautilusCsm* h, void* cuda_stream) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
   return NAUTILUS_OK;
 }
 
 int nautilus_csm_table_dims(const NautilusCsm* h, uint64_t* w_high, uint64_t* w_low) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (w_high) *w_high = (uint64_t)h->geo.w;
   if (w_low) *w_low = (uint64_t)h->geo.wl;
   return NAUTILUS_OK;
@@ -535,6 +538,7 @@ int nautilus_csm_table_dims(const NautilusCsm* h, uint64_t* w_high, uint64_t* w_
 int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* offsets,
                               int32_t n_scans) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   CU_TRY(cudaSetDevice(h->device));
   h->nn.built = false;  // the NN index belongs to the previous scan set
   int rc = upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
@@ -547,6 +551,7 @@ int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* of
 
 int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out) {
   if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   *out = h->timings;
   return NAUTILUS_OK;
 }
@@ -789,6 +794,7 @@ int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t
                              double* score, float* x, float* y, float* theta,
                              NautilusCsmStats* stats) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   CU_TRY(cudaSetDevice(h->device));
   return match_batch_impl(h, h->user_scans, a_ids, b_ids, rot_min, rot_max, n_pairs, score, x, y,
                           theta, stats);
@@ -796,6 +802,7 @@ int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t
 
 int nautilus_csm_copy_results_dev(NautilusCsm* h, void* dst_dev, int32_t n_pairs) {
   if (!h || !dst_dev) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   if (n_pairs < 0 || n_pairs > h->last_n_pairs)
     return fail(NAUTILUS_ESTATE, "no batch result of that size is resident");
   CU_TRY(cudaSetDevice(h->device));
@@ -808,6 +815,7 @@ int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* 
                        double rot_min, double rot_max, double* score, float* x, float* y,
                        float* theta, NautilusCsmStats* stats) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (na < 0 || nb < 0) return fail(NAUTILUS_EINVAL, "negative point count");
   if (na == 0) return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
   CU_TRY(cudaSetDevice(h->device));
@@ -825,6 +833,7 @@ int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* 
 int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,
                              int32_t dims, double rotation, float* out) {
   if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   if (dims != 2 && dims != 3) return fail(NAUTILUS_EINVAL, "dims must be 2 or 3");
   if (na <= 0 || nb < 0) return fail(NAUTILUS_EEMPTY, "empty query cloud");
   if (h->grid_rc) return fail(h->grid_rc, h->grid_error);
@@ -894,6 +903,7 @@ int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const f
 int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points, double* out_high,
                                double* out_low) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (n_points < 0 || (n_points > 0 && !xy)) return fail(NAUTILUS_EINVAL, "bad cloud");
   CU_TRY(cudaSetDevice(h->device));
   int rc = require_tiling(h);
@@ -925,6 +935,7 @@ int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points
 int nautilus_csm_lowres_from_table(NautilusCsm* h, const double* high, uint64_t width,
                                    uint64_t height, double resolution, double* out_low) {
   if (!h || !high || !out_low) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   if (width == 0 || height == 0)
     return fail(NAUTILUS_EINVAL, "empty table (CImg::get_crop throws on an empty image)");
   if (!(resolution > 0) || width > 30000 || height > 30000) return fail(NAUTILUS_EINVAL, "bad table");
@@ -956,6 +967,7 @@ int nautilus_csm_lowres_from_table(NautilusCsm* h, const double* high, uint64_t 
 
 int nautilus_csm_build_tables(NautilusCsm* h, const int32_t* scan_ids, int32_t n, double* checksum) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (n < 0 || (n > 0 && !scan_ids)) return fail(NAUTILUS_EINVAL, "bad scan id list");
   CU_TRY(cudaSetDevice(h->device));
   h->timings = NautilusCsmTimings{};

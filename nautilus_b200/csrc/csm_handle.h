@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -103,7 +104,17 @@ int nautilus_internal_host_xy(NautilusCsm* h);
 using namespace csm;
 using namespace csmh;
 
+// Entry points that take a handle hold its lock for the whole call: the
+// reference object is called concurrently from OpenMP threads
+// (CorrelativeScanMatcher.cc:381-386, bag_avg_matcher.cc:104-141); calls on one
+// handle are serialised here, calls on different handles run concurrently.
+// The CUDA current device is per host thread, so the guard also selects the handle's.
+#define NAUTILUS_GUARD(h)                                               \
+  std::lock_guard<std::recursive_mutex> nautilus_guard_((h)->mu);       \
+  cudaSetDevice((h)->device)
+
 struct NautilusCsm {
+  mutable std::recursive_mutex mu;
   NautilusCsmParams params;
   Geometry geo;
   VanVliet vv;

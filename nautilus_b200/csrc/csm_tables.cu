@@ -451,8 +451,70 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
   }
 }
 
-// YC = rows per checkpointed chunk (32: 64 loads in flight per thread and 150
-// registers; 16: 3 KB of checkpoints per thread, ~90 registers)
+// Global-space accesses of the value buffer (the slot pointers come from memory,
+// so the compiler would otherwise emit generic LD / ST).
+__device__ __forceinline__ double ld_gbl(const double* p) {
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_gbl(double* p, double v) {
+  asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
+// The YC x-pass outputs of one column for rows r0 .. r0+YC-1 of the grid; `bits`
+// has bit u set when row r0+u holds a point (rows without one are exact zeros and
+// are not read).
+template <int YC>
+__device__ __forceinline__ void y_load(double (&a)[YC], const double* p, size_t stride,
+                                       unsigned bits) {
+#pragma unroll
+  for (int u = 0; u < YC; ++u) a[u] = ((bits >> u) & 1u) ? ld_gbl(p + (size_t)u * stride) : 0.0;
+}
+
+// nrow causal steps over a[0 .. nrow-1]; KEEP: the outputs replace the inputs.
+template <int YC, bool FULL, bool KEEP>
+__device__ __forceinline__ void y_causal(double (&a)[YC], int nrow, double& v1, double& v2,
+                                         double& v3, double a1, double a2, double a3) {
+#pragma unroll
+  for (int u = 0; u < YC; ++u) {
+    if (FULL || u < nrow) {
+      const double v0 = vv_step(a[u], v1, v2, v3, a1, a2, a3);
+      if (KEEP) a[u] = v0;
+      v3 = v2; v2 = v1; v1 = v0;
+    }
+  }
+}
+
+// Anti-causal steps over a[hi .. lo] (causal outputs in, final values stored to
+// p + u * stride); edge_u = index whose value is the Triggs w0 (state already
+// set), -1 when none.
+template <int YC, bool FULL, bool NEEDMIN>
+__device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int hi, int edge_u,
+                                             double w0, double* p, size_t stride, double sum,
+                                             double& v1, double& v2, double& v3, double a1,
+                                             double a2, double a3, double& vmax, double& vmin) {
+#pragma unroll
+  for (int u = YC - 1; u >= 0; --u) {
+    if (FULL || (u >= lo && u <= hi)) {
+      double v0;
+      if (!FULL && u == edge_u) {
+        v0 = w0;
+      } else {
+        v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
+        v3 = v2; v2 = v1; v1 = v0;
+      }
+      st_gbl(p + (size_t)u * stride, v0);
+      vmax = v0 > vmax ? v0 : vmax;  // no NaNs here: a compare and a select instead of fmax
+      if (NEEDMIN) vmin = v0 < vmin ? v0 : vmin;
+    }
+  }
+}
+
+// YC = rows per checkpointed chunk (32: 64 loads in flight per thread but ~150
+// registers; 16: 3 KB of checkpoints per thread, ~90 registers).  The minimum is
+// only tracked when the rectangle is the whole grid (a cropped table normalises
+// against 0, see normalize_pool_kernel).
 template <int YC, int MINB>
 __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
@@ -471,36 +533,46 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
   const unsigned char* flag = slot.rowflag;
   const size_t stride = (size_t)m.stride;
 
+  // rows of the occupied box that hold a point, one bit each (zeros past the box)
+  __shared__ unsigned s_rows[RC_MAXCH + 1];
+  {
+    const int rows = m.cy1 - m.cy0 + 1;
+    for (int w = threadIdx.x >> 5; w <= RC_MAXCH; w += YP_THREADS / 32) {
+      const int r = w * 32 + (threadIdx.x & 31);
+      const unsigned b = __ballot_sync(0xffffffffu, r < rows && flag[r] != 0);
+      if ((threadIdx.x & 31) == 0) s_rows[w] = b;
+    }
+  }
+  __syncthreads();
+  constexpr unsigned CMASK = YC == 32 ? 0xffffffffu : ((1u << (YC & 31)) - 1u);
+
+  const bool needmin = !m.cropped;
   double vmax = -INFINITY, vmin = INFINITY;
   if (live) {
     double ck[3 * RC_MAXCH * 32 / YC];
     double v1 = 0.0, v2 = 0.0, v3 = 0.0;  // Neumann seed from grid row 0
     if (m.cy0 == 0 && flag[0]) {
-      const double x0 = colp[(size_t)(0 - m.ay0) * stride];
+      const double x0 = ld_gbl(colp + (size_t)(0 - m.ay0) * stride);
       v1 = v2 = v3 = __ddiv_rn(x0, f.B);
     }
     double iplus = 0.0;  // x-pass output on the grid's last row
     if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
-      iplus = colp[(size_t)(g.w - 1 - m.ay0) * stride];
+      iplus = ld_gbl(colp + (size_t)(g.w - 1 - m.ay0) * stride);
 
     // causal pass, rows cy0 .. ay1: states only
     const int n_fwd = m.ay1 - m.cy0 + 1;
     const int nch = (n_fwd + YC - 1) / YC;
-    for (int ci = 0; ci < nch; ++ci) {
-      const int r0 = m.cy0 + ci * YC;
-      ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
-      double a[YC];
-#pragma unroll
-      for (int u = 0; u < YC; ++u) {
-        const int r = r0 + u;
-        a[u] = (r <= m.cy1 && flag[r - m.cy0]) ? colp[(size_t)(r - m.ay0) * stride] : 0.0;
-      }
-#pragma unroll
-      for (int u = 0; u < YC; ++u) {
-        if (r0 + u <= m.ay1) {
-          const double v0 = vv_step(a[u], v1, v2, v3, a1, a2, a3);
-          v3 = v2; v2 = v1; v1 = v0;
-        }
+    {
+      const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
+      for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
+        ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
+        const int b0 = ci * YC;
+        const unsigned bits = (s_rows[b0 >> 5] >> (b0 & 31)) & CMASK;
+        double a[YC];
+        y_load<YC>(a, p, stride, bits);
+        const int nrow = n_fwd - b0;
+        if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
+        else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
       }
     }
     const bool at_edge = (m.ay1 == g.w - 1);
@@ -515,42 +587,33 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     // anti-causal pass down to the rectangle's first row, chunk by chunk
     const int rel_lo = m.ay0 - m.cy0;  // <= 0
     const int ch_lo = -((-rel_lo + YC - 1) / YC);
-    for (int ch = nch - 1; ch >= ch_lo; --ch) {
-      const int r0 = m.cy0 + ch * YC;
+    double* p = colp + (size_t)(m.cy0 + (nch - 1) * YC - m.ay0) * stride;
+    for (int ch = nch - 1; ch >= ch_lo; --ch, p -= (size_t)YC * stride) {
+      const int b0 = ch * YC;  // row of a[0] relative to cy0
       double a[YC];
       if (ch >= 0) {  // rebuild the chunk's causal outputs from its checkpoint
-#pragma unroll
-        for (int u = 0; u < YC; ++u) {
-          const int r = r0 + u;
-          a[u] = (r <= m.cy1 && flag[r - m.cy0]) ? colp[(size_t)(r - m.ay0) * stride] : 0.0;
-        }
+        const unsigned bits = (s_rows[b0 >> 5] >> (b0 & 31)) & CMASK;
+        y_load<YC>(a, p, stride, bits);
         double f1 = ck[3 * ch], f2 = ck[3 * ch + 1], f3 = ck[3 * ch + 2];
-#pragma unroll
-        for (int u = 0; u < YC; ++u) {
-          if (r0 + u <= m.ay1) {
-            const double v0 = vv_step(a[u], f1, f2, f3, a1, a2, a3);
-            a[u] = v0;
-            f3 = f2; f2 = f1; f1 = v0;
-          }
-        }
+        const int nrow = n_fwd - b0;
+        if (nrow >= YC) y_causal<YC, true, true>(a, YC, f1, f2, f3, a1, a2, a3);
+        else y_causal<YC, false, true>(a, nrow, f1, f2, f3, a1, a2, a3);
       } else {
 #pragma unroll
         for (int u = 0; u < YC; ++u) a[u] = 0.0;  // exact zeros above the box
       }
-#pragma unroll
-      for (int u = YC - 1; u >= 0; --u) {
-        const int r = r0 + u;
-        if (r <= m.ay1 && r >= m.ay0) {
-          double v0;
-          if (at_edge && r == m.ay1) {
-            v0 = w0;  // data[N-1] = val[0] of the Triggs step; the state is already set
-          } else {
-            v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
-            v3 = v2; v2 = v1; v1 = v0;
-          }
-          colp[(size_t)(r - m.ay0) * stride] = v0;
-          vmax = fmax(vmax, v0); vmin = fmin(vmin, v0);
-        }
+      const int lo = max(0, rel_lo - b0), hi = min(YC - 1, n_fwd - 1 - b0);
+      const bool last = at_edge && ch == nch - 1;  // the chunk that holds the grid's last row
+      if (lo == 0 && hi == YC - 1 && !last) {
+        if (needmin)
+          y_anticausal<YC, true, true>(a, 0, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1, a2, a3,
+                                       vmax, vmin);
+        else
+          y_anticausal<YC, true, false>(a, 0, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1, a2,
+                                        a3, vmax, vmin);
+      } else {
+        y_anticausal<YC, false, true>(a, lo, hi, last ? hi : -1, w0, p, stride, sum, v1, v2, v3, a1,
+                                      a2, a3, vmax, vmin);
       }
     }
   }
@@ -558,9 +621,9 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
     vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
   }
-  if ((threadIdx.x & 31) == 0 && vmax >= vmin) {
+  if ((threadIdx.x & 31) == 0 && vmax > -INFINITY) {
     atomicMax(&metas[t].max_key, order_key(vmax));
-    atomicMin(&metas[t].min_key, order_key(vmin));
+    if (needmin) atomicMin(&metas[t].min_key, order_key(vmin));
   }
 }
 
@@ -723,10 +786,7 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   if (g.w <= 32 * RC_MAXCH && !stored) {
     xpass_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
     static const int yc = getenv("NAUTILUS_CSM_YC") ? atoi(getenv("NAUTILUS_CSM_YC")) : 16;
-    static const int minb = getenv("NAUTILUS_CSM_YMINB") ? atoi(getenv("NAUTILUS_CSM_YMINB")) : 5;
     if (yc == 32) ypass_kernel<32, 3><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
-    else if (minb == 6) ypass_kernel<16, 6><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
-    else if (minb == 8) ypass_kernel<16, 8><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
     else ypass_kernel<16, 5><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   } else {
     xpass_stored_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);

@@ -217,6 +217,7 @@ extern "C" {
 int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_scans,
                                int32_t n_beams, const NautilusLaserSpec* spec) {
   if (!h || !spec) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   if (n_scans < 0 || n_beams < 0 || (n_scans > 0 && n_beams > 0 && !ranges))
     return fail(NAUTILUS_EINVAL, "bad range batch");
   if (spec->variant != 0 && spec->variant != 1) return fail(NAUTILUS_EINVAL, "unknown variant");
@@ -310,12 +311,14 @@ int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_sc
 
 int nautilus_csm_frontend_last_ms(const NautilusCsm* h, float* kernel_ms) {
   if (!h || !kernel_ms) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   *kernel_ms = h->frontend_kernel_ms;
   return NAUTILUS_OK;
 }
 
 int nautilus_csm_download_scans(NautilusCsm* h, float* xy, int64_t cap_points, int64_t* offsets) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   ScanSet& ss = h->user_scans;
   if (ss.host_offsets.empty()) return fail(NAUTILUS_ESTATE, "no scans uploaded");
   CU_TRY(cudaSetDevice(h->device));
@@ -334,6 +337,7 @@ int nautilus_csm_download_scans(NautilusCsm* h, float* xy, int64_t cap_points, i
 
 int nautilus_lc_scatter_scores(NautilusCsm* h, double* score) {
   if (!h || !score) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   ScanSet& ss = h->user_scans;
   if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
   CU_TRY(cudaSetDevice(h->device));

@@ -179,6 +179,7 @@ void nautilus_nn_pose_transform(const double* source_pose, const double* target_
 
 int nautilus_nn_build(NautilusCsm* h, double cell_size) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (!(cell_size > 0)) return fail(NAUTILUS_EINVAL, "cell_size must be positive");
   ScanSet& ss = h->user_scans;
   if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
@@ -262,6 +263,7 @@ int nautilus_nn_build(NautilusCsm* h, double cell_size) {
 
 int nautilus_nn_self_index(NautilusCsm* h, int32_t* out) {
   if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   if (!h->nn.built) return fail(NAUTILUS_ESTATE, "nautilus_nn_build has not run for this scan set");
   CU_TRY(cudaSetDevice(h->device));
   const long long total = h->user_scans.host_offsets[h->user_scans.n];
@@ -274,6 +276,7 @@ int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_
                             const float* src_to_tgt, double threshold, int32_t n_pairs,
                             int32_t* match_idx, float* match_dist, int64_t* offsets) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
   NnState& nn = h->nn;
   if (!nn.built) return fail(NAUTILUS_ESTATE, "nautilus_nn_build has not run for this scan set");
@@ -327,6 +330,7 @@ int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_
 
 int nautilus_nn_last_stats(const NautilusCsm* h, float* ms_kernel, uint64_t* n_walked) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (ms_kernel) *ms_kernel = h->nn.ms_last;
   if (n_walked) *n_walked = h->nn.walked_last;
   return NAUTILUS_OK;

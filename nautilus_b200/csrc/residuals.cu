@@ -94,6 +94,7 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
                                        const float* target_normals, double* residuals,
                                        double* jac_source, double* jac_target) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
   if (kind != 0 && kind != 1) return fail(NAUTILUS_EINVAL, "kind must be 0 (point) or 1 (normal)");
   if (n_blocks < 0) return fail(NAUTILUS_EINVAL, "n_blocks < 0");
   if (n_blocks == 0) return NAUTILUS_OK;
@@ -158,6 +159,7 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
 
 extern "C" int nautilus_residuals_last_ms(const NautilusCsm* h, float* kernel_ms) {
   if (!h || !kernel_ms) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
   *kernel_ms = h->residual_kernel_ms;
   return NAUTILUS_OK;
 }

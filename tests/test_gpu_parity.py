@@ -288,3 +288,36 @@ def test_full_size_properties():
     cs1 = m.build_tables(np.arange(40, dtype=np.int32))
     cs2 = m.build_tables(np.arange(40, dtype=np.int32)[::-1].copy())
     assert cs1 > 0 and abs(cs1 - cs2) <= 1e-9 * cs1
+
+
+@pytest.mark.gpu
+def test_concurrent_callers_on_one_handle():
+    """The reference object is called from OpenMP threads (CorrelativeScanMatcher.cc:381-386,
+    bag_avg_matcher.cc:104-141): concurrent single-pair calls on one handle must give the
+    results of the same calls made one after the other (the handle serialises them)."""
+    import threading
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    pairs = [synth.make_pair(40 + k, n_beams=240)[:2] for k in range(12)]
+    serial = [m.GetTransformation(a, b, -0.5, 0.5) for a, b in pairs]
+    out = [None] * len(pairs)
+    errs = []
+
+    def work(k):
+        try:
+            for _ in range(3):
+                out[k] = m.GetTransformation(pairs[k][0], pairs[k][1], -0.5, 0.5)
+                hi = m.GetLookupTableHighRes(pairs[k][1])
+                assert hi.values.max() == 1.0
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(len(pairs))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for got, want in zip(out, serial):
+        assert got[0] == want[0]
+        assert got[1][0][0] == want[1][0][0] and got[1][0][1] == want[1][0][1] and got[1][1] == want[1][1]
+    m.close()
