@@ -353,6 +353,17 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_stored_kernel(
 // bitmap); y-pass: reads the x-pass output twice, writes once.  Lines of up to
 // 32 * RC_MAXCH = 2048 samples; longer grids take the stored variants.
 // ---------------------------------------------------------------------------
+// Global-space accesses of the value buffer (the slot pointers come from memory,
+// so the compiler would otherwise emit generic LD / ST).
+__device__ __forceinline__ double ld_gbl(const double* p) {
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_gbl(double* p, double v) {
+  asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
 constexpr int RC_MAXCH = 64;
 
 __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
@@ -362,19 +373,54 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
   const TableMeta m = metas[t];
   if (m.cx1 < m.cx0) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int group = blockIdx.x * XP_WARPS + warp;
   const int rows = m.cy1 - m.cy0 + 1;
-  if (group * 32 >= rows) return;
+  if (blockIdx.x * XP_WARPS * 32 >= rows) return;  // never more lit rows than rows
   const TableSlot slot = slots[t];
-  const int row_local = group * 32 + lane;
-  const bool has_row = row_local < rows && slot.rowflag[row_local] != 0;
+
+  // Lanes take the rows that hold a point (the others stay exact zeros and are
+  // never touched): row bits of the occupied box, their prefix counts, and the
+  // k-th lit row for lane k of the block's 128-row share.
+  __shared__ unsigned s_rows[RC_MAXCH + 1];
+  __shared__ int s_pref[RC_MAXCH + 1];
+  __shared__ int s_rowidx[XP_WARPS][32];
+  for (int w = warp; w <= RC_MAXCH; w += XP_WARPS) {
+    const int r = w * 32 + lane;
+    const unsigned b = __ballot_sync(0xffffffffu, r < rows && slot.rowflag[r] != 0);
+    if (lane == 0) s_rows[w] = b;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int c0 = __popc(s_rows[2 * lane]), c1 = __popc(s_rows[2 * lane + 1]);
+    int incl = c0 + c1;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    s_pref[2 * lane] = incl - c0 - c1;
+    s_pref[2 * lane + 1] = incl - c1;
+    if (lane == 31) s_pref[RC_MAXCH] = incl;
+  }
+  __syncthreads();
+  const int n_lit = s_pref[RC_MAXCH];
+  const int k_row = (blockIdx.x * XP_WARPS + warp) * 32 + lane;
+  if (k_row - lane >= n_lit) return;
+  const bool has_row = k_row < n_lit;
+  int row_local = 0;
+  if (has_row) {
+    int w = 0;
+    for (int step = RC_MAXCH / 2; step > 0; step >>= 1)
+      if (s_pref[w + step] <= k_row) w += step;
+    row_local = w * 32 + (int)__fns(s_rows[w], 0, k_row - s_pref[w] + 1);
+  }
+  s_rowidx[warp][lane] = row_local;
   const unsigned mask = __ballot_sync(0xffffffffu, has_row);
-  if (mask == 0u) return;
+  __syncwarp();
 
   __shared__ double s_tile[XP_WARPS][32][33];
   double (*tile)[33] = s_tile[warp];
   double ck[3 * RC_MAXCH];
-  double* base = slot.values + (size_t)(m.cy0 + group * 32 - m.ay0) * m.stride;
+  double* base = slot.values + (size_t)(m.cy0 - m.ay0) * m.stride;  // box row 0
+  const int* rowidx = s_rowidx[warp];
   const unsigned* bm = slot.bitmap + (size_t)row_local * g.bm_stride;
   const int words = ((m.cx1 - m.cx0) >> 5) + 1;
   const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
@@ -445,21 +491,10 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     if (lane >= k_lo && lane <= k_hi) {
       double* dst = base + (m.cx0 + r0 + lane - m.ax0);
       for (int rr = 0; rr < 32; ++rr)
-        if ((mask >> rr) & 1u) dst[(size_t)rr * m.stride] = tile[rr][lane];
+        if ((mask >> rr) & 1u) st_gbl(dst + (size_t)rowidx[rr] * m.stride, tile[rr][lane]);
     }
     __syncwarp();
   }
-}
-
-// Global-space accesses of the value buffer (the slot pointers come from memory,
-// so the compiler would otherwise emit generic LD / ST).
-__device__ __forceinline__ double ld_gbl(const double* p) {
-  double v;
-  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
-  return v;
-}
-__device__ __forceinline__ void st_gbl(double* p, double v) {
-  asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
 
 // The YC x-pass outputs of one column for rows r0 .. r0+YC-1 of the grid; `bits`
@@ -675,18 +710,18 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     for (int r0 = rs; r0 <= re; r0 += NP_B, p += (size_t)NP_B * m.stride) {
       double v[NP_B];  // the rows of a window are independent: all loads first
 #pragma unroll
-      for (int u = 0; u < NP_B; ++u) v[u] = (r0 + u <= re) ? p[(size_t)u * m.stride] : 0.0;
+      for (int u = 0; u < NP_B; ++u) v[u] = (r0 + u <= re) ? ld_gbl(p + (size_t)u * m.stride) : 0.0;
 #pragma unroll
       for (int u = 0; u < NP_B; ++u) {
         if (r0 + u <= re) {
           const double d = __dsub_rn(v[u], mn);
-          dm = fmax(dm, d);
+          dm = d > dm ? d : dm;  // no NaNs: compare + select
           // matching only ever needs log(GetPointValue): take it once per cell here
           // instead of once per (candidate, point) in the search
           double out;
           if (store_log) out = (constant || d < sub_floor) ? CSM_FLOOR_LOG : lookup_log(__ddiv_rn(d, range));
           else out = constant ? 0.0 : __ddiv_rn(d, range);
-          p[(size_t)u * m.stride] = out;
+          st_gbl(p + (size_t)u * m.stride, out);
         }
       }
     }
