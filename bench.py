@@ -279,13 +279,16 @@ def run_ours(args):
 
     def timed(upload, steps):
         """K steps between CUDA events on the launching stream; max over ranks."""
-        acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "launches": 0, "cand": 0, "low_cand_pts": 0}
+        acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "launches": 0, "cand": 0, "low_cand_pts": 0,
+               "step_wall_ms": []}
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record(stream)
         for _ in range(steps):
+            ts = time.perf_counter()
             score, x, y, th, st = step(upload)
+            acc["step_wall_ms"].append(round(1e3 * (time.perf_counter() - ts), 3))
             t = m.last_timings()
             acc["tables"] += t["ms_tables"]; acc["low"] += t["ms_low"]; acc["refine"] += t["ms_refine"]
             acc["launches"] += t["launches"]
@@ -306,11 +309,15 @@ def run_ours(args):
         return ms, wall_ms, acc, (score, x, y, th, st)
 
     m.upload_scans(xy_host, offs)
-    sampler = ClockSampler(local)   # NVML start-up happens before the warm-up
-    for _ in range(args.warmup):
-        step(False)
+    # NVML start-up, the sampler thread's start and its first queries (which can
+    # stall the driver for ~0.2 s) happen during the warm-up; only samples taken
+    # inside the timed region are kept
+    sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step(False)
+    sampler.samples = []
     ms, _, acc, last = timed(False, args.steps)          # inputs resident in HBM
     clocks = sampler.stop() if rank == 0 else None
     for _ in range(1):
@@ -380,6 +387,7 @@ def run_ours(args):
                              "clock (measured: scripts/micro/dadd_bench.cu, 2 warp-DADD/clk/SM), "
                              "in Gadd/s; fp64_add_frac is the binding fraction (DESIGN.md 3)"},
         "kernels": kernels,
+        "step_wall_ms": {"resident": acc["step_wall_ms"], "e2e": acc_e2e["step_wall_ms"]},
     }
     if not args.no_cpu_baseline:
         cores = host_cores()

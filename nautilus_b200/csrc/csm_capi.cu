@@ -583,6 +583,69 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if (rc) return rc;
   const int n_t = h->grid.n_t, n_tr = n_t * n_t;
 
+  // ---- validate, and find the distinct targets (ascending scan id) without
+  // sorting: the table kernels only need that list, so they are launched first
+  // and the rest of the host-side planning below overlaps them.
+  std::vector<int> tindex(ss.n, -1);
+  for (int p = 0; p < n_pairs; ++p) {
+    if (a_ids[p] < 0 || a_ids[p] >= ss.n || b_ids[p] < 0 || b_ids[p] >= ss.n)
+      return fail(NAUTILUS_EINVAL, "scan id out of range");
+    if (ss.host_offsets[a_ids[p] + 1] == ss.host_offsets[a_ids[p]])
+      return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
+    if (!(rot_min[p] < rot_max[p]))
+      return fail(NAUTILUS_EEMPTY, "empty rotation window: the reference does not terminate on it");
+    tindex[b_ids[p]] = 0;
+  }
+  std::vector<int> targets;  // distinct target scans, ascending: every target's tables are built once per call
+  for (int s = 0; s < ss.n; ++s)
+    if (tindex[s] == 0) { tindex[s] = (int)targets.size(); targets.push_back(s); }
+  const int n_targets = (int)targets.size();
+
+  rc = ensure_slots(h, n_targets);
+  if (rc) return rc;
+  // ---- waves.  A batch whose targets fit the resident slots is one wave.  With
+  // more targets than slots the slots are reused wave after wave.  Splitting a
+  // batch that fits into several waves (NAUTILUS_CSM_WAVES) builds the tables of
+  // wave w+1 on a second stream while wave w is searched.
+  const int n_slots = h->n_slots;
+  const bool ring = n_targets > n_slots;
+  int wave_tables;
+  if (ring) {
+    wave_tables = n_slots;
+  } else {
+    const char* env = getenv("NAUTILUS_CSM_WAVES");
+    int n_sub = env ? atoi(env) : 1;
+    n_sub = std::max(1, std::min(n_sub, n_targets));
+    wave_tables = (n_targets + n_sub - 1) / n_sub;
+  }
+  const int n_waves = (n_targets + wave_tables - 1) / wave_tables;
+  auto slot_base = [&](int w) { return ring ? 0 : w * wave_tables; };
+
+  if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets.data(), sizeof(int) * n_targets,
+                         cudaMemcpyHostToDevice, st));
+  int launches = 0;
+  // events: 0 = start; per wave w: 1+5w tables begin, +1 tables end (table stream),
+  // +2 search begin, +3 low-res end, +4 refine end (caller stream)
+  auto evt = [&](int w, int k) { return get_event(h, 1 + 5 * (size_t)w + k); };
+  cudaStream_t tst = h->table_stream ? h->table_stream : st;
+  CU_TRY(cudaEventRecord(get_event(h, 0), st));
+  CU_TRY(cudaStreamWaitEvent(tst, get_event(h, 0), 0));  // the target list is uploaded on st
+  auto issue_tables = [&](int w) -> int {
+    const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
+    const int base = slot_base(w);
+    if (ring && w >= 1) CU_TRY(cudaStreamWaitEvent(tst, evt(w - 1, 4), 0));  // slots still being searched
+    CU_TRY(cudaEventRecord(evt(w, 0), tst));
+    launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
+                      h->slots_dev.p + base, h->metas_dev.p + base, h->pool_dev.d, t1 - t0, true,
+                      tst, &launches);
+    CU_TRY(cudaEventRecord(evt(w, 1), tst));
+    return NAUTILUS_OK;
+  };
+  if ((rc = issue_tables(0))) return rc;
+  if (!ring && n_waves > 1 && (rc = issue_tables(1))) return rc;
+
   // ---- rotation lists (cc:92-93: double accumulation, used as float), cached
   // per distinct window; sinf/cosf from the host libm like Rotation2Df does.
   std::map<std::pair<double, double>, std::pair<int, int>> rot_cache;
@@ -590,10 +653,6 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   std::vector<PairWork> work(n_pairs);
   int max_rot = 0;
   for (int p = 0; p < n_pairs; ++p) {
-    if (a_ids[p] < 0 || a_ids[p] >= ss.n || b_ids[p] < 0 || b_ids[p] >= ss.n)
-      return fail(NAUTILUS_EINVAL, "scan id out of range");
-    if (ss.host_offsets[a_ids[p] + 1] == ss.host_offsets[a_ids[p]])
-      return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
     auto key = std::make_pair(rot_min[p], rot_max[p]);
     auto it = rot_cache.find(key);
     if (it == rot_cache.end()) {
@@ -609,8 +668,6 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
       }
       it = rot_cache.emplace(key, std::make_pair(begin, (int)rots.size() - begin)).first;
     }
-    if (it->second.second == 0)
-      return fail(NAUTILUS_EEMPTY, "empty rotation window: the reference does not terminate on it");
     work[p].a_scan = a_ids[p];
     work[p].rot_begin = it->second.first;
     work[p].n_rot = it->second.second;
@@ -619,46 +676,20 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     max_rot = std::max(max_rot, work[p].n_rot);
   }
 
-  // ---- group by target: every target's tables are built once per call
-  std::vector<int> order(n_pairs);
-  std::iota(order.begin(), order.end(), 0);
-  std::stable_sort(order.begin(), order.end(), [&](int l, int r) { return b_ids[l] < b_ids[r]; });
-  std::vector<int> targets;       // distinct target scans in order
-  std::vector<int> first_pair;    // index into `sorted` of each target's first pair
+  // ---- group the pairs by target (counting sort over the target index, stable)
+  std::vector<int> first_pair(n_targets + 1, 0);  // index into `sorted` of each target's first pair
+  for (int p = 0; p < n_pairs; ++p) ++first_pair[tindex[b_ids[p]] + 1];
+  for (int t = 0; t < n_targets; ++t) first_pair[t + 1] += first_pair[t];
   std::vector<PairWork> sorted(n_pairs);
-  for (int k = 0; k < n_pairs; ++k) {
-    const int p = order[k];
-    if (k == 0 || b_ids[p] != targets.back()) {
-      targets.push_back(b_ids[p]);
-      first_pair.push_back(k);
+  {
+    std::vector<int> fill(first_pair.begin(), first_pair.end() - 1);
+    for (int p = 0; p < n_pairs; ++p) {
+      const int t = tindex[b_ids[p]];
+      PairWork& w = sorted[fill[t]++];
+      w = work[p];
+      w.table = t;  // made wave-relative below
     }
-    sorted[k] = work[p];
-    sorted[k].table = (int)targets.size() - 1;  // made wave-relative below
   }
-  first_pair.push_back(n_pairs);
-  const int n_targets = (int)targets.size();
-
-  rc = ensure_slots(h, n_targets);
-  if (rc) return rc;
-  // ---- waves.  A batch whose targets fit the resident slots is one wave.  With
-  // more targets than slots the slots are reused wave after wave.  Splitting a
-  // batch that fits into several waves (NAUTILUS_CSM_WAVES) builds the tables of
-  // wave w+1 on a second stream while wave w is searched; measured on B200 it
-  // loses more to the per-wave tails of the search than the overlap gains
-  // (61.5 / 68.2 / 71.7 ms per step for 1 / 2 / 3 waves), so the default is one.
-  const int n_slots = h->n_slots;
-  const bool ring = n_targets > n_slots;
-  int wave_tables;
-  if (ring) {
-    wave_tables = n_slots;
-  } else {
-    const char* env = getenv("NAUTILUS_CSM_WAVES");
-    int n_sub = env ? atoi(env) : 1;
-    n_sub = std::max(1, std::min(n_sub, n_targets));
-    wave_tables = (n_targets + n_sub - 1) / n_sub;
-  }
-  const int n_waves = (n_targets + wave_tables - 1) / wave_tables;
-  auto slot_base = [&](int w) { return ring ? 0 : w * wave_tables; };
   int max_wave_pairs = 0;
   for (int w = 0; w < n_waves; ++w) {
     const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
@@ -701,38 +732,14 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if (low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
     return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
 
-  if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
   if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
   if ((rc = h->rots_dev.reserve(rots.size()))) return rc;
   if ((rc = h->results_dev.reserve(n_pairs))) return rc;
-  cudaStream_t st = h->stream;
-  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets.data(), sizeof(int) * n_targets,
-                         cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted.data(), sizeof(PairWork) * n_pairs,
                          cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
                          cudaMemcpyHostToDevice, st));
 
-  int launches = 0;
-  // events: 0 = start; per wave w: 1+5w tables begin, +1 tables end (table stream),
-  // +2 search begin, +3 low-res end, +4 refine end (caller stream)
-  auto evt = [&](int w, int k) { return get_event(h, 1 + 5 * (size_t)w + k); };
-  cudaStream_t tst = h->table_stream ? h->table_stream : st;
-  CU_TRY(cudaEventRecord(get_event(h, 0), st));
-  CU_TRY(cudaStreamWaitEvent(tst, get_event(h, 0), 0));  // the lists above are uploaded on st
-  auto issue_tables = [&](int w) -> int {
-    const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
-    const int base = slot_base(w);
-    if (ring && w >= 1) CU_TRY(cudaStreamWaitEvent(tst, evt(w - 1, 4), 0));  // slots still being searched
-    CU_TRY(cudaEventRecord(evt(w, 0), tst));
-    launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
-                      h->slots_dev.p + base, h->metas_dev.p + base, h->pool_dev.d, t1 - t0, true,
-                      tst, &launches);
-    CU_TRY(cudaEventRecord(evt(w, 1), tst));
-    return NAUTILUS_OK;
-  };
-  if ((rc = issue_tables(0))) return rc;
-  if (!ring && n_waves > 1 && (rc = issue_tables(1))) return rc;
   for (int w = 0; w < n_waves; ++w) {
     const int t0 = w * wave_tables, t1 = std::min(n_targets, t0 + wave_tables);
     const int k0 = first_pair[t0], k1 = first_pair[t1];
