@@ -76,6 +76,12 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 #ifndef LS_WARPS_N
 #define LS_WARPS_N 12
 #endif
+#ifndef LS_PREF      // 1: fetch the next run's descriptor before the adds of the current run
+#define LS_PREF 0
+#endif
+#ifndef LS_RUNLOOP   // points per iteration of the add loop (4 + tails, or 2 + tail)
+#define LS_RUNLOOP 4
+#endif
 constexpr int LS_WARPS = LS_WARPS_N;
 constexpr int LS_THREADS = LS_WARPS * 32;
 constexpr int LS_PC = 32;            // points per chunk = one per lane in phase A
@@ -254,9 +260,14 @@ __device__ __forceinline__ void low_score_rounds(
         }
         // phase B (lane = candidate column): per run 7 consecutive cells, added once
         // per point of the run -- each sum still takes its terms in point order
+#if LS_PREF
+        unsigned inf = __shfl_sync(0xffffffffu, info, 0);
+#endif
 #pragma unroll 1
         for (int pl = 0; pl < pc;) {
+#if !LS_PREF
           const unsigned inf = __shfl_sync(0xffffffffu, info, pl);
+#endif
           int c = (int)((inf >> 24) & 63u);  // points in the run
           double t[LS_IU];
           if (inf < LS_FLOOR) {
@@ -275,6 +286,23 @@ __device__ __forceinline__ void low_score_rounds(
             for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
           }
           pl += c;
+#if LS_PREF
+          // the next run's descriptor travels while this run's adds issue
+          inf = __shfl_sync(0xffffffffu, info, pl & 31);
+#endif
+#if LS_RUNLOOP == 2
+#pragma unroll 1
+          for (; c >= 2; c -= 2) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+              for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
+          }
+          if (c) {
+#pragma unroll
+            for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
+          }
+#else
 #pragma unroll 1
           for (; c >= 4; c -= 4) {
 #pragma unroll
@@ -292,6 +320,7 @@ __device__ __forceinline__ void low_score_rounds(
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
           }
+#endif
         }
       }
 #pragma unroll
