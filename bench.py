@@ -263,9 +263,13 @@ def run_ours(args):
     rec = torch.empty(n_pairs * m.RESULT_BYTES, dtype=torch.uint8, device=dev)
     gathered = torch.empty(world * rec.numel(), dtype=torch.uint8, device=dev) if world > 1 else None
 
+    upload_ms = [0.0]
+
     def step(upload):
         if upload:
+            tu = time.perf_counter()
             m.upload_scans(xy_host, offs)
+            upload_ms[0] = round(1e3 * (time.perf_counter() - tu), 3)
         out = m.match_batch(pa, pb, *ROT_WINDOW, with_stats=True)
         if world > 1:  # gather only the per-pair (pose, score) records
             m.copy_results_dev(rec.data_ptr(), n_pairs)
@@ -280,7 +284,7 @@ def run_ours(args):
     def timed(upload, steps):
         """K steps between CUDA events on the launching stream; max over ranks."""
         acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "launches": 0, "cand": 0, "low_cand_pts": 0,
-               "step_wall_ms": []}
+               "step_wall_ms": [], "gpu_span_ms": [], "upload_wall_ms": []}
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
@@ -290,6 +294,9 @@ def run_ours(args):
             score, x, y, th, st = step(upload)
             acc["step_wall_ms"].append(round(1e3 * (time.perf_counter() - ts), 3))
             t = m.last_timings()
+            acc["gpu_span_ms"].append(round(t["ms_total"], 3))
+            if upload:
+                acc["upload_wall_ms"].append(upload_ms[0])
             acc["tables"] += t["ms_tables"]; acc["low"] += t["ms_low"]; acc["refine"] += t["ms_refine"]
             acc["launches"] += t["launches"]
             acc["cand"] += int(st[:, 0].sum() + st[:, 1].sum())
@@ -387,7 +394,9 @@ def run_ours(args):
                              "clock (measured: scripts/micro/dadd_bench.cu, 2 warp-DADD/clk/SM), "
                              "in Gadd/s; fp64_add_frac is the binding fraction (DESIGN.md 3)"},
         "kernels": kernels,
-        "step_wall_ms": {"resident": acc["step_wall_ms"], "e2e": acc_e2e["step_wall_ms"]},
+        "step_wall_ms": {"resident": acc["step_wall_ms"], "e2e": acc_e2e["step_wall_ms"],
+                         "e2e_upload": acc_e2e["upload_wall_ms"],
+                         "resident_gpu_span": acc["gpu_span_ms"], "e2e_gpu_span": acc_e2e["gpu_span_ms"]},
     }
     if not args.no_cpu_baseline:
         cores = host_cores()

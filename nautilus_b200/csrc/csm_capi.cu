@@ -146,6 +146,7 @@ size_t slot_bytes(const Geometry& g) {
 int ensure_slots(NautilusCsm* h, int want) {
   const Geometry& g = h->geo;
   int cap = h->params.max_tables > 0 ? h->params.max_tables : 4096;
+  if (std::max(1, std::min(want, cap)) <= h->n_slots) return NAUTILUS_OK;  // steady state: no driver query
   size_t free_b = 0, total_b = 0;
   CU_TRY(cudaMemGetInfo(&free_b, &total_b));
   const size_t per = slot_bytes(g);
@@ -514,6 +515,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
   h->residual_arena.release();
   h->spec_pairs_dev.release(); h->spec_items_dev.release(); h->spec_out_dev.release(); h->spec_counters_dev.release();
+  h->targets_pin.release(); h->sorted_pin.release(); h->results_pin.release(); h->spec_counts_pin.release();
   for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
   if (h->table_stream) cudaStreamDestroy(h->table_stream);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -586,7 +588,8 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   // ---- validate, and find the distinct targets (ascending scan id) without
   // sorting: the table kernels only need that list, so they are launched first
   // and the rest of the host-side planning below overlaps them.
-  std::vector<int> tindex(ss.n, -1);
+  std::vector<int>& tindex = h->plan_tindex;
+  tindex.assign(ss.n, -1);
   for (int p = 0; p < n_pairs; ++p) {
     if (a_ids[p] < 0 || a_ids[p] >= ss.n || b_ids[p] < 0 || b_ids[p] >= ss.n)
       return fail(NAUTILUS_EINVAL, "scan id out of range");
@@ -596,10 +599,12 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
       return fail(NAUTILUS_EEMPTY, "empty rotation window: the reference does not terminate on it");
     tindex[b_ids[p]] = 0;
   }
-  std::vector<int> targets;  // distinct target scans, ascending: every target's tables are built once per call
+  // distinct target scans, ascending: every target's tables are built once per call
+  if ((rc = h->targets_pin.reserve(std::min<size_t>(ss.n, n_pairs)))) return rc;
+  int* targets = h->targets_pin.p;
+  int n_targets = 0;
   for (int s = 0; s < ss.n; ++s)
-    if (tindex[s] == 0) { tindex[s] = (int)targets.size(); targets.push_back(s); }
-  const int n_targets = (int)targets.size();
+    if (tindex[s] == 0) { tindex[s] = n_targets; targets[n_targets++] = s; }
 
   rc = ensure_slots(h, n_targets);
   if (rc) return rc;
@@ -623,7 +628,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
 
   if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
   cudaStream_t st = h->stream;
-  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets.data(), sizeof(int) * n_targets,
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets, sizeof(int) * n_targets,
                          cudaMemcpyHostToDevice, st));
   int launches = 0;
   // events: 0 = start; per wave w: 1+5w tables begin, +1 tables end (table stream),
@@ -650,7 +655,8 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   // per distinct window; sinf/cosf from the host libm like Rotation2Df does.
   std::map<std::pair<double, double>, std::pair<int, int>> rot_cache;
   std::vector<Rotation> rots;
-  std::vector<PairWork> work(n_pairs);
+  std::vector<PairWork>& work = h->plan_work;
+  work.resize(n_pairs);
   int max_rot = 0;
   for (int p = 0; p < n_pairs; ++p) {
     auto key = std::make_pair(rot_min[p], rot_max[p]);
@@ -677,12 +683,15 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   }
 
   // ---- group the pairs by target (counting sort over the target index, stable)
-  std::vector<int> first_pair(n_targets + 1, 0);  // index into `sorted` of each target's first pair
+  std::vector<int>& first_pair = h->plan_first_pair;  // index into `sorted` of each target's first pair
+  first_pair.assign(n_targets + 1, 0);
   for (int p = 0; p < n_pairs; ++p) ++first_pair[tindex[b_ids[p]] + 1];
   for (int t = 0; t < n_targets; ++t) first_pair[t + 1] += first_pair[t];
-  std::vector<PairWork> sorted(n_pairs);
+  if ((rc = h->sorted_pin.reserve(n_pairs))) return rc;
+  PairWork* sorted = h->sorted_pin.p;
   {
-    std::vector<int> fill(first_pair.begin(), first_pair.end() - 1);
+    std::vector<int>& fill = h->plan_fill;
+    fill.assign(first_pair.begin(), first_pair.end() - 1);
     for (int p = 0; p < n_pairs; ++p) {
       const int t = tindex[b_ids[p]];
       PairWork& w = sorted[fill[t]++];
@@ -735,7 +744,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
   if ((rc = h->rots_dev.reserve(rots.size()))) return rc;
   if ((rc = h->results_dev.reserve(n_pairs))) return rc;
-  CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted.data(), sizeof(PairWork) * n_pairs,
+  CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted, sizeof(PairWork) * n_pairs,
                          cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
                          cudaMemcpyHostToDevice, st));
@@ -760,12 +769,15 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     if (next < n_waves && (rc = issue_tables(next))) return rc;
   }
   CU_TRY(cudaGetLastError());
-  std::vector<PairResult> res(n_pairs);
-  CU_TRY(cudaMemcpyAsync(res.data(), h->results_dev.p, sizeof(PairResult) * n_pairs,
+  if ((rc = h->results_pin.reserve(n_pairs))) return rc;
+  if ((rc = h->spec_counts_pin.reserve(2 * (size_t)n_waves))) return rc;
+  PairResult* res = h->results_pin.p;
+  int* spec_counts = h->spec_counts_pin.p;
+  for (int k = 0; k < 2 * n_waves; ++k) spec_counts[k] = 0;
+  CU_TRY(cudaMemcpyAsync(res, h->results_dev.p, sizeof(PairResult) * n_pairs,
                          cudaMemcpyDeviceToHost, st));
-  std::vector<int> spec_counts(2 * (size_t)n_waves, 0);
   if (!rf_serial)
-    CU_TRY(cudaMemcpyAsync(spec_counts.data(), h->spec_counters_dev.p, sizeof(int) * 2 * n_waves,
+    CU_TRY(cudaMemcpyAsync(spec_counts, h->spec_counters_dev.p, sizeof(int) * 2 * n_waves,
                            cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
 

@@ -93,6 +93,25 @@ struct DevBuf {
   void release() { cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// Pinned host staging that only grows: the per-call lists go H2D and the results
+// come D2H through it, so a steady-state call allocates nothing on the host and
+// its copies are true asynchronous DMA.
+template <typename T>
+struct PinBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return NAUTILUS_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    const size_t want = std::max(n + n / 4, (size_t)16);
+    CU_TRY(cudaHostAlloc((void**)&p, sizeof(T) * want, cudaHostAllocDefault));
+    cap = want;
+    return NAUTILUS_OK;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
 }  // namespace csmh
 
 struct NautilusCsm;
@@ -158,6 +177,13 @@ struct NautilusCsm {
   DevBuf<PairWork> pairs_dev;
   DevBuf<Rotation> rots_dev;
   DevBuf<PairResult> results_dev;
+  // host-side planning scratch of match_batch, kept between calls
+  PinBuf<int> targets_pin;
+  PinBuf<PairWork> sorted_pin;
+  PinBuf<PairResult> results_pin;
+  PinBuf<int> spec_counts_pin;
+  std::vector<int> plan_tindex, plan_first_pair, plan_fill;
+  std::vector<PairWork> plan_work;
   DevBuf<double> chunk_best_dev;
   DevBuf<int> chunk_rot_dev;
   DevBuf<SpecPair> spec_pairs_dev;

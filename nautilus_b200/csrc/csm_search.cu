@@ -80,7 +80,7 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 #define LS_PREF 0
 #endif
 #ifndef LS_RUNLOOP   // points per iteration of the add loop (4 + tails, or 2 + tail)
-#define LS_RUNLOOP 4
+#define LS_RUNLOOP 2
 #endif
 constexpr int LS_WARPS = LS_WARPS_N;
 constexpr int LS_THREADS = LS_WARPS * 32;
