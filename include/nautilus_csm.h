@@ -23,6 +23,11 @@
  *   - tables are double, x fastest: values[x + y * width]
  *     (CImg<double>, CorrelativeScanMatcher.h:31-39).
  *   - all pointers are HOST pointers unless a name ends in _dev.
+ *   - threading: the reference object is stateless and is called from OpenMP
+ *     threads (CorrelativeScanMatcher.cc:381-386, bag_avg_matcher.cc:104-141).
+ *     Every call that takes a handle locks it for the duration of the call and
+ *     selects the handle's device for the calling thread: concurrent callers of
+ *     one handle are serialised, different handles run concurrently.
  */
 #ifndef NAUTILUS_CSM_H_
 #define NAUTILUS_CSM_H_
