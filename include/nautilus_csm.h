@@ -274,6 +274,37 @@ int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_
  * visited duplicate).  out: one entry per uploaded point, scan by scan. */
 int nautilus_nn_self_index(NautilusCsm* h, int32_t* out);
 
+/* ---- the matching -> residual chain without a host round trip ---------------
+ * Solver::AddLidarResiduals (src/optimization/solver.cc:297-318) calls
+ * GetPointToPointMatching for a pair and hands the PointCorrespondences to a
+ * LIDAR*Residual cost function, which Ceres then evaluates many times while the
+ * poses move.  The three calls below keep the correspondences on the device
+ * between those steps: only counts come back from the search, and every
+ * evaluation moves poses in, residuals / Jacobians out. */
+
+/* Normals of the uploaded scan set, one (x, y) per point in upload order: the
+ * KDNodeValue::normal of every tree node, which the reference fills at load time
+ * (src/util/kdtree.cc:29, NormalComputation::GetNormals; slam_types.h:57-75). */
+int nautilus_nn_upload_normals(NautilusCsm* h, const float* normals_xy);
+
+/* nautilus_nn_match_batch whose result stays on the device as the resident
+ * correspondence set: for every pair the matched source points in source order
+ * (the order of AddCorrespondence, data_structures.h:89-99), each with its target
+ * point and the two normals GetPointNormal would return (solver.cc:67-77).
+ * corr_offsets: n_pairs + 1 entries, filled by the call (correspondences per
+ * pair, prefix sums).  A later call replaces the set. */
+int nautilus_nn_match_resident(NautilusCsm* h, const int32_t* src_ids, const int32_t* tgt_ids,
+                               const float* src_to_tgt, double threshold, int32_t n_pairs,
+                               int64_t* corr_offsets);
+
+/* nautilus_residuals_eval over the resident correspondence set: one residual
+ * block per pair of the last nautilus_nn_match_resident, source_poses /
+ * target_poses = 3 doubles (x, y, theta) per pair.  Output layout as
+ * nautilus_residuals_eval; jac_* may be null.  Repeatable with new poses. */
+int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind, const double* source_poses,
+                                     const double* target_poses, double* residuals,
+                                     double* jac_source, double* jac_target);
+
 /* Kernel time of the last nautilus_nn_match_batch (CUDA events) and how many of
  * its queries took the exact tree walk instead of the grid. */
 int nautilus_nn_last_stats(const NautilusCsm* h, float* ms_kernel, uint64_t* n_walked);

@@ -62,6 +62,7 @@ EXPORTS = [
     "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_regular_check",
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
+    "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
     "nautilus_csm_upload_ranges", "nautilus_csm_download_scans", "nautilus_lc_scatter_scores",
     "nautilus_lc_candidates", "nautilus_csm_frontend_last_ms", "nautilus_residuals_eval", "nautilus_residuals_last_ms",
 ]
@@ -130,6 +131,9 @@ def lib():
     L.nautilus_csm_last_timings.argtypes = [vp, C.POINTER(Timings)]
     L.nautilus_csm_uncertainty.argtypes = [vp, vp, i64, vp, i64, i32, d, vp]
     L.nautilus_csm_regular_check.argtypes = [vp, i64, u64, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
+    L.nautilus_nn_upload_normals.argtypes = [vp, vp]
+    L.nautilus_nn_match_resident.argtypes = [vp, vp, vp, vp, d, i32, vp]
+    L.nautilus_residuals_eval_resident.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.nautilus_nn_build.argtypes = [vp, d]
     L.nautilus_nn_pose_transform.restype = None
     L.nautilus_nn_pose_transform.argtypes = [vp, vp, vp]

@@ -21,6 +21,9 @@ void NnState::release() {
   cudaFree(pad_off); cudaFree(sorted_pts); cudaFree(skip_val); cudaFree(skip_dim);
   cudaFree(bucket_start); cudaFree(nodes); cudaFree(self_idx); cudaFree(pairs);
   cudaFree(match_idx); cudaFree(match_dist); cudaFree(counters);
+  cudaFree(normals); cudaFree(corr_cnt); cudaFree(corr_off); cudaFree(corr);
+  normals = nullptr; corr_cnt = nullptr; corr_off = nullptr; corr = nullptr;
+  corr_pairs_cap = corr_cap = 0; corr_pairs = 0;
   pad_off = nullptr; sorted_pts = nullptr; skip_val = nullptr; skip_dim = nullptr;
   bucket_start = nullptr; nodes = nullptr; self_idx = nullptr; pairs = nullptr;
   match_idx = nullptr; match_dist = nullptr; counters = nullptr;
@@ -272,6 +275,44 @@ int nautilus_nn_self_index(NautilusCsm* h, int32_t* out) {
   return NAUTILUS_OK;
 }
 
+// Validates a batch, uploads its work list and launches the search; the indices
+// stay in nn.match_idx (one per source point, pair p at offsets[p]).
+static int nn_match_launch(NautilusCsm* h, const int32_t* src_ids, const int32_t* tgt_ids,
+                           const float* src_to_tgt, double threshold, int32_t n_pairs,
+                           bool want_dist, int64_t* offsets, long long* n_queries) {
+  NnState& nn = h->nn;
+  const ScanSet& ss = h->user_scans;
+  std::vector<NnPair> pairs(n_pairs);
+  long long run = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    if (src_ids[p] < 0 || src_ids[p] >= ss.n || tgt_ids[p] < 0 || tgt_ids[p] >= ss.n)
+      return fail(NAUTILUS_EINVAL, "scan id out of range");
+    pairs[p].src = src_ids[p];
+    pairs[p].tgt = tgt_ids[p];
+    memcpy(pairs[p].m, src_to_tgt + 6 * (size_t)p, sizeof(float) * 6);
+    pairs[p].out = run;
+    run += ss.host_offsets[src_ids[p] + 1] - ss.host_offsets[src_ids[p]];
+    if (offsets) offsets[p + 1] = run;
+  }
+  int rc = reserve_out(nn, n_pairs, (size_t)run);
+  if (rc) return rc;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(nn.pairs, pairs.data(), sizeof(NnPair) * n_pairs, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemsetAsync(nn.counters, 0, sizeof(unsigned long long) * 4, st));
+  while (h->events.size() < 2) {
+    cudaEvent_t e;
+    CU_TRY(cudaEventCreate(&e));
+    h->events.push_back(e);
+  }
+  CU_TRY(cudaEventRecord(h->events[0], st));
+  launch_nn_match(make_index(h), nn.pairs, n_pairs, nn.max_points, (float)threshold, threshold,
+                  nn.match_idx, want_dist ? nn.match_dist : nullptr, nn.counters, st);
+  CU_TRY(cudaEventRecord(h->events[1], st));
+  CU_TRY(cudaGetLastError());
+  *n_queries = run;
+  return NAUTILUS_OK;
+}
+
 int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_t* tgt_ids,
                             const float* src_to_tgt, double threshold, int32_t n_pairs,
                             int32_t* match_idx, float* match_dist, int64_t* offsets) {
@@ -288,34 +329,11 @@ int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_
   if (!src_ids || !tgt_ids || !src_to_tgt || !match_idx || !offsets)
     return fail(NAUTILUS_EINVAL, "null argument");
   CU_TRY(cudaSetDevice(h->device));
-  const ScanSet& ss = h->user_scans;
-  std::vector<NnPair> pairs(n_pairs);
   long long run = 0;
-  for (int p = 0; p < n_pairs; ++p) {
-    if (src_ids[p] < 0 || src_ids[p] >= ss.n || tgt_ids[p] < 0 || tgt_ids[p] >= ss.n)
-      return fail(NAUTILUS_EINVAL, "scan id out of range");
-    pairs[p].src = src_ids[p];
-    pairs[p].tgt = tgt_ids[p];
-    memcpy(pairs[p].m, src_to_tgt + 6 * (size_t)p, sizeof(float) * 6);
-    pairs[p].out = run;
-    run += ss.host_offsets[src_ids[p] + 1] - ss.host_offsets[src_ids[p]];
-    offsets[p + 1] = run;
-  }
-  int rc = reserve_out(nn, n_pairs, (size_t)run);
+  int rc = nn_match_launch(h, src_ids, tgt_ids, src_to_tgt, threshold, n_pairs, match_dist != nullptr,
+                           offsets, &run);
   if (rc) return rc;
   cudaStream_t st = h->stream;
-  CU_TRY(cudaMemcpyAsync(nn.pairs, pairs.data(), sizeof(NnPair) * n_pairs, cudaMemcpyHostToDevice, st));
-  CU_TRY(cudaMemsetAsync(nn.counters, 0, sizeof(unsigned long long) * 4, st));
-  while (h->events.size() < 2) {
-    cudaEvent_t e;
-    CU_TRY(cudaEventCreate(&e));
-    h->events.push_back(e);
-  }
-  CU_TRY(cudaEventRecord(h->events[0], st));
-  launch_nn_match(make_index(h), nn.pairs, n_pairs, nn.max_points, (float)threshold, threshold,
-                  nn.match_idx, match_dist ? nn.match_dist : nullptr, nn.counters, st);
-  CU_TRY(cudaEventRecord(h->events[1], st));
-  CU_TRY(cudaGetLastError());
   if (run > 0) {
     CU_TRY(cudaMemcpyAsync(match_idx, nn.match_idx, sizeof(int) * run, cudaMemcpyDeviceToHost, st));
     if (match_dist)
@@ -325,6 +343,78 @@ int nautilus_nn_match_batch(NautilusCsm* h, const int32_t* src_ids, const int32_
                          cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
   cudaEventElapsedTime(&nn.ms_last, h->events[0], h->events[1]);
+  return NAUTILUS_OK;
+}
+
+int nautilus_nn_upload_normals(NautilusCsm* h, const float* normals_xy) {
+  if (!h || !normals_xy) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
+  NnState& nn = h->nn;
+  if (!nn.built) return fail(NAUTILUS_ESTATE, "nautilus_nn_build has not run for this scan set");
+  const long long total = h->user_scans.host_offsets[h->user_scans.n];
+  cudaFree(nn.normals);
+  nn.normals = nullptr;
+  CU_TRY(cudaMalloc(&nn.normals, sizeof(float2) * std::max<long long>(total, 1)));
+  CU_TRY(cudaMemcpyAsync(nn.normals, normals_xy, sizeof(float2) * total, cudaMemcpyHostToDevice,
+                         h->stream));
+  CU_TRY(cudaStreamSynchronize(h->stream));
+  return NAUTILUS_OK;
+}
+
+int nautilus_nn_match_resident(NautilusCsm* h, const int32_t* src_ids, const int32_t* tgt_ids,
+                               const float* src_to_tgt, double threshold, int32_t n_pairs,
+                               int64_t* corr_offsets) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
+  if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
+  NnState& nn = h->nn;
+  if (!nn.built) return fail(NAUTILUS_ESTATE, "nautilus_nn_build has not run for this scan set");
+  if (!(threshold > 0) || threshold > nn.cell)
+    return fail(NAUTILUS_EINVAL, "threshold must be in (0, cell_size of nautilus_nn_build]");
+  if (!corr_offsets) return fail(NAUTILUS_EINVAL, "null argument");
+  corr_offsets[0] = 0;
+  nn.ms_last = 0; nn.walked_last = 0; nn.corr_pairs = 0;
+  if (n_pairs == 0) return NAUTILUS_OK;
+  if (!src_ids || !tgt_ids || !src_to_tgt) return fail(NAUTILUS_EINVAL, "null argument");
+  if (h->user_scans.host_offsets[h->user_scans.n] > 2147483647LL)
+    return fail(NAUTILUS_EINVAL, "scan set too large for 32-bit correspondence indices");
+  long long run = 0;
+  int rc = nn_match_launch(h, src_ids, tgt_ids, src_to_tgt, threshold, n_pairs, false, nullptr, &run);
+  if (rc) return rc;
+  cudaStream_t st = h->stream;
+  if ((size_t)n_pairs > nn.corr_pairs_cap) {
+    cudaFree(nn.corr_cnt); cudaFree(nn.corr_off);
+    nn.corr_cnt = nullptr; nn.corr_off = nullptr; nn.corr_pairs_cap = 0;
+    const size_t want = std::max<size_t>(n_pairs, 64);
+    CU_TRY(cudaMalloc(&nn.corr_cnt, sizeof(int) * want));
+    CU_TRY(cudaMalloc(&nn.corr_off, sizeof(long long) * (want + 1)));
+    nn.corr_pairs_cap = want;
+  }
+  const NnIndex ix = make_index(h);
+  launch_corr_count(ix, nn.pairs, n_pairs, nn.match_idx, nn.corr_cnt, st);
+  std::vector<int> cnt(n_pairs);
+  CU_TRY(cudaMemcpyAsync(cnt.data(), nn.corr_cnt, sizeof(int) * n_pairs, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(&nn.walked_last, nn.counters, sizeof(unsigned long long),
+                         cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  nn.corr_off_host.assign((size_t)n_pairs + 1, 0);
+  for (int p = 0; p < n_pairs; ++p) nn.corr_off_host[p + 1] = nn.corr_off_host[p] + cnt[p];
+  const long long n_corr = nn.corr_off_host[n_pairs];
+  if ((size_t)n_corr > nn.corr_cap) {
+    cudaFree(nn.corr);
+    nn.corr = nullptr; nn.corr_cap = 0;
+    const size_t want = std::max<size_t>((size_t)n_corr, 1024);
+    CU_TRY(cudaMalloc(&nn.corr, sizeof(int4) * want));
+    nn.corr_cap = want;
+  }
+  CU_TRY(cudaMemcpyAsync(nn.corr_off, nn.corr_off_host.data(), sizeof(long long) * ((size_t)n_pairs + 1),
+                         cudaMemcpyHostToDevice, st));
+  launch_corr_write(ix, nn.pairs, n_pairs, nn.match_idx, nn.self_idx, nn.corr_off, nn.corr, st);
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&nn.ms_last, h->events[0], h->events[1]);
+  for (int p = 0; p <= n_pairs; ++p) corr_offsets[p] = nn.corr_off_host[p];
+  nn.corr_pairs = n_pairs;
   return NAUTILUS_OK;
 }
 

@@ -363,6 +363,84 @@ __global__ void __launch_bounds__(NM_THREADS) nn_match_kernel(
   if (walked && counters) atomicAdd(counters, walked);
 }
 
+// ---------------------------------------------------------------------------
+// Resident correspondences: the matched source points of a pair, compacted in
+// source order (the order Solver::GetPointToPointMatching appends them,
+// solver.cc:146-170).  One block per pair; ballot + running count keep the order.
+// ---------------------------------------------------------------------------
+constexpr int CC_THREADS = 128;
+
+__global__ void __launch_bounds__(CC_THREADS) corr_count_kernel(
+    NnIndex ix, const NnPair* __restrict__ pairs, const int* __restrict__ match_idx,
+    int* __restrict__ cnt) {
+  const NnPair pr = pairs[blockIdx.x];
+  const int n = (int)(ix.offsets[pr.src + 1] - ix.offsets[pr.src]);
+  const int* m = match_idx + pr.out;
+  int c = 0;
+  for (int i = threadIdx.x; i < n; i += CC_THREADS) c += m[i] >= 0;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  __shared__ int s_c[CC_THREADS / 32];
+  if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < CC_THREADS / 32; ++w) t += s_c[w];
+    cnt[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(CC_THREADS) corr_write_kernel(
+    NnIndex ix, const NnPair* __restrict__ pairs, const int* __restrict__ match_idx,
+    const int* __restrict__ self_idx, const long long* __restrict__ corr_off,
+    int4* __restrict__ corr) {
+  const NnPair pr = pairs[blockIdx.x];
+  const long long so = ix.offsets[pr.src], to = ix.offsets[pr.tgt];
+  const int n = (int)(ix.offsets[pr.src + 1] - so);
+  const int* m = match_idx + pr.out;
+  int4* out = corr + corr_off[blockIdx.x];
+  __shared__ int s_w[CC_THREADS / 32];
+  __shared__ int s_base;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i0 = 0; i0 < n; i0 += CC_THREADS) {
+    const int i = i0 + threadIdx.x;
+    const int t = i < n ? m[i] : -1;
+    const unsigned b = __ballot_sync(0xffffffffu, t >= 0);
+    if (lane == 0) s_w[warp] = __popc(b);
+    __syncthreads();
+    int before = s_base;
+    for (int w = 0; w < warp; ++w) before += s_w[w];
+    if (t >= 0) {
+      const int k = before + __popc(b & ((1u << lane) - 1u));
+      const long long si = so + i, ti = to + t;
+      // the normal of a point is the one stored with the tree node GetPointNormal
+      // finds for it (solver.cc:67-77): self_idx
+      out[k] = make_int4((int)si, (int)ti, (int)(so + self_idx[si]), (int)(to + self_idx[ti]));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t_all = 0;
+      for (int w = 0; w < CC_THREADS / 32; ++w) t_all += s_w[w];
+      s_base += t_all;
+    }
+    __syncthreads();
+  }
+}
+
+void launch_corr_count(const NnIndex& ix, const NnPair* pairs, int n_pairs, const int* match_idx,
+                       int* cnt, cudaStream_t stream) {
+  if (n_pairs > 0) corr_count_kernel<<<n_pairs, CC_THREADS, 0, stream>>>(ix, pairs, match_idx, cnt);
+}
+
+void launch_corr_write(const NnIndex& ix, const NnPair* pairs, int n_pairs, const int* match_idx,
+                       const int* self_idx, const long long* corr_off, int4* corr,
+                       cudaStream_t stream) {
+  if (n_pairs > 0)
+    corr_write_kernel<<<n_pairs, CC_THREADS, 0, stream>>>(ix, pairs, match_idx, self_idx, corr_off,
+                                                          corr);
+}
+
 void launch_nn_match(const NnIndex& ix, const NnPair* pairs, int n_pairs, int max_tgt_points,
                      float thr_f, double thr_d, int* match_idx, float* match_dist,
                      unsigned long long* counters, cudaStream_t stream) {

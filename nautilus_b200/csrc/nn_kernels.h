@@ -61,6 +61,16 @@ void launch_nn_match(const NnIndex& ix, const NnPair* pairs, int n_pairs, int ma
                      unsigned long long* counters, cudaStream_t stream);
 size_t nn_match_smem_bytes(int n_buckets, int max_points);
 
+// Resident correspondence set (AddCorrespondence order, data_structures.h:89-99):
+// per matched source point {source point, target point, source normal, target
+// normal} as indices into the scan set's point / normal arrays.
+// count: cnt[p] = matches of pair p.  write: corr[corr_off[p] ..] in source order.
+void launch_corr_count(const NnIndex& ix, const NnPair* pairs, int n_pairs, const int* match_idx,
+                       int* cnt, cudaStream_t stream);
+void launch_corr_write(const NnIndex& ix, const NnPair* pairs, int n_pairs, const int* match_idx,
+                       const int* self_idx, const long long* corr_off, int4* corr,
+                       cudaStream_t stream);
+
 }  // namespace csm
 
 namespace csmh {
@@ -85,6 +95,16 @@ struct NnState {
   float* match_dist = nullptr;
   size_t match_cap = 0;
   unsigned long long* counters = nullptr;
+  // resident chain: normals of the scan set, compacted correspondences of the last
+  // nautilus_nn_match_resident
+  float2* normals = nullptr;
+  int* corr_cnt = nullptr;
+  long long* corr_off = nullptr;
+  size_t corr_pairs_cap = 0;
+  int4* corr = nullptr;
+  size_t corr_cap = 0;
+  int corr_pairs = 0;                       // pairs of the resident set, 0 = none
+  std::vector<long long> corr_off_host;
   float ms_last = 0;
   unsigned long long walked_last = 0;
   void release();

@@ -28,21 +28,14 @@ struct ResidualArgs {
   int kind;                 // 0: point residual, 1: normal residual
 };
 
-__global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long n_corr) {
-  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n_corr) return;
-  // residual block of this correspondence: last b with offsets[b] <= k
-  int lo = 0, hi = a.n_blocks;
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (a.offsets[mid] <= k) lo = mid; else hi = mid;
-  }
-  const double xs = a.src_pose[3 * lo], ys = a.src_pose[3 * lo + 1], ths = a.src_pose[3 * lo + 2];
-  const double xt = a.tgt_pose[3 * lo], yt = a.tgt_pose[3 * lo + 1], tht = a.tgt_pose[3 * lo + 2];
+// Residuals and Jacobians of correspondence k of residual block `blk`.
+__device__ __forceinline__ void residual_math(const ResidualArgs& a, long long k, int blk, float2 pf,
+                                              float2 qf, float2 nsf, float2 ntf) {
+  const double xs = a.src_pose[3 * blk], ys = a.src_pose[3 * blk + 1], ths = a.src_pose[3 * blk + 2];
+  const double xt = a.tgt_pose[3 * blk], yt = a.tgt_pose[3 * blk + 1], tht = a.tgt_pose[3 * blk + 2];
   double ss, cs, st, ct;
   sincos(ths, &ss, &cs);
   sincos(tht, &st, &ct);
-  const float2 pf = a.sp[k], qf = a.tp[k];
   const double px = pf.x, py = pf.y, qx = qf.x, qy = qf.y;
   // w = R(th_s) p + t_s - t_t (world frame, relative to the target origin)
   const double rx = cs * px - ss * py, ry = ss * px + cs * py;
@@ -64,7 +57,6 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long
 #pragma unroll
     for (int c = 0; c < 6; ++c) { g0[c] = -dx[c]; g1[c] = -dy[c]; }
   } else {                        // n_t . (p' - q),  n_s . (q - p')
-    const float2 nsf = a.sn[k], ntf = a.tn[k];
     const double nsx = nsf.x, nsy = nsf.y, ntx = ntf.x, nty = ntf.y;
     r0 = ntx * (ppx - qx) + nty * (ppy - qy);
     r1 = nsx * (qx - ppx) + nsy * (qy - ppy);
@@ -83,6 +75,38 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long
     double* j = a.jac_t + 6 * k;
     j[0] = g0[3]; j[1] = g0[4]; j[2] = g0[5]; j[3] = g1[3]; j[4] = g1[4]; j[5] = g1[5];
   }
+}
+
+// residual block of correspondence k: last b with offsets[b] <= k
+__device__ __forceinline__ int block_of(const long long* offsets, int n_blocks, long long k) {
+  int lo = 0, hi = n_blocks;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (offsets[mid] <= k) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long n_corr) {
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_corr) return;
+  const int blk = block_of(a.offsets, a.n_blocks, k);
+  const float2 z = make_float2(0.f, 0.f);
+  residual_math(a, k, blk, a.sp[k], a.tp[k], a.kind ? a.sn[k] : z, a.kind ? a.tn[k] : z);
+}
+
+// The same over the resident correspondence set of nautilus_nn_match_resident:
+// points and normals are gathered from the scan set on the device.
+__global__ void __launch_bounds__(256) residual_resident_kernel(
+    ResidualArgs a, long long n_corr, const int4* __restrict__ corr,
+    const float2* __restrict__ points, const float2* __restrict__ normals) {
+  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_corr) return;
+  const int blk = block_of(a.offsets, a.n_blocks, k);
+  const int4 c = corr[k];
+  const float2 z = make_float2(0.f, 0.f);
+  residual_math(a, k, blk, points[c.x], points[c.y], a.kind ? normals[c.z] : z,
+                a.kind ? normals[c.w] : z);
 }
 
 }  // namespace csm
@@ -146,6 +170,59 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
   csm::residual_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, n);
+  cudaEventRecord(e1, st);
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(residuals, d_res, b_res, cudaMemcpyDeviceToHost, st));
+  if (jac_source) CU_TRY(cudaMemcpyAsync(jac_source, d_js, b_jac, cudaMemcpyDeviceToHost, st));
+  if (jac_target) CU_TRY(cudaMemcpyAsync(jac_target, d_jt, b_jac, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  cudaEventElapsedTime(&h->residual_kernel_ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return NAUTILUS_OK;
+}
+
+extern "C" int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind,
+                                                const double* source_poses,
+                                                const double* target_poses, double* residuals,
+                                                double* jac_source, double* jac_target) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
+  if (kind != 0 && kind != 1) return fail(NAUTILUS_EINVAL, "kind must be 0 (point) or 1 (normal)");
+  NnState& nn = h->nn;
+  if (!nn.built || nn.corr_pairs <= 0)
+    return fail(NAUTILUS_ESTATE, "no resident correspondence set: call nautilus_nn_match_resident");
+  if (kind == 1 && !nn.normals)
+    return fail(NAUTILUS_ESTATE, "normal residuals need nautilus_nn_upload_normals");
+  const int n_blocks = nn.corr_pairs;
+  const long long n = nn.corr_off_host[n_blocks];
+  if (n == 0) return NAUTILUS_OK;
+  if (!source_poses || !target_poses || !residuals) return fail(NAUTILUS_EINVAL, "null argument");
+  cudaStream_t st = h->stream;
+  const size_t b_pose = sizeof(double) * 3 * (size_t)n_blocks;
+  const size_t b_res = sizeof(double) * 2 * (size_t)n;
+  const size_t b_jac = sizeof(double) * 6 * (size_t)n;
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const size_t total = 2 * up(b_pose) + up(b_res) + 2 * up(b_jac);
+  int rc = h->residual_arena.reserve(total);
+  if (rc) return rc;
+  unsigned char* base = h->residual_arena.p;
+  size_t at = 0;
+  auto take = [&](size_t bytes) { unsigned char* p = base + at; at += up(bytes); return p; };
+  double* d_sp = (double*)take(b_pose); double* d_tp = (double*)take(b_pose);
+  double* d_res = (double*)take(b_res);
+  double* d_js = (double*)take(b_jac); double* d_jt = (double*)take(b_jac);
+  CU_TRY(cudaMemcpyAsync(d_sp, source_poses, b_pose, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(d_tp, target_poses, b_pose, cudaMemcpyHostToDevice, st));
+  csm::ResidualArgs a;
+  a.src_pose = d_sp; a.tgt_pose = d_tp; a.offsets = nn.corr_off; a.n_blocks = n_blocks;
+  a.sp = a.tp = a.sn = a.tn = nullptr;
+  a.res = d_res; a.jac_s = jac_source ? d_js : nullptr; a.jac_t = jac_target ? d_jt : nullptr;
+  a.kind = kind;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  csm::residual_resident_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+      a, n, nn.corr, h->user_scans.points, nn.normals);
   cudaEventRecord(e1, st);
   CU_TRY(cudaGetLastError());
   CU_TRY(cudaMemcpyAsync(residuals, d_res, b_res, cudaMemcpyDeviceToHost, st));

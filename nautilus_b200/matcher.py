@@ -304,6 +304,26 @@ class CorrelativeScanMatcher:
         idx = idx[:total]
         return (idx, offsets, dist[:total]) if with_dist else (idx, offsets)
 
+    def nn_upload_normals(self, normals) -> None:
+        """One normal per uploaded point (KDNodeValue::normal of the reference's tree nodes)."""
+        nrm = np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 2)
+        if len(nrm) != int(self._scan_sizes.sum()):
+            raise ValueError("one normal per uploaded point")
+        check(self._L.nautilus_nn_upload_normals(self._h, ptr(nrm)))
+
+    def nn_match_resident(self, src_ids, tgt_ids, transforms, threshold: float) -> np.ndarray:
+        """The search of nn_match_batch with the correspondences kept on the device
+        (source order, as GetPointToPointMatching appends them); -> correspondence
+        offsets int64 [n_pairs + 1]."""
+        src_ids = np.ascontiguousarray(src_ids, dtype=np.int32)
+        tgt_ids = np.ascontiguousarray(tgt_ids, dtype=np.int32)
+        n = len(src_ids)
+        m = np.ascontiguousarray(transforms, dtype=np.float32).reshape(n, 6)
+        offsets = np.zeros(n + 1, np.int64)
+        check(self._L.nautilus_nn_match_resident(self._h, ptr(src_ids), ptr(tgt_ids), ptr(m),
+                                                 float(threshold), n, ptr(offsets)))
+        return offsets
+
     def nn_self_index(self) -> np.ndarray:
         out = np.empty(max(int(self._scan_sizes.sum()), 1), np.int32)
         check(self._L.nautilus_nn_self_index(self._h, ptr(out)))

@@ -37,6 +37,26 @@ def evaluate_residual_blocks(matcher, kind, source_poses, target_poses, offsets,
     return (res, js, jt) if jacobians else res
 
 
+def evaluate_resident_blocks(matcher, kind, source_poses, target_poses, corr_offsets,
+                             jacobians: bool = True):
+    """evaluate_residual_blocks over the correspondence set nn_match_resident left on
+    the device (one block per pair of that call): only poses go in and residuals /
+    Jacobians come out.  Repeatable with new poses, as Ceres re-evaluates a cost function."""
+    sp = np.ascontiguousarray(source_poses, np.float64).reshape(-1, 3)
+    tp = np.ascontiguousarray(target_poses, np.float64).reshape(-1, 3)
+    nb = len(corr_offsets) - 1
+    if len(sp) != nb or len(tp) != nb:
+        raise ValueError("one source and one target pose per block")
+    n = int(corr_offsets[-1])
+    res = np.zeros((n, 2), np.float64)
+    js = np.zeros((n, 2, 3), np.float64) if jacobians else None
+    jt = np.zeros((n, 2, 3), np.float64) if jacobians else None
+    o = lambda a: None if a is None else ptr(a)  # noqa: E731
+    check(matcher._L.nautilus_residuals_eval_resident(matcher._h, int(kind), ptr(sp), ptr(tp),
+                                                      ptr(res), o(js), o(jt)))
+    return (res, js, jt) if jacobians else res
+
+
 def last_kernel_ms(matcher) -> float:
     ms = C.c_float()
     check(matcher._L.nautilus_residuals_last_ms(matcher._h, C.byref(ms)))

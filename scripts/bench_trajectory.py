@@ -25,7 +25,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from nautilus_b200 import CorrelativeScanMatcher, synth_ranges as sr  # noqa: E402
-from nautilus_b200.residuals import evaluate_residual_blocks, last_kernel_ms  # noqa: E402
+from nautilus_b200.residuals import (evaluate_residual_blocks, evaluate_resident_blocks,  # noqa: E402
+                                     last_kernel_ms)
 
 HALF_W, HALF_H = 30.0, 20.0
 
@@ -177,13 +178,13 @@ def main():
             ms_k += m.nn_last_stats()["ms_kernel"]
             tot_pairs += len(src[sl]); tot_q += len(idx)
             if w == 10 and c0 == 0:
-                last = (src[sl], tgt[sl], idx, offs)
+                last = (src[sl], tgt[sl], idx, offs, tr[sl])
     st["nn_growing_window"] = {"pair_matchings": int(tot_pairs), "queries": int(tot_q), "ms_kernel": ms_k,
                                "ms_wall_with_copies": ms_w, "pairs_per_sec_kernel": tot_pairs / (ms_k * 1e-3),
                                "queries_per_sec_kernel": tot_q / (ms_k * 1e-3)}
 
     # residual blocks of one 60k-pair slice of the widest round (point residuals)
-    src, tgt, idx, offs = last
+    src, tgt, idx, offs, tr_last = last
     xy, soffs = m.download_scans()
     t0 = time.perf_counter()
     hit = idx >= 0
@@ -198,6 +199,26 @@ def main():
     st["residual_blocks"] = {"blocks": int(len(src)), "correspondences": int(len(sp)),
                              "ms_host_gather": host_ms, "ms_wall_with_copies": 1e3 * (time.perf_counter() - t0),
                              "ms_kernel": last_kernel_ms(m), "rms_residual_m": float(np.sqrt((res ** 2).mean()))}
+
+    # the same slice with the correspondences kept on the device (nn_match_resident ->
+    # evaluate_resident_blocks): only counts, poses and residuals / Jacobians cross PCIe
+    t0 = time.perf_counter()
+    co = m.nn_match_resident(src, tgt, tr_last, 0.25)
+    ms_match = 1e3 * (time.perf_counter() - t0)
+    ms_match_k = m.nn_last_stats()["ms_kernel"]
+    t0 = time.perf_counter()
+    r_only = evaluate_resident_blocks(m, 0, est[src], est[tgt], co, jacobians=False)
+    ms_res = 1e3 * (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    r_all = evaluate_resident_blocks(m, 0, est[src], est[tgt], co)
+    ms_all = 1e3 * (time.perf_counter() - t0)
+    st["resident_chain"] = {"blocks": int(len(src)), "correspondences": int(co[-1]),
+                            "ms_match_wall": ms_match, "ms_match_kernel": ms_match_k,
+                            "ms_residuals_only_wall": ms_res, "ms_with_jacobians_wall": ms_all,
+                            "ms_kernel": last_kernel_ms(m),
+                            "identical_to_host_chain": bool(np.array_equal(co, roffs) and np.array_equal(r_only, res)
+                                                            and np.array_equal(r_all[1], js)
+                                                            and np.array_equal(r_all[2], jt))}
 
     if args.cpu:
         from oracle import ref

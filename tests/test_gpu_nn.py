@@ -136,3 +136,69 @@ def test_nn_errors_and_edges():
     with pytest.raises(CsmError):
         m.nn_match_batch([0], [0], ident, 0.25)
     m.close()
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_resident_chain_equals_host_chain(kind):
+    """nn_match_resident -> evaluate_resident_blocks (correspondences never leave the
+    device) against the host-buffer chain nn_match_batch -> AddCorrespondence gather ->
+    evaluate_residual_blocks, which is itself pinned to the oracles above: same
+    correspondences in the same order, residuals and Jacobians bit for bit.  Duplicate
+    points make the normal lookup go through GetPointNormal's self index."""
+    from nautilus_b200.point_matching import correspondences_from_matches
+    from nautilus_b200.residuals import evaluate_residual_blocks, evaluate_resident_blocks
+    xy, offs, poses = synth.make_scan_set(12, group=4, seed=9, n_beams=360, return_poses=True)
+    xy = xy.copy()
+    for s in range(12):               # a few exact duplicates per scan
+        o = int(offs[s])
+        if offs[s + 1] - o > 40:
+            xy[o + 30] = xy[o + 10]
+            xy[o + 31] = xy[o + 10]
+    rng = np.random.default_rng(3)
+    normals = rng.normal(size=xy.shape).astype(np.float32)
+    m = make_matcher(xy, offs, 0.25)
+    m.nn_upload_normals(normals)
+    src = np.asarray([0, 1, 2, 3, 5, 4, 8, 9, 10, 11, 0, 7], np.int32)
+    tgt = np.asarray([1, 0, 3, 2, 4, 5, 9, 8, 11, 10, 6, 7], np.int32)
+    tf = np.stack([pose_transform(poses[s], poses[t]) for s, t in zip(src, tgt)])
+    tf[10] = [1, 0, 1000, 0, 1, 1000]   # a pair without a single match: an empty block
+    # host chain
+    idx, out_offs = m.nn_match_batch(src, tgt, tf, 0.25)
+    cs = correspondences_from_matches(m, xy, offs, normals, poses, src, tgt, idx, out_offs)
+    counts = np.asarray([len(c.source_points) for c in cs], np.int64)
+    want_offs = np.concatenate([[0], np.cumsum(counts)])
+    cat = lambda k: np.concatenate([getattr(c, k) for c in cs])  # noqa: E731
+    sp, tp = poses[src] + rng.normal(scale=0.05, size=(len(src), 3)), poses[tgt]
+    want = evaluate_residual_blocks(m, kind, sp, tp, want_offs, cat("source_points"),
+                                    cat("target_points"), cat("source_normals"), cat("target_normals"))
+    # resident chain
+    corr_offs = m.nn_match_resident(src, tgt, tf, 0.25)
+    assert np.array_equal(corr_offs, want_offs)
+    assert corr_offs[-1] > 1000 and counts[10] == 0
+    got = evaluate_resident_blocks(m, kind, sp, tp, corr_offs)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    # re-evaluation with moved poses, residuals only (what a Ceres iteration does)
+    sp2 = sp + 0.01
+    r2 = evaluate_resident_blocks(m, kind, sp2, tp, corr_offs, jacobians=False)
+    w2 = evaluate_residual_blocks(m, kind, sp2, tp, want_offs, cat("source_points"), cat("target_points"),
+                                  cat("source_normals"), cat("target_normals"), jacobians=False)
+    assert np.array_equal(r2, w2)
+    m.close()
+
+
+def test_resident_chain_errors():
+    xy, offs = synth.make_scan_set(4, group=4, seed=2, n_beams=120)
+    m = make_matcher(xy, offs, 0.25)
+    from nautilus_b200.residuals import evaluate_resident_blocks
+    ident = np.asarray([1, 0, 0, 0, 1, 0], np.float32)
+    with pytest.raises(CsmError):     # nothing resident yet
+        evaluate_resident_blocks(m, 0, np.zeros((1, 3)), np.zeros((1, 3)), np.asarray([0, 1]))
+    co = m.nn_match_resident([0], [1], ident, 0.25)
+    with pytest.raises(CsmError):     # normal residuals need the normals
+        evaluate_resident_blocks(m, 1, np.zeros((1, 3)), np.zeros((1, 3)), co)
+    r = evaluate_resident_blocks(m, 0, np.zeros((1, 3)), np.zeros((1, 3)), co, jacobians=False)
+    assert r.shape == (int(co[-1]), 2)
+    co = m.nn_match_resident([], [], np.zeros((0, 6), np.float32), 0.25)
+    assert co.tolist() == [0]
+    m.close()
