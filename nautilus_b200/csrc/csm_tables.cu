@@ -364,6 +364,9 @@ __device__ __forceinline__ void st_gbl(double* p, double v) {
   asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
 
+#ifndef YP_PREF   // 1: y-pass causal sweep loads one chunk ahead (A/B knob)
+#define YP_PREF 0
+#endif
 constexpr int RC_MAXCH = 64;
 
 __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
@@ -599,6 +602,22 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     const int nch = (n_fwd + YC - 1) / YC;
     {
       const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
+#if YP_PREF
+      // the next chunk's loads are in flight while this chunk's recursion steps
+      double a[YC], an[YC];
+      y_load<YC>(a, p, stride, s_rows[0] & CMASK);
+      for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
+        ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
+        const int b0 = ci * YC, b1 = b0 + YC;
+        const unsigned nbits = ci + 1 < nch ? (s_rows[b1 >> 5] >> (b1 & 31)) & CMASK : 0u;
+        y_load<YC>(an, p + (size_t)YC * stride, stride, nbits);
+        const int nrow = n_fwd - b0;
+        if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
+        else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
+#pragma unroll
+        for (int u = 0; u < YC; ++u) a[u] = an[u];
+      }
+#else
       for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
         ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
         const int b0 = ci * YC;
@@ -609,6 +628,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
         if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
         else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
       }
+#endif
     }
     const bool at_edge = (m.ay1 == g.w - 1);
     double w0 = 0.0;
