@@ -305,6 +305,13 @@ int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind, const double*
                                      const double* target_poses, double* residuals,
                                      double* jac_source, double* jac_target);
 
+/* Page-locked host memory for large result arrays (residuals / Jacobians of
+ * nautilus_residuals_eval*, match indices): device -> host copies into it run at
+ * PCIe speed instead of through the driver's staging of pageable memory.  Any
+ * host pointer argument of this library may point into such a buffer. */
+int nautilus_host_alloc(uint64_t bytes, void** out);
+int nautilus_host_free(void* p);
+
 /* Kernel time of the last nautilus_nn_match_batch (CUDA events) and how many of
  * its queries took the exact tree walk instead of the grid. */
 int nautilus_nn_last_stats(const NautilusCsm* h, float* ms_kernel, uint64_t* n_walked);

@@ -62,6 +62,7 @@ EXPORTS = [
     "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_regular_check",
     "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
+    "nautilus_host_alloc", "nautilus_host_free",
     "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
     "nautilus_csm_upload_ranges", "nautilus_csm_download_scans", "nautilus_lc_scatter_scores",
     "nautilus_lc_candidates", "nautilus_csm_frontend_last_ms", "nautilus_residuals_eval", "nautilus_residuals_last_ms",
@@ -131,6 +132,8 @@ def lib():
     L.nautilus_csm_last_timings.argtypes = [vp, C.POINTER(Timings)]
     L.nautilus_csm_uncertainty.argtypes = [vp, vp, i64, vp, i64, i32, d, vp]
     L.nautilus_csm_regular_check.argtypes = [vp, i64, u64, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
+    L.nautilus_host_alloc.argtypes = [u64, C.POINTER(vp)]
+    L.nautilus_host_free.argtypes = [vp]
     L.nautilus_nn_upload_normals.argtypes = [vp, vp]
     L.nautilus_nn_match_resident.argtypes = [vp, vp, vp, vp, d, i32, vp]
     L.nautilus_residuals_eval_resident.argtypes = [vp, i32, vp, vp, vp, vp, vp]
@@ -158,3 +161,31 @@ def check(rc: int):
 
 def ptr(a: np.ndarray):
     return a.ctypes.data_as(C.c_void_p)
+
+
+class _PinnedBlock:
+    """Owner of one nautilus_host_alloc block; freed when the last array over it goes."""
+
+    def __init__(self, nbytes: int):
+        p = C.c_void_p()
+        check(lib().nautilus_host_alloc(int(nbytes), C.byref(p)))
+        self.p, self.nbytes = p, int(nbytes)
+
+    def __del__(self):
+        try:
+            if self.p:
+                lib().nautilus_host_free(self.p)
+        except Exception:  # interpreter shutdown
+            pass
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """np.empty over page-locked host memory (nautilus_host_alloc)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) if np.ndim(shape) else int(shape)
+    if n == 0:
+        return np.empty(shape, dtype)
+    blk = _PinnedBlock(n * dtype.itemsize)
+    buf = (C.c_char * blk.nbytes).from_address(blk.p.value)
+    buf._owner = blk  # the ctypes object (the array's base) keeps the block alive
+    return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)

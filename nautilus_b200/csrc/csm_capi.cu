@@ -551,6 +551,19 @@ int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* of
   return NAUTILUS_OK;
 }
 
+int nautilus_host_alloc(uint64_t bytes, void** out) {
+  if (!out) return fail(NAUTILUS_EINVAL, "null argument");
+  *out = nullptr;
+  if (bytes == 0) return NAUTILUS_OK;
+  CU_TRY(cudaHostAlloc(out, (size_t)bytes, cudaHostAllocPortable));
+  return NAUTILUS_OK;
+}
+
+int nautilus_host_free(void* p) {
+  if (p) CU_TRY(cudaFreeHost(p));
+  return NAUTILUS_OK;
+}
+
 int nautilus_csm_last_timings(const NautilusCsm* h, NautilusCsmTimings* out) {
   if (!h || !out) return fail(NAUTILUS_EINVAL, "null argument");
   NAUTILUS_GUARD(h);

@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import check, ptr
+from ._lib import check, pinned_empty, ptr
 
 POINT, NORMAL = 0, 1
 
@@ -38,7 +38,7 @@ def evaluate_residual_blocks(matcher, kind, source_poses, target_poses, offsets,
 
 
 def evaluate_resident_blocks(matcher, kind, source_poses, target_poses, corr_offsets,
-                             jacobians: bool = True):
+                             jacobians: bool = True, pinned: bool = False, out=None):
     """evaluate_residual_blocks over the correspondence set nn_match_resident left on
     the device (one block per pair of that call): only poses go in and residuals /
     Jacobians come out.  Repeatable with new poses, as Ceres re-evaluates a cost function."""
@@ -48,9 +48,13 @@ def evaluate_resident_blocks(matcher, kind, source_poses, target_poses, corr_off
     if len(sp) != nb or len(tp) != nb:
         raise ValueError("one source and one target pose per block")
     n = int(corr_offsets[-1])
-    res = np.zeros((n, 2), np.float64)
-    js = np.zeros((n, 2, 3), np.float64) if jacobians else None
-    jt = np.zeros((n, 2, 3), np.float64) if jacobians else None
+    if out is not None:          # buffers of an earlier call (a solver iterates on the same set)
+        res, js, jt = out
+    else:
+        new = pinned_empty if pinned else np.zeros   # pinned: D2H at PCIe speed (nautilus_host_alloc)
+        res = new((n, 2), np.float64)
+        js = new((n, 2, 3), np.float64) if jacobians else None
+        jt = new((n, 2, 3), np.float64) if jacobians else None
     o = lambda a: None if a is None else ptr(a)  # noqa: E731
     check(matcher._L.nautilus_residuals_eval_resident(matcher._h, int(kind), ptr(sp), ptr(tp),
                                                       ptr(res), o(js), o(jt)))

@@ -212,7 +212,17 @@ def main():
     t0 = time.perf_counter()
     r_all = evaluate_resident_blocks(m, 0, est[src], est[tgt], co)
     ms_all = 1e3 * (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    r_pin = evaluate_resident_blocks(m, 0, est[src], est[tgt], co, pinned=True)   # allocates the pinned buffers
+    ms_pin_first = 1e3 * (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    r_pin = evaluate_resident_blocks(m, 0, est[src], est[tgt], co, out=r_pin)     # a later solver iteration
+    ms_pin = 1e3 * (time.perf_counter() - t0)
     st["resident_chain"] = {"blocks": int(len(src)), "correspondences": int(co[-1]),
+                            "ms_with_jacobians_pinned_first_wall": ms_pin_first,
+                            "ms_with_jacobians_pinned_wall": ms_pin,
+                            "pinned_identical": bool(np.array_equal(r_pin[0], res) and np.array_equal(r_pin[1], js)
+                                                     and np.array_equal(r_pin[2], jt)),
                             "ms_match_wall": ms_match, "ms_match_kernel": ms_match_k,
                             "ms_residuals_only_wall": ms_res, "ms_with_jacobians_wall": ms_all,
                             "ms_kernel": last_kernel_ms(m),

@@ -178,6 +178,12 @@ def test_resident_chain_equals_host_chain(kind):
     got = evaluate_resident_blocks(m, kind, sp, tp, corr_offs)
     for g, w in zip(got, want):
         assert np.array_equal(g, w)
+    # page-locked result buffers (nautilus_host_alloc), reused by a second call
+    pin = evaluate_resident_blocks(m, kind, sp, tp, corr_offs, pinned=True)
+    pin = evaluate_resident_blocks(m, kind, sp, tp, corr_offs, out=pin)
+    for g, w in zip(pin, want):
+        assert np.array_equal(g, w)
+    del pin
     # re-evaluation with moved poses, residuals only (what a Ceres iteration does)
     sp2 = sp + 0.01
     r2 = evaluate_resident_blocks(m, kind, sp2, tp, corr_offs, jacobians=False)
