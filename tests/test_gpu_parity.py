@@ -291,6 +291,30 @@ def test_full_size_properties():
 
 
 @pytest.mark.gpu
+def test_grid_wider_than_checkpoint_budget_vs_oracle():
+    """scanner_range 40 m at 0.03 m: 2666 cells per line, more than the 2048 the
+    checkpointed x/y passes cover, so the table build takes the stored variants
+    (csm_tables.cu: xpass_stored_kernel / ypass_stored_kernel).  Tables bit-identical
+    with margin -1, the match identical to the oracle's."""
+    pm = port.PortMatcher(40, 2, 0.3, 0.03)
+    a, b, _ = synth.make_pair(23)
+    ph = pm.highres(b)
+    pl = pm.lowres(ph)
+    m = CorrelativeScanMatcher(40, 2, 0.3, 0.03, margin_cells=-1)
+    assert m.w_high == 2666
+    hi, lo = m.GetLookupTables(b)
+    assert np.array_equal(hi.values, ph.values) and np.array_equal(lo.values, pl.values)
+    m.close()
+    m = CorrelativeScanMatcher(40, 2, 0.3, 0.03)
+    got, stats = m.GetTransformation(a, b, -0.5, 0.5, with_stats=True)
+    want, wstats = pm.match(a, b, -0.5, 0.5, with_stats=True)
+    assert (got[1][0][0], got[1][0][1], got[1][1]) == (want[1], want[2], want[3])
+    assert abs(got[0] - want[0]) <= REL * abs(want[0])
+    assert tuple(stats) == tuple(int(v) for v in wstats)
+    m.close()
+
+
+@pytest.mark.gpu
 def test_concurrent_callers_on_one_handle():
     """The reference object is called from OpenMP threads (CorrelativeScanMatcher.cc:381-386,
     bag_avg_matcher.cc:104-141): concurrent single-pair calls on one handle must give the
