@@ -208,3 +208,43 @@ def test_resident_chain_errors():
     co = m.nn_match_resident([], [], np.zeros((0, 6), np.float32), 0.25)
     assert co.tolist() == [0]
     m.close()
+
+
+def test_planar_subsets_through_resident_chain():
+    """PointcloudType::PLANAR / EDGE (solver.cc:96-107): source points and the lookup tree
+    come from the planar subsets (<= 20 points per scan), the normals from the FULL clouds'
+    trees (solver.cc:152-155).  The subsets are uploaded as a scan set of their own; their
+    normals are gathered once through the full clouds' self index (GetPointNormal depends on
+    the coordinates only).  Checked against the oracle's search on the subsets."""
+    from nautilus_b200.residuals import evaluate_residual_blocks, evaluate_resident_blocks
+    xy, offs, poses = synth.make_scan_set(8, group=4, seed=13, n_beams=360, return_poses=True)
+    rng = np.random.default_rng(7)
+    normals = rng.normal(size=xy.shape).astype(np.float32)
+    full = make_matcher(xy, offs, 0.25)
+    self_full = full.nn_self_index()
+    # planar subsets: 20 evenly spaced points of every scan
+    pick = [int(offs[s]) + np.linspace(0, offs[s + 1] - offs[s] - 1, 20).astype(np.int64) for s in range(8)]
+    sub_xy = np.concatenate([xy[p] for p in pick])
+    sub_offs = np.arange(9, dtype=np.int64) * 20
+    sub_normals = np.concatenate([normals[int(offs[s]) + self_full[pick[s]]] for s in range(8)])
+    m = make_matcher(sub_xy, sub_offs, 0.25)
+    m.nn_upload_normals(sub_normals)
+    src = np.asarray([0, 1, 2, 3, 4, 5, 6, 7], np.int32)
+    tgt = np.asarray([1, 0, 3, 2, 5, 4, 7, 6], np.int32)
+    tf = np.stack([pose_transform(poses[s], poses[t]) for s, t in zip(src, tgt)])
+    co = m.nn_match_resident(src, tgt, tf, 0.25)
+    want_idx, wo, _ = nn_port.match_batch(sub_xy, sub_offs, src, tgt, tf, 0.25)
+    hit = want_idx >= 0
+    blk = np.searchsorted(wo, np.arange(len(want_idx)), side="right") - 1
+    assert np.array_equal(co, np.concatenate([[0], np.cumsum(np.bincount(blk[hit], minlength=8))]))
+    assert co[-1] > 0
+    sp = sub_xy[sub_offs[src[blk[hit]]] + (np.arange(len(want_idx)) - wo[blk])[hit]]
+    tp = sub_xy[sub_offs[tgt[blk[hit]]] + want_idx[hit]]
+    sn = sub_normals[sub_offs[src[blk[hit]]] + (np.arange(len(want_idx)) - wo[blk])[hit]]
+    tn = sub_normals[sub_offs[tgt[blk[hit]]] + want_idx[hit]]
+    got = evaluate_resident_blocks(m, 1, poses[src], poses[tgt], co)
+    want = evaluate_residual_blocks(m, 1, poses[src], poses[tgt], co, sp, tp, sn, tn)
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    m.close()
+    full.close()
