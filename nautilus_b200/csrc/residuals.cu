@@ -26,16 +26,29 @@ struct ResidualArgs {
   double* jac_s;            // [n_corr][2][3] or null
   double* jac_t;
   int kind;                 // 0: point residual, 1: normal residual
+  const double4* trig;      // [n_blocks] sin/cos of the source and target headings
 };
+
+// sin / cos of a block's two headings, once per block instead of once per
+// correspondence (the same device sincos on the same arguments: same bits).
+__global__ void pose_trig_kernel(const double* __restrict__ src_pose,
+                                 const double* __restrict__ tgt_pose, int n_blocks,
+                                 double4* __restrict__ trig) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_blocks) return;
+  double ss, cs, st, ct;
+  sincos(src_pose[3 * b + 2], &ss, &cs);
+  sincos(tgt_pose[3 * b + 2], &st, &ct);
+  trig[b] = make_double4(ss, cs, st, ct);
+}
 
 // Residuals and Jacobians of correspondence k of residual block `blk`.
 __device__ __forceinline__ void residual_math(const ResidualArgs& a, long long k, int blk, float2 pf,
                                               float2 qf, float2 nsf, float2 ntf) {
-  const double xs = a.src_pose[3 * blk], ys = a.src_pose[3 * blk + 1], ths = a.src_pose[3 * blk + 2];
-  const double xt = a.tgt_pose[3 * blk], yt = a.tgt_pose[3 * blk + 1], tht = a.tgt_pose[3 * blk + 2];
-  double ss, cs, st, ct;
-  sincos(ths, &ss, &cs);
-  sincos(tht, &st, &ct);
+  const double xs = a.src_pose[3 * blk], ys = a.src_pose[3 * blk + 1];
+  const double xt = a.tgt_pose[3 * blk], yt = a.tgt_pose[3 * blk + 1];
+  const double4 tr = a.trig[blk];
+  const double ss = tr.x, cs = tr.y, st = tr.z, ct = tr.w;
   const double px = pf.x, py = pf.y, qx = qf.x, qy = qf.y;
   // w = R(th_s) p + t_s - t_t (world frame, relative to the target origin)
   const double rx = cs * px - ss * py, ry = ss * px + cs * py;
@@ -67,30 +80,42 @@ __device__ __forceinline__ void residual_math(const ResidualArgs& a, long long k
     }
   }
   reinterpret_cast<double2*>(a.res)[k] = make_double2(r0, r1);
+  // 48 bytes per correspondence and array, 16-byte aligned: three 16-byte stores
   if (a.jac_s) {
-    double* j = a.jac_s + 6 * k;
-    j[0] = g0[0]; j[1] = g0[1]; j[2] = g0[2]; j[3] = g1[0]; j[4] = g1[1]; j[5] = g1[2];
+    double2* j = reinterpret_cast<double2*>(a.jac_s + 6 * k);
+    j[0] = make_double2(g0[0], g0[1]); j[1] = make_double2(g0[2], g1[0]); j[2] = make_double2(g1[1], g1[2]);
   }
   if (a.jac_t) {
-    double* j = a.jac_t + 6 * k;
-    j[0] = g0[3]; j[1] = g0[4]; j[2] = g0[5]; j[3] = g1[3]; j[4] = g1[4]; j[5] = g1[5];
+    double2* j = reinterpret_cast<double2*>(a.jac_t + 6 * k);
+    j[0] = make_double2(g0[3], g0[4]); j[1] = make_double2(g0[5], g1[3]); j[2] = make_double2(g1[4], g1[5]);
   }
 }
 
-// residual block of correspondence k: last b with offsets[b] <= k
-__device__ __forceinline__ int block_of(const long long* offsets, int n_blocks, long long k) {
-  int lo = 0, hi = n_blocks;
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (offsets[mid] <= k) lo = mid; else hi = mid;
+// residual block of correspondence k: last b with offsets[b] <= k.  One binary
+// search per CUDA block (for its first correspondence), then every thread walks
+// forward from there: consecutive correspondences sit in the same or the next
+// few residual blocks.
+__device__ __forceinline__ int block_of(const long long* __restrict__ offsets, int n_blocks,
+                                        long long k, long long k_first, int* s_first) {
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = n_blocks;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (offsets[mid] <= k_first) lo = mid; else hi = mid;
+    }
+    *s_first = lo;
   }
-  return lo;
+  __syncthreads();
+  int b = *s_first;
+  while (b + 1 < n_blocks && offsets[b + 1] <= k) ++b;
+  return b;
 }
 
 __global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long n_corr) {
-  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ int s_first;
+  const long long k0 = (long long)blockIdx.x * blockDim.x, k = k0 + threadIdx.x;
+  const int blk = block_of(a.offsets, a.n_blocks, min(k, n_corr - 1), k0, &s_first);
   if (k >= n_corr) return;
-  const int blk = block_of(a.offsets, a.n_blocks, k);
   const float2 z = make_float2(0.f, 0.f);
   residual_math(a, k, blk, a.sp[k], a.tp[k], a.kind ? a.sn[k] : z, a.kind ? a.tn[k] : z);
 }
@@ -100,9 +125,10 @@ __global__ void __launch_bounds__(256) residual_kernel(ResidualArgs a, long long
 __global__ void __launch_bounds__(256) residual_resident_kernel(
     ResidualArgs a, long long n_corr, const int4* __restrict__ corr,
     const float2* __restrict__ points, const float2* __restrict__ normals) {
-  const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ int s_first;
+  const long long k0 = (long long)blockIdx.x * blockDim.x, k = k0 + threadIdx.x;
+  const int blk = block_of(a.offsets, a.n_blocks, min(k, n_corr - 1), k0, &s_first);
   if (k >= n_corr) return;
-  const int blk = block_of(a.offsets, a.n_blocks, k);
   const int4 c = corr[k];
   const float2 z = make_float2(0.f, 0.f);
   residual_math(a, k, blk, points[c.x], points[c.y], a.kind ? normals[c.z] : z,
@@ -140,7 +166,8 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
   const size_t b_res = sizeof(double) * 2 * (size_t)n;
   const size_t b_jac = sizeof(double) * 6 * (size_t)n;
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-  const size_t total = 2 * up(b_pose) + up(b_off) + 4 * up(b_pts) + up(b_res) + 2 * up(b_jac);
+  const size_t b_trig = sizeof(double4) * (size_t)n_blocks;
+  const size_t total = 2 * up(b_pose) + up(b_off) + 4 * up(b_pts) + up(b_res) + 2 * up(b_jac) + up(b_trig);
   int rc = h->residual_arena.reserve(total);
   if (rc) return rc;
   unsigned char* base = h->residual_arena.p;
@@ -153,6 +180,7 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
   float2* d_ns = (float2*)take(b_pts); float2* d_nt = (float2*)take(b_pts);
   double* d_res = (double*)take(b_res);
   double* d_js = (double*)take(b_jac); double* d_jt = (double*)take(b_jac);
+  double4* d_trig = (double4*)take(b_trig);
   CU_TRY(cudaMemcpyAsync(d_sp, source_poses, b_pose, cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(d_tp, target_poses, b_pose, cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(d_off, offsets, b_off, cudaMemcpyHostToDevice, st));
@@ -166,9 +194,11 @@ extern "C" int nautilus_residuals_eval(NautilusCsm* h, int32_t kind, const doubl
   a.sp = d_p; a.tp = d_q; a.sn = d_ns; a.tn = d_nt;
   a.res = d_res; a.jac_s = jac_source ? d_js : nullptr; a.jac_t = jac_target ? d_jt : nullptr;
   a.kind = kind;
+  a.trig = d_trig;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
+  csm::pose_trig_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_sp, d_tp, n_blocks, d_trig);
   csm::residual_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, n);
   cudaEventRecord(e1, st);
   CU_TRY(cudaGetLastError());
@@ -202,7 +232,8 @@ extern "C" int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind,
   const size_t b_res = sizeof(double) * 2 * (size_t)n;
   const size_t b_jac = sizeof(double) * 6 * (size_t)n;
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-  const size_t total = 2 * up(b_pose) + up(b_res) + 2 * up(b_jac);
+  const size_t b_trig = sizeof(double4) * (size_t)n_blocks;
+  const size_t total = 2 * up(b_pose) + up(b_res) + 2 * up(b_jac) + up(b_trig);
   int rc = h->residual_arena.reserve(total);
   if (rc) return rc;
   unsigned char* base = h->residual_arena.p;
@@ -211,6 +242,7 @@ extern "C" int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind,
   double* d_sp = (double*)take(b_pose); double* d_tp = (double*)take(b_pose);
   double* d_res = (double*)take(b_res);
   double* d_js = (double*)take(b_jac); double* d_jt = (double*)take(b_jac);
+  double4* d_trig = (double4*)take(b_trig);
   CU_TRY(cudaMemcpyAsync(d_sp, source_poses, b_pose, cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(d_tp, target_poses, b_pose, cudaMemcpyHostToDevice, st));
   csm::ResidualArgs a;
@@ -218,9 +250,11 @@ extern "C" int nautilus_residuals_eval_resident(NautilusCsm* h, int32_t kind,
   a.sp = a.tp = a.sn = a.tn = nullptr;
   a.res = d_res; a.jac_s = jac_source ? d_js : nullptr; a.jac_t = jac_target ? d_jt : nullptr;
   a.kind = kind;
+  a.trig = d_trig;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
+  csm::pose_trig_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_sp, d_tp, n_blocks, d_trig);
   csm::residual_resident_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
       a, n, nn.corr, h->user_scans.points, nn.normals);
   cudaEventRecord(e1, st);
