@@ -17,6 +17,8 @@ def main():
     ap.add_argument("--seeds", type=int, default=4)
     ap.add_argument("--pairs", type=int, default=1200, help="pairs checked per seed")
     ap.add_argument("--scans", type=int, default=400)
+    ap.add_argument("--cross", action="store_true",
+                    help="pair scans of DIFFERENT rooms (no overlap: flat score landscapes, many pops)")
     args = ap.parse_args()
     cores = bench.host_cores()
     m = CorrelativeScanMatcher(*bench.PARAMS, device=0)
@@ -26,6 +28,9 @@ def main():
     t0 = time.perf_counter()
     for seed in range(100, 100 + args.seeds):
         xy, offs, pa, pb = bench.make_batch(args.scans, seed=seed)
+        if args.cross:   # same queries, targets drawn from anywhere in the set
+            rng = np.random.default_rng(seed)
+            pb = rng.integers(0, args.scans, size=len(pa)).astype(pb.dtype)
         m.upload_scans(xy, offs)
         score, x, y, th, st = m.match_batch(pa, pb, *bench.ROT_WINDOW, with_stats=True)
         idx = np.linspace(0, len(pa) - 1, min(args.pairs, len(pa))).astype(np.int64)
@@ -36,7 +41,7 @@ def main():
         tot += len(idx)
     m.close()
     print(json.dumps({"check": "GPU match_batch vs reference CPU GetTransformation", "kind": kind,
-                      "pairs": tot, "seeds": args.seeds, "pose_mismatches": bad_pose,
+                      "pairs": tot, "seeds": args.seeds, "cross_room_pairs": bool(args.cross), "pose_mismatches": bad_pose,
                       "worst_score_rel_err": worst, "cores": cores,
                       "seconds": round(time.perf_counter() - t0, 1)}), flush=True)
     sys.exit(1 if bad_pose or worst > 1e-5 else 0)
