@@ -848,7 +848,8 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
     ypass_stored_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   }
   dim3 gn(g.n_pool, n_tables);
-  normalize_pool_kernel<<<gn, 256, sizeof(double) * g.w, stream>>>(
+  static const int np_threads = getenv("NAUTILUS_CSM_NP_THREADS") ? atoi(getenv("NAUTILUS_CSM_NP_THREADS")) : 128;  // A/B knob: 256 / 192 / 128 / 96 / 64 threads -> 10.24 / 10.30 / 10.04 / 10.24 / 10.59 ms table stage
+  normalize_pool_kernel<<<gn, np_threads, sizeof(double) * g.w, stream>>>(
       g, slots, metas, pool.s, pool.e, pool.dst, pool.win, store_log ? 1 : 0);
   if (launches) *launches += 4;
 }
