@@ -130,7 +130,10 @@ __global__ void __launch_bounds__(256) raster_kernel(
 // serial recursions 32 columns at a time into a shared-memory tile which the
 // warp then writes out row-contiguously (256 B per row segment).
 // ---------------------------------------------------------------------------
-constexpr int XP_WARPS = 4;
+#ifndef XP_WARPS_N
+#define XP_WARPS_N 4
+#endif
+constexpr int XP_WARPS = XP_WARPS_N;
 
 __global__ void __launch_bounds__(XP_WARPS * 32) xpass_stored_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
@@ -247,7 +250,10 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_stored_kernel(
 // box's first row (exact zeros above it), runs to the rectangle's last row;
 // the anti-causal pass walks back to the rectangle's first row.
 // ---------------------------------------------------------------------------
-constexpr int YP_THREADS = 128;
+#ifndef YP_THREADS_N
+#define YP_THREADS_N 128
+#endif
+constexpr int YP_THREADS = YP_THREADS_N;
 constexpr int YP_B = 8;  // rows loaded ahead of the recursion
 
 __global__ void __launch_bounds__(YP_THREADS) ypass_stored_kernel(
