@@ -77,20 +77,45 @@ def needs_build() -> bool:
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
+def _stale(obj: str, src: str) -> bool:
+    if not os.path.exists(obj):
+        return True
+    t = os.path.getmtime(obj)
+    deps = [src] + [os.path.join(CSRC, h) for h in HEADERS]
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile the CUDA library for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    """Compile the CUDA library for sm_100a in-tree (nvcc cross-compiles without a GPU).
+    One object per translation unit, compiled in parallel, then one link."""
     if not force and not needs_build():
         return LIB_PATH
+    from concurrent.futures import ThreadPoolExecutor
     os.makedirs(LIB_DIR, exist_ok=True)
-    cmd = ["nvcc", *NVCC_FLAGS, *[os.path.join(CSRC, s) for s in SOURCES], "-o", LIB_PATH]
+    obj_dir = os.path.join(LIB_DIR, "obj")
+    os.makedirs(obj_dir, exist_ok=True)
+    cflags = [f for f in NVCC_FLAGS if f != "-shared"]
+
+    def compile_one(name):
+        src = os.path.join(CSRC, name)
+        obj = os.path.join(obj_dir, name.replace(".cu", ".o"))
+        if not force and not _stale(obj, src):
+            return obj, ""
+        cmd = ["nvcc", *cflags, *(["-Xptxas", "-v"] if verbose else []), "-c", src, "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+        return obj, r.stderr
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+        res = list(ex.map(compile_one, SOURCES))
     if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
+        print("".join(log for _, log in res))
+    cmd = ["nvcc", "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
+           *[o for o, _ in res], "-o", LIB_PATH, "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
     return LIB_PATH
 
 

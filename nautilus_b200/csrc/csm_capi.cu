@@ -38,7 +38,7 @@ namespace {
 // convertX / convertY on the host (CorrelativeScanMatcher.h:43-49)
 long long host_cell(float v, double res, uint64_t dim) {
   const double c = (double)(dim / 2) + floor((double)v / res);
-  if (c < -4.0e18) return -4000000000000000000LL;
+  if (!(c >= -4.0e18)) return -4000000000000000000LL;  // also NaN
   if (c > 4.0e18) return 4000000000000000000LL;
   return (long long)c;
 }
@@ -631,8 +631,10 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if (ring) {
     wave_tables = n_slots;
   } else {
-    const char* env = getenv("NAUTILUS_CSM_WAVES");
-    int n_sub = env ? atoi(env) : 1;
+    int n_sub = 1;
+#ifdef NAUTILUS_CSM_TUNING
+    if (const char* env = getenv("NAUTILUS_CSM_WAVES")) n_sub = atoi(env);
+#endif
     n_sub = std::max(1, std::min(n_sub, n_targets));
     wave_tables = (n_targets + n_sub - 1) / n_sub;
   }
@@ -731,8 +733,10 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   if ((rc = h->chunk_rot_dev.reserve((size_t)max_wave_pairs * chunks * n_tr))) return rc;
   sb.chunk_best = h->chunk_best_dev.p;
   sb.chunk_rot = h->chunk_rot_dev.p;
-  const char* rf_env = getenv("NAUTILUS_CSM_REFINE");
-  const bool rf_serial = rf_env && !strcmp(rf_env, "serial");
+  bool rf_serial = false;
+#ifdef NAUTILUS_CSM_TUNING
+  if (const char* rf_env = getenv("NAUTILUS_CSM_REFINE")) rf_serial = !strcmp(rf_env, "serial");
+#endif
   sb.spec_cap = spec_cap_for(n_tr);
   sb.spec_pairs = nullptr; sb.spec_items = nullptr; sb.spec_out = nullptr; sb.spec_counters = nullptr;
   if (!rf_serial) {

@@ -8,6 +8,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #define CSM_MIN_VALUE_FOR_LOOKUP 1E-10  // CorrelativeScanMatcher.h:20
 #define CSM_EPSILON 1e-6                // CorrelativeScanMatcher.cc:19
 
@@ -106,6 +108,7 @@ __host__ __device__ __forceinline__ int cell_fast(const CellMap& m, float v) {
   const float fl0 = floorf(e);
   int q = !(fl0 > -2.0e9f) ? -2147483647 - 1 : (fl0 > 2.0e9f ? 2147483647 : (int)fl0);
 #endif
+  if (!(v == v)) return -1;      // NaN: outside, like the reference's double -> uint64 conversion
   const float fr = e - (float)q;  // exact while |q| < 2^24; irrelevant once saturated
   // strictly inside the grid and clear of both cell boundaries: the estimate is the cell
   const bool inside = (unsigned)(q - m.qlo - 1) < (unsigned)(m.qhi - m.qlo - 1);
@@ -122,7 +125,7 @@ __host__ __device__ __forceinline__ int cell_fast(const CellMap& m, float v) {
 __device__ __forceinline__ long long cell_of(float v, double res, int dim) {
   const double q = floor(__ddiv_rn((double)v, res));
   const double c = (double)(dim / 2) + q;
-  if (c < -4.0e18) return -4000000000000000000LL;
+  if (!(c >= -4.0e18)) return -4000000000000000000LL;  // also NaN: outside the grid
   if (c > 4.0e18) return 4000000000000000000LL;
   return (long long)c;
 }
@@ -172,5 +175,42 @@ __device__ __forceinline__ void vv_triggs(const VanVliet& f, double iplus, doubl
   w2 = __dmul_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(M[6], unp), __dmul_rn(M[7], unp1)),
                                      __dmul_rn(M[8], unp2)), vplus), sum);
 }
+
+// Opt-in to more than 48 KB of dynamic shared memory.  The attribute belongs to
+// the (kernel, device) pair, so the largest size already granted is remembered per
+// device ordinal of the calling thread's current device; handles on different
+// devices and on different host threads may launch concurrently.
+struct SmemOptIn {
+  static constexpr int kMaxDev = 64;
+  std::mutex mu;
+  size_t granted[kMaxDev] = {};
+  int per_sm[kMaxDev] = {};      // resident blocks per SM at per_sm_smem (persistent launches)
+  size_t per_sm_smem[kMaxDev] = {};
+  template <typename K>
+  cudaError_t allow(K kernel, size_t smem) {
+    if (smem <= 48 * 1024) return cudaSuccess;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> g(mu);
+    if (dev < 0 || dev >= kMaxDev || smem > granted[dev]) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess && dev >= 0 && dev < kMaxDev) granted[dev] = smem;
+    }
+    return e;
+  }
+  template <typename K>
+  int blocks_per_sm(K kernel, int threads, size_t smem) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> g(mu);
+    if (dev >= 0 && dev < kMaxDev && per_sm[dev] > 0 && per_sm_smem[dev] == smem) return per_sm[dev];
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem);
+    if (n < 1) n = 1;
+    if (dev >= 0 && dev < kMaxDev) { per_sm[dev] = n; per_sm_smem[dev] = smem; }
+    return n;
+  }
+};
 
 }  // namespace csm

@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
   const double* __restrict__ lowlog = slots[pw.table].lowlog;
   const int lstride = lowlog_stride(g.wl);
 
-  for (int k = threadIdx.x; k < g.wl + 2; k += LS_THREADS) s_thr[k] = cm_global.lowf[k];
+  for (int k = threadIdx.x; k < g.wl + 1; k += LS_THREADS) s_thr[k] = cm_global.lowf[k];  // make_thresholds: dim + 1 entries
   for (int k = threadIdx.x; k < n_t; k += LS_THREADS) s_tlow[k] = sg.t_low[k];
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
     s_best[tr] = -INFINITY;
@@ -425,11 +425,8 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
                       int n_pairs, const SearchBuffers& sb, int table_cells, cudaStream_t stream) {
   if (n_pairs <= 0) return;
   const size_t smem = low_score_smem_bytes(sg.n_t, g.wl, table_cells);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaFuncSetAttribute(low_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
+  static SmemOptIn opt;
+  opt.allow(low_score_kernel, smem);  // a refusal surfaces as the launch error
   dim3 grid(sb.chunks_per_pair, n_pairs);
   low_score_kernel<<<grid, LS_THREADS, smem, stream>>>(g, sg, cm_low, points, offsets, slots,
                                                        metas, pairs, rots, sb, table_cells);
@@ -930,14 +927,6 @@ static size_t refine_smem_bytes(int n_t, int nh_max, bool with_memo) {
   return b;
 }
 
-template <typename K>
-static void allow_smem(K kernel, size_t smem, size_t* configured) {
-  if (smem > 48 * 1024 && smem > *configured) {
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    *configured = smem;
-  }
-}
-
 int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_high,
                   const float2* points, const long long* offsets, const TableSlot* slots,
                   const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
@@ -945,26 +934,22 @@ int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hig
                   int sm_count, cudaStream_t stream) {
   if (n_pairs <= 0) return 0;
   const size_t smem = refine_smem_bytes(sg.n_t, sg.n_h_max, true);
-  static size_t conf_serial = 0, conf_first = 0, conf_spec = 0, conf_finish = 0;
+  static SmemOptIn opt_serial, opt_first, opt_spec, opt_finish;
   if (serial) {
-    allow_smem(refine_kernel, smem, &conf_serial);
+    opt_serial.allow(refine_kernel, smem);
     refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots, metas,
                                                          pairs, rots, sb, results);
     return 1;
   }
   const size_t smem_spec = refine_smem_bytes(sg.n_t, sg.n_h_max, false);
-  allow_smem(refine_first_kernel, smem, &conf_first);
-  allow_smem(refine_spec_kernel, smem_spec, &conf_spec);
-  allow_smem(refine_finish_kernel, smem, &conf_finish);
+  opt_first.allow(refine_first_kernel, smem);
+  opt_spec.allow(refine_spec_kernel, smem_spec);
+  opt_finish.allow(refine_finish_kernel, smem);
   cudaMemsetAsync(sb.spec_counters, 0, 2 * sizeof(int), stream);
   refine_first_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots,
                                                              metas, pairs, rots, sb);
   // persistent: as many blocks as stay resident, each fetching windows from the queue
-  static int per_sm = 0;
-  if (!per_sm) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, refine_spec_kernel, RF_THREADS, smem_spec);
-    if (per_sm < 1) per_sm = 1;
-  }
+  const int per_sm = opt_spec.blocks_per_sm(refine_spec_kernel, RF_THREADS, smem_spec);
   const long long max_items = (long long)n_pairs * sb.spec_cap;
   const int grid = (int)std::min<long long>((long long)sm_count * per_sm, std::max<long long>(max_items, 1));
   refine_spec_kernel<<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets, slots,

@@ -356,8 +356,10 @@ __global__ void __launch_bounds__(YP_THREADS) ypass_stored_kernel(
 // anti-causal pass rebuilds each 32-sample chunk from its checkpoint just
 // before it walks it backwards.  The rebuilt values are the same operations on
 // the same operands, hence the same bits.  x-pass: write-only (its input is the
-// bitmap); y-pass: reads the x-pass output twice, writes once.  Lines of up to
-// 32 * RC_MAXCH = 2048 samples; longer grids take the stored variants.
+// bitmap); y-pass: reads the x-pass output twice, writes once.  MAXCH = checkpoint
+// capacity in 32-sample chunks: 64 for grids up to 2048 cells per line (0.03 m
+// tables), 192 for grids up to 6144 (the solver's 0.01 m tables, W = 6000,
+// solver.cc:56); longer grids take the stored variants.
 // ---------------------------------------------------------------------------
 // Global-space accesses of the value buffer (the slot pointers come from memory,
 // so the compiler would otherwise emit generic LD / ST).
@@ -370,11 +372,9 @@ __device__ __forceinline__ void st_gbl(double* p, double v) {
   asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
 
-#ifndef YP_PREF   // 1: y-pass causal sweep loads one chunk ahead (A/B knob)
-#define YP_PREF 0
-#endif
-constexpr int RC_MAXCH = 64;
+constexpr int RC_MAXCH_SMALL = 64, RC_MAXCH_LARGE = 192;
 
+template <int MAXCH>
 __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas) {
@@ -389,36 +389,43 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
   // Lanes take the rows that hold a point (the others stay exact zeros and are
   // never touched): row bits of the occupied box, their prefix counts, and the
   // k-th lit row for lane k of the block's 128-row share.
-  __shared__ unsigned s_rows[RC_MAXCH + 1];
-  __shared__ int s_pref[RC_MAXCH + 1];
+  constexpr int WPL = MAXCH / 32;  // row words per lane of the prefix scan
+  static_assert(MAXCH % 32 == 0, "the prefix scan gives every lane WPL words");
+  __shared__ unsigned s_rows[MAXCH + 1];
+  __shared__ int s_pref[MAXCH + 1];
   __shared__ int s_rowidx[XP_WARPS][32];
-  for (int w = warp; w <= RC_MAXCH; w += XP_WARPS) {
+  for (int w = warp; w <= MAXCH; w += XP_WARPS) {
     const int r = w * 32 + lane;
     const unsigned b = __ballot_sync(0xffffffffu, r < rows && slot.rowflag[r] != 0);
     if (lane == 0) s_rows[w] = b;
   }
   __syncthreads();
   if (warp == 0) {
-    const int c0 = __popc(s_rows[2 * lane]), c1 = __popc(s_rows[2 * lane + 1]);
-    int incl = c0 + c1;
+    int c[WPL], tot = 0;
+#pragma unroll
+    for (int u = 0; u < WPL; ++u) { c[u] = __popc(s_rows[WPL * lane + u]); tot += c[u]; }
+    int incl = tot;
     for (int o = 1; o < 32; o <<= 1) {
       const int v = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += v;
     }
-    s_pref[2 * lane] = incl - c0 - c1;
-    s_pref[2 * lane + 1] = incl - c1;
-    if (lane == 31) s_pref[RC_MAXCH] = incl;
+    int run = incl - tot;
+#pragma unroll
+    for (int u = 0; u < WPL; ++u) { s_pref[WPL * lane + u] = run; run += c[u]; }
+    if (lane == 31) s_pref[MAXCH] = incl;
   }
   __syncthreads();
-  const int n_lit = s_pref[RC_MAXCH];
+  const int n_lit = s_pref[MAXCH];
   const int k_row = (blockIdx.x * XP_WARPS + warp) * 32 + lane;
   if (k_row - lane >= n_lit) return;
   const bool has_row = k_row < n_lit;
   int row_local = 0;
   if (has_row) {
-    int w = 0;
-    for (int step = RC_MAXCH / 2; step > 0; step >>= 1)
-      if (s_pref[w + step] <= k_row) w += step;
+    int w = 0, hi = MAXCH;  // s_pref[w] <= k_row < s_pref[hi]
+    while (hi - w > 1) {
+      const int mid = (w + hi) >> 1;
+      if (s_pref[mid] <= k_row) w = mid; else hi = mid;
+    }
     row_local = w * 32 + (int)__fns(s_rows[w], 0, k_row - s_pref[w] + 1);
   }
   s_rowidx[warp][lane] = row_local;
@@ -427,7 +434,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
 
   __shared__ double s_tile[XP_WARPS][32][33];
   double (*tile)[33] = s_tile[warp];
-  double ck[3 * RC_MAXCH];
+  double ck[3 * MAXCH];
   double* base = slot.values + (size_t)(m.cy0 - m.ay0) * m.stride;  // box row 0
   const int* rowidx = s_rowidx[warp];
   const unsigned* bm = slot.bitmap + (size_t)row_local * g.bm_stride;
@@ -559,7 +566,7 @@ __device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int 
 // registers; 16: 3 KB of checkpoints per thread, ~90 registers).  The minimum is
 // only tracked when the rectangle is the whole grid (a cropped table normalises
 // against 0, see normalize_pool_kernel).
-template <int YC, int MINB>
+template <int YC, int MINB, int MAXCH>
 __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     Geometry g, VanVliet f, const TableSlot* __restrict__ slots,
     TableMeta* __restrict__ metas) {
@@ -578,10 +585,10 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
   const size_t stride = (size_t)m.stride;
 
   // rows of the occupied box that hold a point, one bit each (zeros past the box)
-  __shared__ unsigned s_rows[RC_MAXCH + 1];
+  __shared__ unsigned s_rows[MAXCH + 1];
   {
     const int rows = m.cy1 - m.cy0 + 1;
-    for (int w = threadIdx.x >> 5; w <= RC_MAXCH; w += YP_THREADS / 32) {
+    for (int w = threadIdx.x >> 5; w <= MAXCH; w += YP_THREADS / 32) {
       const int r = w * 32 + (threadIdx.x & 31);
       const unsigned b = __ballot_sync(0xffffffffu, r < rows && flag[r] != 0);
       if ((threadIdx.x & 31) == 0) s_rows[w] = b;
@@ -593,7 +600,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
   const bool needmin = !m.cropped;
   double vmax = -INFINITY, vmin = INFINITY;
   if (live) {
-    double ck[3 * RC_MAXCH * 32 / YC];
+    double ck[3 * MAXCH * 32 / YC];
     double v1 = 0.0, v2 = 0.0, v3 = 0.0;  // Neumann seed from grid row 0
     if (m.cy0 == 0 && flag[0]) {
       const double x0 = ld_gbl(colp + (size_t)(0 - m.ay0) * stride);
@@ -608,22 +615,6 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     const int nch = (n_fwd + YC - 1) / YC;
     {
       const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
-#if YP_PREF
-      // the next chunk's loads are in flight while this chunk's recursion steps
-      double a[YC], an[YC];
-      y_load<YC>(a, p, stride, s_rows[0] & CMASK);
-      for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
-        ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
-        const int b0 = ci * YC, b1 = b0 + YC;
-        const unsigned nbits = ci + 1 < nch ? (s_rows[b1 >> 5] >> (b1 & 31)) & CMASK : 0u;
-        y_load<YC>(an, p + (size_t)YC * stride, stride, nbits);
-        const int nrow = n_fwd - b0;
-        if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
-        else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
-#pragma unroll
-        for (int u = 0; u < YC; ++u) a[u] = an[u];
-      }
-#else
       for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
         ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
         const int b0 = ci * YC;
@@ -634,7 +625,6 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
         if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
         else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
       }
-#endif
     }
     const bool at_edge = (m.ay1 == g.w - 1);
     double w0 = 0.0;
@@ -835,6 +825,15 @@ __global__ void low_checksum_kernel(Geometry g, const TableSlot* __restrict__ sl
 }
 
 // ---- launchers --------------------------------------------------------------
+// NAUTILUS_CSM_TUNING builds (scripts/ab_build.sh) read A/B knobs from the
+// environment; the shipped library has no getenv on its launch paths.
+#ifdef NAUTILUS_CSM_TUNING
+static int tuning_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+#endif
+
 void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
                        TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
@@ -843,19 +842,27 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   raster_kernel<<<n_tables, 256, 0, stream>>>(g, points, offsets, scan_ids, slots, metas);
   dim3 gx((g.w + XP_WARPS * 32 - 1) / (XP_WARPS * 32), n_tables);
   dim3 gy((g.w + YP_THREADS - 1) / YP_THREADS, n_tables);
-  static const bool stored = getenv("NAUTILUS_CSM_TABLE_STORED") != nullptr;  // A/B knob
-  if (g.w <= 32 * RC_MAXCH && !stored) {
-    xpass_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
-    static const int yc = getenv("NAUTILUS_CSM_YC") ? atoi(getenv("NAUTILUS_CSM_YC")) : 16;
-    if (yc == 32) ypass_kernel<32, 3><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
-    else ypass_kernel<16, 5><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  bool stored = false;
+  int np_threads = 128;  // 256 / 192 / 128 / 96 / 64 threads -> 10.24 / 10.30 / 10.04 / 10.24 / 10.59 ms table stage (r1)
+#ifdef NAUTILUS_CSM_TUNING
+  stored = tuning_int("NAUTILUS_CSM_TABLE_STORED", 0) != 0;
+  np_threads = tuning_int("NAUTILUS_CSM_NP_THREADS", np_threads);
+#endif
+  if (g.w <= 32 * RC_MAXCH_SMALL && !stored) {
+    xpass_kernel<RC_MAXCH_SMALL><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+    ypass_kernel<16, 5, RC_MAXCH_SMALL><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+  } else if (g.w <= 32 * RC_MAXCH_LARGE && !stored) {
+    xpass_kernel<RC_MAXCH_LARGE><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+    ypass_kernel<16, 5, RC_MAXCH_LARGE><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   } else {
     xpass_stored_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
     ypass_stored_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   }
   dim3 gn(g.n_pool, n_tables);
-  static const int np_threads = getenv("NAUTILUS_CSM_NP_THREADS") ? atoi(getenv("NAUTILUS_CSM_NP_THREADS")) : 128;  // A/B knob: 256 / 192 / 128 / 96 / 64 threads -> 10.24 / 10.30 / 10.04 / 10.24 / 10.59 ms table stage
-  normalize_pool_kernel<<<gn, np_threads, sizeof(double) * g.w, stream>>>(
+  const size_t np_smem = sizeof(double) * g.w;
+  static SmemOptIn np_opt;
+  np_opt.allow(normalize_pool_kernel, np_smem);
+  normalize_pool_kernel<<<gn, np_threads, np_smem, stream>>>(
       g, slots, metas, pool.s, pool.e, pool.dst, pool.win, store_log ? 1 : 0);
   if (launches) *launches += 4;
 }

@@ -130,11 +130,8 @@ void launch_nn_build(const float2* points, const long long* offsets, const long 
                      cudaStream_t stream) {
   if (n_scans <= 0) return;
   const size_t smem = sizeof(int) * (size_t)n_buckets;
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(nn_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
+  static SmemOptIn opt;
+  opt.allow(nn_build_kernel, smem);
   nn_build_kernel<<<n_scans, NB_THREADS, smem, stream>>>(points, offsets, pad_off, skip_val,
                                                          skip_dim, n_buckets, inv_cell,
                                                          sorted_pts, bucket_start);
@@ -447,12 +444,8 @@ void launch_nn_match(const NnIndex& ix, const NnPair* pairs, int n_pairs, int ma
   if (n_pairs <= 0) return;
   const size_t smem = nn_match_smem_bytes(ix.n_buckets, max_tgt_points);
   if (smem <= 200 * 1024) {
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-      cudaFuncSetAttribute(nn_match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)smem);
-      configured = smem;
-    }
+    static SmemOptIn opt;
+    opt.allow(nn_match_kernel<true>, smem);
     nn_match_kernel<true><<<n_pairs, NM_THREADS, smem, stream>>>(ix, pairs, thr_f, thr_d, match_idx,
                                                                  match_dist, counters);
   } else {  // clouds too large to stage: read the grid through L1/L2

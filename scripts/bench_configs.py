@@ -4,7 +4,7 @@ point-to-point NN path (configs[4]).  One JSON line per config, CUDA-event times
 from the library, the reference's CPU code (oracle/_ref) timed beside it on a
 bounded sample.  Usage (on a B200):
 
-  python scripts/bench_configs.py [tables] [wide] [nn] [frontend] [residuals] [--cpu]
+  python scripts/bench_configs.py [tables] [wide] [solver] [nn] [frontend] [residuals] [--cpu]
 """
 import json
 import os
@@ -95,6 +95,59 @@ def bench_wide(cpu):
                                 "kind": "reference", "sample": f"{k} pairs at the reference's 1 degree step, {secs:.1f} s",
                                 "poses_bit_identical_to_gpu": bool(np.array_equal(rx, g[1]) and np.array_equal(ry, g[2]) and np.array_equal(rt, g[3]))}
         m1.close()
+    m.close()
+    return line
+
+
+def bench_solver(cpu):
+    """The matcher the Nautilus node itself constructs: CSM(30, 2, 0.3, 0.01) through the
+    5-argument overload with a 90 degree window (src/optimization/solver.cc:56, 633-638),
+    as a loop-closure batch: 400 scans, every target matched by 5 queries."""
+    n_scans, group = 400, 5
+    xy, offs, poses = synth.make_scan_set(n_scans, group=group, seed=5, return_poses=True)
+    pa, pb = synth.make_pair_list(n_scans, group=group)        # 2000 pairs
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.01)
+    rng = np.random.default_rng(5)
+    est = poses[:, 2] + rng.normal(0, 0.05, n_scans)           # pose-graph angle estimates
+    wins = np.asarray([m.rotation_window(est[a], est[b], np.pi / 2) for a, b in zip(pa, pb)])
+    m.upload_scans(xy, offs)
+    m.match_batch(pa[:50], pb[:50], wins[:50, 0], wins[:50, 1])
+    runs = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        s, x, y, th, st = m.match_batch(pa, pb, wins[:, 0], wins[:, 1], with_stats=True)
+        wall = time.perf_counter() - t0
+        runs.append((m.last_timings(), wall))
+    tm, wall = sorted(runs, key=lambda r: r[0]["ms_total"])[1]
+    cand = int(st[:, 0].sum() + st[:, 1].sum())
+    dense = 8.0 * (m.w_high ** 2 + m.w_low ** 2) * n_scans
+    line = {"config": "solver matcher CSM(30, 2, 0.3, 0.01), 5-arg overload, 90 deg window "
+                      "(solver.cc:56,633-638): 2000 pairs over 400 scans",
+            "metric": "candidate_transforms_scored_per_sec", "value": cand / (tm["ms_total"] * 1e-3),
+            "pairs_per_sec": len(pa) / (tm["ms_total"] * 1e-3), "ms": tm["ms_total"], "ms_wall": wall * 1e3,
+            "kernels_ms": {k: tm[k] for k in ("ms_tables", "ms_low", "ms_refine")},
+            "waves": tm["waves"], "w_high": m.w_high, "hi_candidates_per_window": int(st[0, 1] // max(1, st[0, 2])),
+            "mean_pops": float(st[:, 2].mean()), "spec_windows": tm["spec_windows"],
+            "tables": {"dense_layout_GBps": dense / (tm["ms_tables"] * 1e-3) / 1e9,
+                       "dense_layout_frac_of_hbm": dense / (tm["ms_tables"] * 1e-3) / 1e9 / PEAK,
+                       "note": "dense-layout bytes are the reference's 8 (W^2 + Wl^2) per table; the "
+                               "kernels move the cropped rectangle only - actual traffic: "
+                               "profiles/r2_traffic.json"}}
+    if cpu:
+        from oracle import ref
+        k = cores()
+        rm = ref.RefMatcher(30, 2, 0.3, 0.01)
+        idx = np.linspace(0, len(pa) - 1, k).astype(np.int64)
+        secs, rs, rx, ry, rt = rm.match_batch(xy, offs, pa[idx], pb[idx], wins[idx, 0], wins[idx, 1],
+                                              threads=k)
+        c1 = int(st[idx, 0].sum() + st[idx, 1].sum())
+        line["cpu_baseline"] = {"value": c1 / secs, "unit": "candidates/s", "pairs_per_sec": k / secs,
+                                "cores": k, "kind": "reference",
+                                "sample": f"{k} of {len(pa)} pairs, one pair per thread, {secs:.1f} s",
+                                "poses_bit_identical_to_gpu": bool(
+                                    np.array_equal(rx, x[idx]) and np.array_equal(ry, y[idx])
+                                    and np.array_equal(rt, th[idx])),
+                                "worst_score_rel_err": float(np.max(np.abs(rs - s[idx]) / np.abs(rs)))}
     m.close()
     return line
 
@@ -238,10 +291,10 @@ def bench_residuals(cpu):
 
 
 def main():
-    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "nn", "frontend", "residuals"]
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "solver", "nn", "frontend", "residuals"]
     cpu = "--cpu" in sys.argv
     for w in which:
-        out = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn,
+        out = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn, "solver": bench_solver,
                "frontend": bench_frontend, "residuals": bench_residuals}[w](cpu)
         for line in (out if isinstance(out, list) else [out]):
             print(json.dumps(line), flush=True)

@@ -144,8 +144,12 @@ def test_tables_edge_inputs():
         hi, lo = m.GetLookupTables(np.asarray([[9, 9], [-4.01, 0]], np.float32))
         assert not hi.values.any()
         # single point, corner points (Neumann seed + Triggs boundary), duplicates
+        # non-finite coordinates fall outside the grid (NaN like the reference's
+        # double -> uint64 conversion; +-inf / |v| >= 2^63: the reference's conversion is
+        # undefined behaviour there, the library and the oracle drop the point)
         for pts in ([[0.0, 0.0]], [[-4.0, -4.0], [3.99, 3.99]], [[1, 1], [1, 1], [1.001, 1.001]],
-                    [[-4.0, 3.99], [3.99, -4.0], [0, 0]]):
+                    [[-4.0, 3.99], [3.99, -4.0], [0, 0]],
+                    [[np.nan, 0.5], [1.0, np.nan], [np.inf, 1.0], [1.0, -np.inf], [0.5, 0.25]]):
             pts = np.asarray(pts, np.float32)
             hi, lo = m.GetLookupTables(pts)
             ph = pm.highres(pts)
@@ -203,10 +207,12 @@ def test_match_edge_inputs():
     a = np.asarray([[0.5, 0.5], [1.0, -1.0], [-2.0, 0.3]], np.float32)
     empty = np.zeros((0, 2), np.float32)
     far = np.asarray([[10.0, 0.0], [0.0, -9.0], [0.2, 0.1]], np.float32)
+    a_nan = np.asarray([[0.5, 0.5], [np.nan, 1.0], [1.0, -1.0], [np.inf, 0.0], [-2.0, 0.3]], np.float32)
     # empty target: every candidate scores log(1e-10) -> all ties, all windows popped
-    for b, win in ((empty, (-0.1, 0.1)), (far, (-0.1, 0.1)), (a, (-0.2, 0.2)), (a, (6.0, 6.5))):
-        got, st = m.GetTransformation(a, b, *win, with_stats=True)
-        want, wst = pm.match(a, b, *win, with_stats=True)
+    for qa, b, win in ((a, empty, (-0.1, 0.1)), (a, far, (-0.1, 0.1)), (a, a, (-0.2, 0.2)),
+                       (a, a, (6.0, 6.5)), (a_nan, a, (-0.2, 0.2)), (a, a_nan, (-0.2, 0.2))):
+        got, st = m.GetTransformation(qa, b, *win, with_stats=True)
+        want, wst = pm.match(qa, b, *win, with_stats=True)
         assert pose(got) == (want[1], want[2], want[3]), (got, want)
         assert abs(got[0] - want[0]) <= REL * abs(want[0])
         assert tuple(st) == tuple(int(v) for v in wst)
@@ -291,21 +297,23 @@ def test_full_size_properties():
 
 
 @pytest.mark.gpu
-def test_grid_wider_than_checkpoint_budget_vs_oracle():
-    """scanner_range 40 m at 0.03 m: 2666 cells per line, more than the 2048 the
-    checkpointed x/y passes cover, so the table build takes the stored variants
+@pytest.mark.parametrize("cfg,w", [((40, 2, 0.3, 0.03), 2666), ((40, 2, 0.3, 0.0125), 6400)])
+def test_grid_wider_than_checkpoint_budget_vs_oracle(cfg, w):
+    """Grids wider than the 2048 cells the small checkpointed x/y passes cover:
+    2666 cells per line takes the large-capacity instantiation (up to 6144 cells, the
+    one the solver's 0.01 m tables use), 6400 cells the stored variants
     (csm_tables.cu: xpass_stored_kernel / ypass_stored_kernel).  Tables bit-identical
     with margin -1, the match identical to the oracle's."""
-    pm = port.PortMatcher(40, 2, 0.3, 0.03)
+    pm = port.PortMatcher(*cfg)
     a, b, _ = synth.make_pair(23)
     ph = pm.highres(b)
     pl = pm.lowres(ph)
-    m = CorrelativeScanMatcher(40, 2, 0.3, 0.03, margin_cells=-1)
-    assert m.w_high == 2666
+    m = CorrelativeScanMatcher(*cfg, margin_cells=-1)
+    assert m.w_high == w
     hi, lo = m.GetLookupTables(b)
     assert np.array_equal(hi.values, ph.values) and np.array_equal(lo.values, pl.values)
     m.close()
-    m = CorrelativeScanMatcher(40, 2, 0.3, 0.03)
+    m = CorrelativeScanMatcher(*cfg)
     got, stats = m.GetTransformation(a, b, -0.5, 0.5, with_stats=True)
     want, wstats = pm.match(a, b, -0.5, 0.5, with_stats=True)
     assert (got[1][0][0], got[1][0][1], got[1][1]) == (want[1], want[2], want[3])

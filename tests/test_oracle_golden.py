@@ -203,3 +203,34 @@ def test_nn_port_vs_compiled_reference(ref_lib):
         idx, off, _ = nn_port.match_batch(xy, offs, src, tgt, tr, thr)
         _, want, wo = ref_lib.nn_match_batch(xy, offs, src, tgt, tr, thr)
         assert np.array_equal(off, wo) and np.array_equal(idx, want)
+
+
+# ---- the solver's own matcher: CSM(30, 2, 0.3, 0.01), 5-argument overload with a
+# 90 degree window (src/optimization/solver.cc:56, 633-638); fixtures from oracle/_ref
+@pytest.fixture(scope="module")
+def solver_golden():
+    import os
+    from conftest import ROOT
+    return np.load(os.path.join(ROOT, "tests", "golden", "solver_golden.npz"))
+
+
+def test_port_solver_config_table_vs_golden(solver_golden):
+    import hashlib
+    g = solver_golden
+    pm = port.PortMatcher(*g["params"])
+    hi = pm.highres(g["b_2"])
+    assert hi.values.shape == (6000, 6000)
+    assert hashlib.sha256(hi.values.tobytes()).digest() == bytes(g["hi_sha_2"])
+    assert np.array_equal(hi.values[g["hi_ys_2"], g["hi_xs_2"]], g["hi_vals_2"])
+    assert np.array_equal(pm.lowres(hi).values, g["lo_2"])
+
+
+@pytest.mark.parametrize("k", [2, 3])  # 3: the window wraps (rot_max += 2 pi, cc:255-257)
+def test_port_solver_config_match_vs_golden(solver_golden, k):
+    g = solver_golden
+    pm = port.PortMatcher(*g["params"])
+    rot_a, rot_b, s, x, y, th = g["match"][k]
+    lo, hi = pm.rotation_window(rot_a, rot_b, float(g["restriction"]))
+    r, st = pm.match(g[f"a_{k}"], g[f"b_{k}"], lo, hi, with_stats=True)
+    assert r == (s, np.float32(x), np.float32(y), np.float32(th))
+    assert st[1] == 900 * st[2]  # 30 x 30 hi-res candidates per popped window
