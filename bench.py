@@ -4,9 +4,11 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 A "step" is one pass of the hot path over one batch: build the lookup tables of
-the batch's 2000 target scans and match its 10 000 (query, target) pairs.  With
-N GPUs every rank owns its own batch (weak scaling, pairs are independent); the
-only exchange is an NCCL all_gather of the 48-byte per-pair results.
+the batch's target scans and match its (query, target) pairs: 10 000 pairs over
+2 000 scans per GPU.  With N GPUs there is ONE batch of N x 10 000 pairs which the
+library partitions over the ranks (nautilus_csm_match_batch_sharded: sort by target,
+balanced contiguous blocks, one ncclAllGather of the 48-byte records); the
+strong-scaling split of a single 10 000-pair batch is measured in the same run.
 
 One JSON line is printed by rank 0; see DESIGN.md "Measurement" for every key.
 """
@@ -40,6 +42,10 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scans", type=int, default=N_SCANS)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = one batch of N x 10 000 pairs partitioned over the N GPUs "
+                         "(headline); strong = the 10 000-pair batch split N ways.  The other split "
+                         "is measured too and reported under 'other_split'")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-cells", type=int, default=0, help="tuning: staged low-res table budget")
     return ap.parse_args()
@@ -51,7 +57,7 @@ def workload_config(n_scans, n_gpus):
         "pairs_per_gpu": n_scans * GROUP, "scans_per_gpu": n_scans,
         "beams": 1080, "matcher": "CSM(range=30, trans=2, low=0.3, high=0.03)",
         "rotation_window_rad": list(ROT_WINDOW), "rot_step_deg": 1.0,
-        "parallelism": f"pairs x{n_gpus} (independent batches, all_gather of results)",
+        "parallelism": "single GPU",
         "l2": "per-step working set (tables) ~10 GB >> 126 MB L2, no flush needed",
     }
 
@@ -128,12 +134,12 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
 
 
-def ncu_traffic_bytes(kernel):
-    """dram read+write bytes per launch of `kernel` from the committed ncu capture
-    (profiles/*_traffic.json, written by scripts/ncu_summary.py); None if absent."""
+def ncu_traffic():
+    """Per-kernel DRAM traffic of the committed ncu capture (profiles/traffic.json,
+    written by scripts/ncu_summary.py); None if absent."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     try:
-        return json.load(open(p)).get(kernel)
+        return json.load(open(p))
     except Exception:
         return None
 
@@ -217,8 +223,10 @@ def run_reference_arm(args):
         secs, kind, _ = cpu_reference_run(xy, offs, pa, pb, idx, cores)
         total += secs
     value = sum(cands) * args.steps / total
-    sample = (f"{n_sample} of {args.scans * GROUP} pairs per step, one pair per thread, tables "
-              f"rebuilt per pair as GetTransformation does")
+    sample = (f"{n_sample} pairs per step, evenly spaced in a {len(pa)}-pair batch over "
+              f"{min(args.scans, 200)} scans of the same generator (the full workload has "
+              f"{args.scans * GROUP} pairs; candidates/s extrapolates linearly), one pair per thread, "
+              f"tables rebuilt per pair as GetTransformation does")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -235,10 +243,39 @@ def run_reference_arm(args):
 
 
 # ---- the B200 arm --------------------------------------------------------------
+def global_batch(args, rank, world, torch, dist, dev, strong):
+    """The batch the world works on.  weak: ONE batch of world x 10 000 pairs over
+    world x 2 000 scans (every rank synthesises its 2 000 scans, the clouds are
+    exchanged once during set-up so that every rank holds the whole batch, as the
+    sharded C-ABI call expects); strong: the 10 000-pair batch of the N = 1 run."""
+    xy, offs, pa, pb = make_batch(args.scans, seed=0 if strong else rank)
+    if world == 1 or strong:
+        return xy, offs, pa, pb
+    n_pts = torch.tensor([len(xy)], device=dev, dtype=torch.int64)
+    all_n = [torch.zeros_like(n_pts) for _ in range(world)]
+    dist.all_gather(all_n, n_pts)
+    all_n = [int(v) for v in all_n]
+    mx = max(all_n)
+    buf = torch.zeros((mx, 2), device=dev, dtype=torch.float32)
+    buf[:len(xy)] = torch.from_numpy(xy).to(dev)
+    sizes = torch.zeros(args.scans, device=dev, dtype=torch.int64)
+    sizes[:] = torch.from_numpy(np.diff(offs)).to(dev)
+    xy_all = [torch.zeros_like(buf) for _ in range(world)]
+    sz_all = [torch.zeros_like(sizes) for _ in range(world)]
+    dist.all_gather(xy_all, buf)
+    dist.all_gather(sz_all, sizes)
+    xy_g = np.concatenate([t[:n].cpu().numpy() for t, n in zip(xy_all, all_n)])
+    offs_g = np.zeros(world * args.scans + 1, np.int64)
+    offs_g[1:] = np.cumsum(np.concatenate([t.cpu().numpy() for t in sz_all]))
+    pa_g = np.concatenate([pa + r * args.scans for r in range(world)]).astype(np.int32)
+    pb_g = np.concatenate([pb + r * args.scans for r in range(world)]).astype(np.int32)
+    return np.ascontiguousarray(xy_g), offs_g, pa_g, pb_g
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from nautilus_b200 import CorrelativeScanMatcher
+    from nautilus_b200 import CorrelativeScanMatcher, distributed as D
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -251,39 +288,73 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    xy, offs, pa, pb = make_batch(args.scans, seed=rank)
-    n_pairs = len(pa)
-    m = CorrelativeScanMatcher(*PARAMS, device=local, stage_cells=args.stage_cells)
+    m = CorrelativeScanMatcher(*PARAMS, device=local, stage_cells=args.stage_cells,
+                               world_rank=rank, world_size=world)
     stream = torch.cuda.current_stream()
     m.set_stream(stream.cuda_stream)
-
-    # pinned host staging for the end-to-end leg
-    xy_pin = torch.from_numpy(xy).pin_memory()
-    xy_host = xy_pin.numpy()
-    rec = torch.empty(n_pairs * m.RESULT_BYTES, dtype=torch.uint8, device=dev)
-    gathered = torch.empty(world * rec.numel(), dtype=torch.uint8, device=dev) if world > 1 else None
-
-    upload_ms = [0.0]
-
-    def step(upload):
-        if upload:
-            tu = time.perf_counter()
-            m.upload_scans(xy_host, offs)
-            upload_ms[0] = round(1e3 * (time.perf_counter() - tu), 3)
-        out = m.match_batch(pa, pb, *ROT_WINDOW, with_stats=True)
-        if world > 1:  # gather only the per-pair (pose, score) records
-            m.copy_results_dev(rec.data_ptr(), n_pairs)
-            dist.all_gather_into_tensor(gathered, rec)
-        return out
+    if world > 1:
+        # the library's own communicator: rank 0 makes the id, torch only carries the bytes
+        box = [m.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        m.comm_init(box[0])
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(upload, steps):
+    class Leg:
+        """One workload (weak or strong batch) with its two step functions."""
+
+        def __init__(self, strong):
+            self.strong = strong
+            self.xy, self.offs, self.pa, self.pb = global_batch(args, rank, world, torch, dist, dev, strong)
+            self.n_pairs = len(self.pa)
+            self.rmin = np.full(self.n_pairs, ROT_WINDOW[0])
+            self.rmax = np.full(self.n_pairs, ROT_WINDOW[1])
+            self.xy_pin = torch.from_numpy(self.xy).pin_memory()
+            self.xy_host = self.xy_pin.numpy()
+            self.upload_ms = 0.0
+            self.h2d = 0
+
+        def make_resident(self):
+            m.upload_scans(self.xy_host, self.offs)
+
+        def step_resident(self):
+            """Scans resident on every rank; one sharded call for the whole batch."""
+            if world == 1:
+                return m.match_batch(self.pa, self.pb, self.rmin, self.rmax, with_stats=True)
+            return m.match_batch_sharded(self.pa, self.pb, self.rmin, self.rmax, with_stats=True)
+
+        def step_e2e(self):
+            """Host buffers: this rank partitions the batch, uploads the scans its block
+            touches, matches the block and gathers (nautilus_csm_partition ->
+            upload_scans -> match_batch -> nautilus_csm_gather)."""
+            if world == 1:
+                tu = time.perf_counter()
+                m.upload_scans(self.xy_host, self.offs)
+                self.upload_ms = round(1e3 * (time.perf_counter() - tu), 3)
+                self.h2d = int(self.xy.nbytes + self.offs.nbytes + self.pa.nbytes + self.pb.nbytes
+                               + 16 * self.n_pairs)
+                return m.match_batch(self.pa, self.pb, self.rmin, self.rmax, with_stats=True)
+            w = m.pair_weights(self.pa, self.rmin, self.rmax, self.offs)
+            order, bounds = D.partition_pairs(self.pb, w, world)
+            mine = order[bounds[rank]:bounds[rank + 1]]
+            a, b = self.pa[mine], self.pb[mine]
+            s0 = int(min(a.min(), b.min())) if len(mine) else 0
+            s1 = int(max(a.max(), b.max())) + 1 if len(mine) else 0
+            tu = time.perf_counter()
+            sub_offs = self.offs[s0:s1 + 1] - self.offs[s0]
+            m.upload_scans(self.xy_host[self.offs[s0]:self.offs[s1]], sub_offs)
+            self.upload_ms = round(1e3 * (time.perf_counter() - tu), 3)
+            self.h2d = int(8 * (self.offs[s1] - self.offs[s0]) + sub_offs.nbytes + 24 * len(mine))
+            self.local = m.match_batch(a - s0, b - s0, self.rmin[mine], self.rmax[mine], with_stats=True)
+            self.mine = mine
+            return m.gather(order, bounds, with_stats=True)
+
+    def timed(leg, upload, steps):
         """K steps between CUDA events on the launching stream; max over ranks."""
-        acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "launches": 0, "cand": 0, "low_cand_pts": 0,
+        acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "gather": 0.0, "launches": 0, "cand": 0,
                "step_wall_ms": [], "gpu_span_ms": [], "upload_wall_ms": []}
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -291,14 +362,16 @@ def run_ours(args):
         e0.record(stream)
         for _ in range(steps):
             ts = time.perf_counter()
-            score, x, y, th, st = step(upload)
+            score, x, y, th, st = leg.step_e2e() if upload else leg.step_resident()
             acc["step_wall_ms"].append(round(1e3 * (time.perf_counter() - ts), 3))
             t = m.last_timings()
             acc["gpu_span_ms"].append(round(t["ms_total"], 3))
             if upload:
-                acc["upload_wall_ms"].append(upload_ms[0])
+                acc["upload_wall_ms"].append(leg.upload_ms)
             acc["tables"] += t["ms_tables"]; acc["low"] += t["ms_low"]; acc["refine"] += t["ms_refine"]
-            acc["launches"] += t["launches"]
+            acc["gather"] += t["ms_gather"]
+            acc["launches"] += t["launches"] + (1 if world > 1 else 0)
+            # every rank holds every result: the whole job's candidates, counted once
             acc["cand"] += int(st[:, 0].sum() + st[:, 1].sum())
         e1.record(stream)
         barrier()
@@ -308,97 +381,177 @@ def run_ours(args):
             v = torch.tensor([ms, wall_ms], device=dev, dtype=torch.float64)
             dist.all_reduce(v, op=dist.ReduceOp.MAX)
             ms, wall_ms = float(v[0]), float(v[1])
-            c = torch.tensor([acc["cand"]], device=dev, dtype=torch.int64)
-            dist.all_reduce(c)
-            acc["cand_all"] = int(c[0])
-        else:
-            acc["cand_all"] = acc["cand"]
         return ms, wall_ms, acc, (score, x, y, th, st)
 
-    m.upload_scans(xy_host, offs)
-    # NVML start-up, the sampler thread's start and its first queries (which can
-    # stall the driver for ~0.2 s) happen during the warm-up; only samples taken
-    # inside the timed region are kept
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    for _ in range(args.warmup):
-        step(False)
-    sampler.samples = []
-    ms, _, acc, last = timed(False, args.steps)          # inputs resident in HBM
-    clocks = sampler.stop() if rank == 0 else None
-    for _ in range(1):
-        step(True)
-    ms_e2e_dev, wall_e2e, acc_e2e, _ = timed(True, args.steps)  # host buffers, copies inside
+    def check_gather(leg):
+        """Before anything is timed: the gathered records of THIS rank's block are the
+        records this rank computed, every rank holds the same gathered result, and the
+        sharded call returns it too."""
+        if world == 1:
+            return {"checked": False}
+        full = leg.step_e2e()
+        for u, v in zip(full, leg.local):
+            assert np.array_equal(u[leg.mine], v), "gathered block differs from the local records"
+        leg.make_resident()
+        sharded = leg.step_resident()
+        for u, v in zip(full, sharded):
+            assert np.array_equal(u, v), "sharded call differs from partition + match + gather"
+        digest = np.frombuffer(np.ascontiguousarray(full[0]).tobytes(), np.uint8).astype(np.int64)
+        h = torch.tensor([int(digest.sum()), int((digest * (np.arange(len(digest)) % 251 + 1)).sum())],
+                         device=dev, dtype=torch.int64)
+        lo, hi = h.clone(), h.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert bool((lo == hi).all()), "ranks hold different gathered results"
+        return {"checked": True, "pairs": int(leg.n_pairs), "block_pairs": int(len(leg.mine))}
+
+    def run_leg(strong, sample_clocks):
+        leg = Leg(strong)
+        gather_check = check_gather(leg)
+        leg.make_resident()
+        # NVML start-up, the sampler thread's start and its first queries (which can
+        # stall the driver for ~0.2 s) happen during the warm-up; only samples taken
+        # inside the timed region are kept
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler is not None and rank == 0:
+            sampler.start()
+        for _ in range(args.warmup):
+            leg.step_resident()
+        if sampler is not None:
+            sampler.samples = []
+        ms, _, acc, last = timed(leg, False, args.steps)          # inputs resident in HBM
+        clocks = sampler.stop() if (sampler is not None and rank == 0) else None
+        leg.step_e2e()
+        ms_e2e_dev, wall_e2e, acc_e2e, _ = timed(leg, True, args.steps)  # host buffers, copies inside
+        return leg, ms, acc, last, clocks, ms_e2e_dev, wall_e2e, acc_e2e, gather_check
+
+    main_strong = args.scaling == "strong" and world > 1
+    leg, ms, acc, last, clocks, ms_e2e_dev, wall_e2e, acc_e2e, gather_check = run_leg(main_strong, True)
     ms_e2e = max(ms_e2e_dev, wall_e2e)  # the call is synchronous: host time counts
+    other = None
+    if world > 1:  # the other split of the same machine, as a second line inside this one
+        o_leg, o_ms, o_acc, _, _, o_dev, o_wall, o_acc_e2e, o_check = run_leg(not main_strong, False)
+        o_e2e = max(o_dev, o_wall)
+        other = {"scaling": "weak" if main_strong else "strong",
+                 "workload": ("one batch of %d pairs split over %d GPUs" % (o_leg.n_pairs, world)),
+                 "value": o_acc["cand"] / (o_ms * 1e-3), "unit": UNIT, "ms_per_step": o_ms / args.steps,
+                 "pairs_per_sec": o_leg.n_pairs * args.steps / (o_ms * 1e-3),
+                 "e2e": {"value": o_acc_e2e["cand"] / (o_e2e * 1e-3), "unit": UNIT,
+                         "ms_per_step": o_e2e / args.steps, "h2d_bytes_per_step": o_leg.h2d,
+                         "d2h_bytes_per_step": int(48 * o_leg.n_pairs)},
+                 "kernels_ms_per_step_rank0": {k: o_acc[k] / args.steps for k in ("tables", "low", "refine", "gather")},
+                 "gather_check": o_check}
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     score, x, y, th, st = last
-    value = acc["cand_all"] / (ms * 1e-3)
-    e2e_value = acc_e2e["cand_all"] / (ms_e2e * 1e-3)
-    # roofline of the dominant kernel (low-res scorer): algorithmic bytes = one
-    # 8-byte table read per (candidate, point)  [SURVEY 8(d): 8*N B per candidate]
+    xy, offs, pa, pb, n_pairs = leg.xy, leg.offs, leg.pa, leg.pb, leg.n_pairs
+    value = acc["cand"] / (ms * 1e-3)
+    e2e_value = acc_e2e["cand"] / (ms_e2e * 1e-3)
+    # ---- roofline of the dominant kernel, the low-res scorer (rank 0's block).  What
+    # binds it is one fp64 add per (candidate, point) in point order (DESIGN.md 3, K5);
+    # the byte views SURVEY 8(d) asks for (8 B per (candidate, point) against HBM and
+    # against shared memory) are kept as secondary keys.
     pts = (offs[1:] - offs[:-1])[pa].astype(np.int64)
-    low_bytes = float((st[:, 0] * pts).sum() * 8) * args.steps
+    adds_all = float((st[:, 0] * pts).sum())                  # whole batch, one step
+    if world > 1:  # rank 0 timed its own block only
+        w = m.pair_weights(pa, leg.rmin, leg.rmax, offs)
+        order, bounds = D.partition_pairs(pb, w, world)
+        mine = order[bounds[0]:bounds[1]]
+        adds = float((st[mine, 0] * pts[mine]).sum()) * args.steps
+    else:
+        adds = adds_all * args.steps
+    low_s = acc["low"] * 1e-3
     waves = max(1, m.last_timings()["waves"])
     peak, peak_kind = measured_peak_gbs()
-    achieved = low_bytes / (acc["low"] * 1e-3) / 1e9
     props = torch.cuda.get_device_properties(local)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    smem_peak = props.multi_processor_count * 128 * sm_mhz * 1e6 / 1e9
-    fp64_peak = props.multi_processor_count * 64 * sm_mhz * 1e6 / 1e9       # Gadd/s
-    fp64_achieved = low_bytes / 8.0 / (acc["low"] * 1e-3) / 1e9             # one add per table read
-    table_bytes = 8.0 * (m.w_high ** 2 + m.w_low ** 2) * args.scans * args.steps
+    n_sm = props.multi_processor_count
+    fp64_peak = n_sm * 64 * sm_mhz * 1e6 / 1e9       # Gadd/s: 2 warp-DADD / clk / SM (scripts/micro/dadd_bench.cu)
+    smem_peak = n_sm * 128 * sm_mhz * 1e6 / 1e9      # GB/s
+    fp64_achieved = adds / low_s / 1e9
+    traffic = ncu_traffic()
+    tot_k = acc["tables"] + acc["low"] + acc["refine"] + acc["gather"]
+    n_tables = args.scans if (world == 1 or main_strong) else args.scans  # per rank and step (weak: its own 2000)
+    if main_strong:
+        n_tables = args.scans / world
+    dense_bytes = 8.0 * (m.w_high ** 2 + m.w_low ** 2) * n_tables * args.steps
+    tab = {"ms_per_step": acc["tables"] / args.steps, "share": acc["tables"] / tot_k,
+           "dense_layout_GBps": dense_bytes / (acc["tables"] * 1e-3) / 1e9,
+           "dense_layout_note": "8 (W^2 + Wl^2) B per table, the reference's dense layout (SURVEY 8d); "
+                                "the kernels only compute the cropped rectangle, so this is NOT a "
+                                "bandwidth the hardware sees"}
+    per_table = traffic.get("table_bytes_per_table") if traffic else None
+    if per_table:
+        actual = per_table * n_tables * args.steps / (acc["tables"] * 1e-3) / 1e9
+        tab.update({"bound": "hbm", "actual_GBps": actual, "peak": peak, "frac": actual / peak,
+                    "dram_bytes_per_table": per_table,
+                    "min_bytes_per_table": traffic.get("table_min_bytes_per_table"),
+                    "traffic_over_min": (per_table / traffic["table_min_bytes_per_table"]
+                                         if traffic.get("table_min_bytes_per_table") else None),
+                    "traffic_source": traffic.get("_source")})
     kernels = {
-        "low_score_kernel": {"ms_per_step": acc["low"] / args.steps,
-                             "share": acc["low"] / (acc["tables"] + acc["low"] + acc["refine"])},
-        "refine_kernels": {"ms_per_step": acc["refine"] / args.steps,
-                           "share": acc["refine"] / (acc["tables"] + acc["low"] + acc["refine"]),
+        "low_score_kernel": {"ms_per_step": acc["low"] / args.steps, "share": acc["low"] / tot_k},
+        "refine_kernels": {"ms_per_step": acc["refine"] / args.steps, "share": acc["refine"] / tot_k,
                            "kernels": "refine_first + refine_spec + refine_finish",
                            "speculative_windows_per_step": m.last_timings()["spec_windows"]},
-        "table_kernels": {"ms_per_step": acc["tables"] / args.steps,
-                          "share": acc["tables"] / (acc["tables"] + acc["low"] + acc["refine"]),
-                          "algorithmic_GBps": table_bytes / (acc["tables"] * 1e-3) / 1e9,
-                          "frac_of_hbm_peak": table_bytes / (acc["tables"] * 1e-3) / 1e9 / peak},
+        "table_kernels": tab,
     }
+    if world > 1:
+        kernels["nccl_all_gather"] = {"ms_per_step": acc["gather"] / args.steps, "share": acc["gather"] / tot_k,
+                                      "bytes_per_rank": int(48 * n_pairs / world)}
+    cfg = workload_config(args.scans, world)
+    if world > 1:
+        cfg["parallelism"] = (
+            f"one batch of {n_pairs} pairs over {len(offs) - 1} scans, partitioned by the library over "
+            f"{world} ranks (sorted by target, blocks balanced by N_theta*N_t^2*N), ncclAllGather of the "
+            f"48-byte records inside nautilus_csm_match_batch_sharded; every rank ends with all results")
+        cfg["pairs_total"] = int(n_pairs)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.scans, world),
-        "pairs_per_sec": world * n_pairs * args.steps / (ms * 1e-3),
+        "scaling": "strong" if main_strong else "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": cfg,
+        "pairs_per_sec": n_pairs * args.steps / (ms * 1e-3),
         "e2e": {"value": e2e_value, "unit": UNIT,
-                "h2d_bytes_per_step": int(xy.nbytes + offs.nbytes + pa.nbytes + pb.nbytes + 16 * n_pairs),
-                "d2h_bytes_per_step": int(48 * n_pairs),
+                "h2d_bytes_per_step": leg.h2d, "d2h_bytes_per_step": int(48 * n_pairs),
                 "ms_per_step": ms_e2e / args.steps,
                 "ms_per_step_device_events": ms_e2e_dev / args.steps,
-                "ms_per_step_host_wall": wall_e2e / args.steps},
+                "ms_per_step_host_wall": wall_e2e / args.steps,
+                "path": ("nautilus_csm_upload_scans + nautilus_csm_match_batch" if world == 1 else
+                         "per rank: nautilus_csm_partition + upload of the block's scans + "
+                         "nautilus_csm_match_batch + nautilus_csm_gather")},
         "gpu_launches": acc["launches"],
         "clocks": clocks,
-        "roofline": {"kernel": "low_score_kernel", "bound": "hbm", "achieved": achieved,
-                     "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic_bytes("low_score_kernel"),
-                     "peak_source": peak_kind, "launches": waves * args.steps,
-                     "smem_peak": smem_peak, "smem_frac": achieved / smem_peak,
-                     "fp64_add_peak": fp64_peak, "fp64_add_achieved": fp64_achieved,
-                     "fp64_add_frac": fp64_achieved / fp64_peak,
-                     "note": "algorithmic 8 B per (candidate, point), SURVEY 8(d).  The kernel "
-                             "stages its table in shared memory and loads a patch once per run "
-                             "of points that share it, so neither HBM (traffic ~0, frac > 1 "
-                             "expected) nor shared memory (smem_peak = SMs x 128 B/clk x SM "
-                             "clock) binds it: what remains is one fp64 add per (candidate, "
-                             "point) in point order.  fp64_add_peak = SMs x 64 adds/clk x SM "
-                             "clock (measured: scripts/micro/dadd_bench.cu, 2 warp-DADD/clk/SM), "
-                             "in Gadd/s; fp64_add_frac is the binding fraction (DESIGN.md 3)"},
+        "roofline": {"kernel": "low_score_kernel", "bound": "fp64_add", "achieved": fp64_achieved,
+                     "peak": fp64_peak, "unit": "Gadd/s", "frac": fp64_achieved / fp64_peak,
+                     "traffic": (traffic or {}).get("low_score_kernel_bytes_per_launch"),
+                     "peak_source": f"{n_sm} SMs x 64 fp64 add/clk x {sm_mhz:.0f} MHz sampled in the timed "
+                                    "region (pipe rate measured by scripts/micro/dadd_bench.cu; derived, "
+                                    "not driver-measured)",
+                     "launches": waves * args.steps,
+                     "units_per_launch": adds / (waves * args.steps),
+                     "ncu_fp64_pipe_pct": (traffic or {}).get("low_score_kernel_fp64_pipe_pct"),
+                     "hbm_view": {"algorithmic_GBps": 8.0 * fp64_achieved, "peak": peak,
+                                  "peak_source": peak_kind, "frac": 8.0 * fp64_achieved / peak},
+                     "smem_view": {"algorithmic_GBps": 8.0 * fp64_achieved, "peak": smem_peak,
+                                   "frac": 8.0 * fp64_achieved / smem_peak},
+                     "note": "one fp64 add per (candidate, point), summed in point order like cc:66-77; "
+                             "the staged table lives in shared memory and a patch is loaded once per run "
+                             "of points that share it, so the SURVEY 8(d) byte model (8 B per (candidate, "
+                             "point)) describes neither HBM (traffic ~ 0) nor shared memory: both views "
+                             "exceed 1 and are informational only"},
         "kernels": kernels,
         "step_wall_ms": {"resident": acc["step_wall_ms"], "e2e": acc_e2e["step_wall_ms"],
                          "e2e_upload": acc_e2e["upload_wall_ms"],
                          "resident_gpu_span": acc["gpu_span_ms"], "e2e_gpu_span": acc_e2e["gpu_span_ms"]},
     }
-    if not args.no_cpu_baseline:
+    if world > 1:
+        line["gather_check"] = gather_check
+        line["other_split"] = other
+    if not args.no_cpu_baseline and world == 1:
         cores = host_cores()
         n_sample = min(n_pairs, 60 * cores)   # ~15 s of all-core CPU work
         idx = np.linspace(0, n_pairs - 1, n_sample).astype(np.int64)

@@ -68,6 +68,8 @@ typedef struct NautilusCsmParams {
   int32_t max_tables;   /* resident hi-res table slots per wave; 0 => auto     */
   int32_t stage_cells;  /* shared-memory budget of the low-res scorer's staged table,
                            in doubles; 0 => default                             */
+  int32_t world_rank;   /* multi-GPU (one process per GPU): this process's rank ...  */
+  int32_t world_size;   /* ... of world_size; 0 or 1 => single GPU                 */
 } NautilusCsmParams;
 
 /* Per-pair search statistics, counted by the same rule as the oracle:
@@ -87,6 +89,7 @@ typedef struct NautilusCsmTimings {
   int32_t launches;  /* kernels launched by the call                           */
   int32_t waves;     /* table waves the call was split into                    */
   int32_t spec_windows; /* hi-res windows scored speculatively (K6 queue length) */
+  float ms_gather;   /* NCCL all-gather of the result records (sharded calls)  */
 } NautilusCsmTimings;
 
 const char* nautilus_csm_last_error(void);
@@ -160,6 +163,58 @@ int nautilus_csm_match_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t
  * order, each { double score; float x, y, theta; int32 status; int64 n_low,
  * n_high, n_pops; }.  dst_dev is a DEVICE pointer; the copy is stream-ordered. */
 int nautilus_csm_copy_results_dev(NautilusCsm* h, void* dst_dev, int32_t n_pairs);
+
+/* --- multi-GPU: one batch partitioned over the GPUs of a box ---------------------
+ * The reference has no distributed runtime; pairs are independent
+ * (CorrelativeScanMatcher.cc:145-245 keeps no cross-pair state), so a batch is cut
+ * into world_size blocks, each rank matches its block, and the only exchange is one
+ * ncclAllGather of the 48-byte result records on the search stream.  One process per
+ * GPU; libnccl.so.2 is bound at run time (dlopen), so a process that already holds
+ * an NCCL (e.g. torch's) shares it and a single-GPU caller needs none.
+ *
+ * Partition (pure host code, no handle, no GPU): pairs sorted by target scan id
+ * (stable), cut into world_size contiguous blocks of near-equal total weight, so the
+ * pairs that share a lookup table land on the rank that builds it; a target whose
+ * pairs straddle a cut is rasterised on both sides (8.6 KB of points against a 32 MB
+ * table).  order: permutation of 0..n_pairs-1; rank r owns
+ * order[bounds[r] .. bounds[r+1]).  weights == NULL => equal weights. */
+int nautilus_csm_partition(const int32_t* b_ids, const double* weights, int32_t n_pairs,
+                           int32_t world_size, int32_t* order, int64_t* bounds);
+/* Low-res work of every pair, N_theta * N_t^2 * N (rotation steps of cc:92-93,
+ * translations of cc:96-99, points of the query scan); scan_offsets = the offsets
+ * array of nautilus_csm_upload_scans. */
+int nautilus_csm_pair_weights(const NautilusCsmParams* params, const int32_t* a_ids,
+                              const double* rot_min, const double* rot_max,
+                              const int64_t* scan_offsets, int32_t n_pairs, double* weights);
+
+/* Bootstrap.  Rank 0 calls comm_unique_id and hands the 128 bytes to every rank by
+ * whatever channel the host program has (the Nautilus node would use its launcher's
+ * environment or a ROS parameter; bench.py broadcasts it); every rank then calls
+ * comm_init with the handle created with its world_rank / world_size.  Collective. */
+#define NAUTILUS_COMM_ID_BYTES 128
+int nautilus_csm_comm_unique_id(void* id_out);
+int nautilus_csm_comm_init(NautilusCsm* h, const void* id);
+/* Alternative: use a caller-owned ncclComm_t of the same world (not destroyed by the
+ * library). */
+int nautilus_csm_comm_attach(NautilusCsm* h, void* nccl_comm, int32_t world_rank,
+                             int32_t world_size);
+
+/* After this rank matched ITS block with nautilus_csm_match_batch (pairs
+ * order[bounds[rank] .. bounds[rank+1]) in that order): all-gathers every rank's
+ * records and writes all n_pairs = bounds[world_size] results in caller order.
+ * Collective; every rank receives everything. */
+int nautilus_csm_gather(NautilusCsm* h, const int32_t* order, const int64_t* bounds,
+                        double* score, float* x, float* y, float* theta,
+                        NautilusCsmStats* stats);
+
+/* nautilus_csm_match_batch for one batch split over the world: every rank passes the
+ * SAME arguments (the whole batch; the scan set resident on every rank), the library
+ * partitions, matches this rank's block, gathers, and every rank returns all results.
+ * With world_size 1 it is nautilus_csm_match_batch. */
+int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
+                                     const double* rot_min, const double* rot_max,
+                                     int32_t n_pairs, double* score, float* x, float* y,
+                                     float* theta, NautilusCsmStats* stats);
 
 /* Single pair from host clouds = batch of one (upload + tables + search). */
 int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b,

@@ -455,11 +455,15 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
   const double wld = floor((p->scanner_range * 2.0) / p->low_res);
   if (wd < 1 || wd > 30000 || wld < 1 || wld > 65000)
     return fail(NAUTILUS_EINVAL, "table dimensions out of the supported range");
+  if (p->world_size > 1 && (p->world_rank < 0 || p->world_rank >= p->world_size))
+    return fail(NAUTILUS_EINVAL, "world_rank outside [0, world_size)");
   NautilusCsm* h = new NautilusCsm();
   h->params = *p;
   h->device = p->device;
   h->sm_count = prop.multiProcessorCount;
   h->rot_step = p->rot_step > 0 ? p->rot_step : M_PI / 180;
+  h->world_size = p->world_size > 1 ? p->world_size : 1;
+  h->world_rank = p->world_size > 1 ? p->world_rank : 0;
   h->geo.w = (int)wd;
   h->geo.wl = (int)wld;
   h->geo.res_h = p->high_res;
@@ -503,6 +507,8 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
+  nautilus_internal_comm_release(h);
+  h->gather_dev.release(); h->gather_pin.release();
   free_slots(h);
   h->nn.release();
   h->pool_dev.release();
@@ -583,15 +589,22 @@ int require_tiling(NautilusCsm* h) {
   return NAUTILUS_OK;
 }
 
-// Core of GetTransformation for a batch over one scan set.
-int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const int32_t* b_ids,
-                     const double* rot_min, const double* rot_max, int32_t n_pairs,
-                     double* score, float* x, float* y, float* theta, NautilusCsmStats* stats) {
+}  // namespace
+
+// Core of GetTransformation for a batch over one scan set, first half: validates,
+// plans and launches everything; the records land in h->results_dev (room for
+// result_capacity >= n_pairs of them) in caller order.  Nothing is copied back and
+// the stream is not synchronised: nautilus_internal_match_collect does that, and a
+// sharded call puts its all-gather in between.
+int nautilus_internal_match_launch(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids,
+                                   const int32_t* b_ids, const double* rot_min,
+                                   const double* rot_max, int32_t n_pairs,
+                                   size_t result_capacity) {
   if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
   h->timings = NautilusCsmTimings{};
+  h->pending = PendingBatch{};
   if (n_pairs == 0) return NAUTILUS_OK;
-  if (!a_ids || !b_ids || !rot_min || !rot_max || !score || !x || !y || !theta)
-    return fail(NAUTILUS_EINVAL, "null argument");
+  if (!a_ids || !b_ids || !rot_min || !rot_max) return fail(NAUTILUS_EINVAL, "null argument");
   if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
   if (h->grid_rc) return fail(h->grid_rc, h->grid_error);
   int rc = require_tiling(h);
@@ -760,7 +773,7 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
 
   if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
   if ((rc = h->rots_dev.reserve(rots.size()))) return rc;
-  if ((rc = h->results_dev.reserve(n_pairs))) return rc;
+  if ((rc = h->results_dev.reserve(std::max<size_t>(n_pairs, result_capacity)))) return rc;
   CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted, sizeof(PairWork) * n_pairs,
                          cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
@@ -786,21 +799,22 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     if (next < n_waves && (rc = issue_tables(next))) return rc;
   }
   CU_TRY(cudaGetLastError());
-  if ((rc = h->results_pin.reserve(n_pairs))) return rc;
-  if ((rc = h->spec_counts_pin.reserve(2 * (size_t)n_waves))) return rc;
-  PairResult* res = h->results_pin.p;
-  int* spec_counts = h->spec_counts_pin.p;
-  for (int k = 0; k < 2 * n_waves; ++k) spec_counts[k] = 0;
-  CU_TRY(cudaMemcpyAsync(res, h->results_dev.p, sizeof(PairResult) * n_pairs,
-                         cudaMemcpyDeviceToHost, st));
-  if (!rf_serial)
-    CU_TRY(cudaMemcpyAsync(spec_counts, h->spec_counters_dev.p, sizeof(int) * 2 * n_waves,
-                           cudaMemcpyDeviceToHost, st));
-  CU_TRY(cudaStreamSynchronize(st));
+  h->pending.n_pairs = n_pairs;
+  h->pending.n_waves = n_waves;
+  h->pending.launches = launches;
+  h->pending.rf_serial = rf_serial;
+  h->last_n_pairs = n_pairs;
+  return NAUTILUS_OK;
+}
 
-  h->timings.launches = launches;
+// Second half, after the caller synchronised the stream: timings of the launched
+// batch from its events and the speculative-queue counters.
+int nautilus_internal_match_timings(NautilusCsm* h, const int* spec_counts) {
+  const int n_waves = h->pending.n_waves;
+  auto evt = [&](int w, int k) { return get_event(h, 1 + 5 * (size_t)w + k); };
+  h->timings.launches = h->pending.launches;
   h->timings.waves = n_waves;
-  for (int w = 0; w < n_waves; ++w) h->timings.spec_windows += spec_counts[2 * w];
+  for (int w = 0; w < n_waves; ++w) h->timings.spec_windows += spec_counts ? spec_counts[2 * w] : 0;
   for (int w = 0; w < n_waves; ++w) {
     float a = 0, b = 0, c = 0;
     cudaEventElapsedTime(&a, evt(w, 0), evt(w, 1));
@@ -808,9 +822,41 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     cudaEventElapsedTime(&c, evt(w, 3), evt(w, 4));
     h->timings.ms_tables += a; h->timings.ms_low += b; h->timings.ms_refine += c;
   }
-  cudaEventElapsedTime(&h->timings.ms_total, get_event(h, 0), evt(n_waves - 1, 4));
+  if (n_waves > 0) cudaEventElapsedTime(&h->timings.ms_total, get_event(h, 0), evt(n_waves - 1, 4));
+  return NAUTILUS_OK;
+}
 
-  h->last_n_pairs = n_pairs;
+// Queues the D2H copy of the speculative-queue counters of the launched batch.
+int nautilus_internal_queue_spec_counts(NautilusCsm* h, int** out) {
+  const int n_waves = h->pending.n_waves;
+  int rc;
+  if ((rc = h->spec_counts_pin.reserve(2 * (size_t)std::max(1, n_waves)))) return rc;
+  int* spec_counts = h->spec_counts_pin.p;
+  for (int k = 0; k < 2 * n_waves; ++k) spec_counts[k] = 0;
+  if (!h->pending.rf_serial && n_waves > 0)
+    CU_TRY(cudaMemcpyAsync(spec_counts, h->spec_counters_dev.p, sizeof(int) * 2 * n_waves,
+                           cudaMemcpyDeviceToHost, h->stream));
+  *out = spec_counts;
+  return NAUTILUS_OK;
+}
+
+namespace {
+
+int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const int32_t* b_ids,
+                     const double* rot_min, const double* rot_max, int32_t n_pairs,
+                     double* score, float* x, float* y, float* theta, NautilusCsmStats* stats) {
+  if (n_pairs > 0 && (!score || !x || !y || !theta)) return fail(NAUTILUS_EINVAL, "null argument");
+  int rc = nautilus_internal_match_launch(h, ss, a_ids, b_ids, rot_min, rot_max, n_pairs, 0);
+  if (rc || n_pairs == 0) return rc;
+  cudaStream_t st = h->stream;
+  if ((rc = h->results_pin.reserve(n_pairs))) return rc;
+  PairResult* res = h->results_pin.p;
+  int* spec_counts = nullptr;
+  CU_TRY(cudaMemcpyAsync(res, h->results_dev.p, sizeof(PairResult) * n_pairs,
+                         cudaMemcpyDeviceToHost, st));
+  if ((rc = nautilus_internal_queue_spec_counts(h, &spec_counts))) return rc;
+  CU_TRY(cudaStreamSynchronize(st));
+  nautilus_internal_match_timings(h, spec_counts);
   int bad = 0;
   for (int p = 0; p < n_pairs; ++p) {
     score[p] = res[p].score; x[p] = res[p].x; y[p] = res[p].y; theta[p] = res[p].theta;

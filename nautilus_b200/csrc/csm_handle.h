@@ -115,6 +115,14 @@ struct PinBuf {
 }  // namespace csmh
 
 struct NautilusCsm;
+// csm_capi.cu: the two halves of a batch match (see there)
+int nautilus_internal_match_launch(NautilusCsm* h, csmh::ScanSet& ss, const int32_t* a_ids,
+                                   const int32_t* b_ids, const double* rot_min,
+                                   const double* rot_max, int32_t n_pairs, size_t result_capacity);
+int nautilus_internal_queue_spec_counts(NautilusCsm* h, int** out);
+int nautilus_internal_match_timings(NautilusCsm* h, const int* spec_counts);
+// csm_comm.cu: releases the handle's communicator
+void nautilus_internal_comm_release(NautilusCsm* h);
 // frontend.cu: makes ScanSet::host_xy of the user scans valid (D2H when the clouds
 // were produced on the device)
 int nautilus_internal_host_xy(NautilusCsm* h);
@@ -131,6 +139,12 @@ using namespace csmh;
 #define NAUTILUS_GUARD(h)                                               \
   std::lock_guard<std::recursive_mutex> nautilus_guard_((h)->mu);       \
   cudaSetDevice((h)->device)
+
+// A launched, not yet collected batch (nautilus_internal_match_launch).
+struct PendingBatch {
+  int n_pairs = 0, n_waves = 0, launches = 0;
+  bool rf_serial = false;
+};
 
 struct NautilusCsm {
   mutable std::recursive_mutex mu;
@@ -193,6 +207,17 @@ struct NautilusCsm {
   std::vector<cudaEvent_t> events;
   NautilusCsmTimings timings{};
   int last_n_pairs = 0;
+  PendingBatch pending;
+
+  // multi-GPU (csm_comm.cu): one process per GPU, NCCL bound at run time
+  void* nccl_comm = nullptr;   // ncclComm_t
+  bool comm_owned = false;     // created by nautilus_csm_comm_init (else attached)
+  int world_rank = 0, world_size = 1;
+  DevBuf<PairResult> gather_dev;
+  PinBuf<PairResult> gather_pin;
+  std::vector<int> shard_order, shard_a, shard_b;
+  std::vector<long long> shard_bounds;
+  std::vector<double> shard_w, shard_rmin, shard_rmax;
 
   // residual evaluation (residuals.cu)
   DevBuf<unsigned char> residual_arena;

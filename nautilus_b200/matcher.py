@@ -81,12 +81,14 @@ class CorrelativeScanMatcher:
     def __init__(self, scanner_range: float, trans_range: float, low_res: float,
                  high_res: float, *, rot_step: float = 0.0, device: int = 0,
                  margin_cells: int = 0, max_tables: int = 0, blur_sigma: float = 0.0,
-                 stage_cells: int = 0):
+                 stage_cells: int = 0, world_rank: int = 0, world_size: int = 1):
         self._L = _lib.lib()
         self.range_, self.trans_range_ = float(scanner_range), float(trans_range)
         self.low_res_, self.high_res_ = float(low_res), float(high_res)
         p = Params(scanner_range, trans_range, low_res, high_res, rot_step, blur_sigma,
-                   device, margin_cells, max_tables, stage_cells)
+                   device, margin_cells, max_tables, stage_cells, world_rank, world_size)
+        self._params = p
+        self.world_rank, self.world_size = (world_rank, world_size) if world_size > 1 else (0, 1)
         h = C.c_void_p()
         check(self._L.nautilus_csm_create(C.byref(p), C.byref(h)))
         self._h = h
@@ -263,6 +265,51 @@ class CorrelativeScanMatcher:
         x, y, th = (np.empty(n, np.float32) for _ in range(3))
         stats = np.zeros((n, 3), np.int64) if with_stats else None
         check(self._L.nautilus_csm_match_batch(
+            self._h, ptr(a_ids), ptr(b_ids), ptr(rot_min), ptr(rot_max), n, ptr(score), ptr(x),
+            ptr(y), ptr(th), ptr(stats) if with_stats else None))
+        return (score, x, y, th, stats) if with_stats else (score, x, y, th)
+
+    # ---- multi-GPU: one batch partitioned over the ranks (include/nautilus_csm.h) ----
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """ncclGetUniqueId through the library; rank 0 calls it and distributes the bytes."""
+        buf = C.create_string_buffer(128)
+        check(_lib.lib().nautilus_csm_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes) -> None:
+        """ncclCommInitRank for this handle's (world_rank, world_size).  Collective."""
+        assert len(unique_id) == 128
+        check(self._L.nautilus_csm_comm_init(self._h, C.c_char_p(unique_id)))
+
+    def pair_weights(self, a_ids, rot_min, rot_max, offsets) -> np.ndarray:
+        from . import distributed
+        return distributed.pair_weights_c(self._params, a_ids, rot_min, rot_max, offsets)
+
+    def gather(self, order, bounds, *, with_stats: bool = False):
+        """After match_batch on this rank's block: all ranks' results in caller order."""
+        order = np.ascontiguousarray(order, dtype=np.int32)
+        bounds = np.ascontiguousarray(bounds, dtype=np.int64)
+        n = int(bounds[-1])
+        score = np.empty(n, np.float64)
+        x, y, th = (np.empty(n, np.float32) for _ in range(3))
+        stats = np.zeros((n, 3), np.int64) if with_stats else None
+        check(self._L.nautilus_csm_gather(self._h, ptr(order), ptr(bounds), ptr(score), ptr(x),
+                                          ptr(y), ptr(th), ptr(stats) if with_stats else None))
+        return (score, x, y, th, stats) if with_stats else (score, x, y, th)
+
+    def match_batch_sharded(self, a_ids, b_ids, rot_min, rot_max, *, with_stats: bool = False):
+        """match_batch of ONE batch split over the world: every rank passes the whole
+        batch and gets every result (nautilus_csm_match_batch_sharded)."""
+        a_ids = np.ascontiguousarray(a_ids, dtype=np.int32)
+        b_ids = np.ascontiguousarray(b_ids, dtype=np.int32)
+        n = len(a_ids)
+        rot_min = np.ascontiguousarray(np.broadcast_to(np.asarray(rot_min, np.float64), (n,)))
+        rot_max = np.ascontiguousarray(np.broadcast_to(np.asarray(rot_max, np.float64), (n,)))
+        score = np.empty(n, np.float64)
+        x, y, th = (np.empty(n, np.float32) for _ in range(3))
+        stats = np.zeros((n, 3), np.int64) if with_stats else None
+        check(self._L.nautilus_csm_match_batch_sharded(
             self._h, ptr(a_ids), ptr(b_ids), ptr(rot_min), ptr(rot_max), n, ptr(score), ptr(x),
             ptr(y), ptr(th), ptr(stats) if with_stats else None))
         return (score, x, y, th, stats) if with_stats else (score, x, y, th)

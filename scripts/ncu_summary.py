@@ -86,10 +86,14 @@ def full_table(rep):
         out.append(f"| {label} | " + " | ".join(vals) + " |")
     ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
     scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    ifp = hdr.index("sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active") \
+        if "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active" in hdr else None
     for k in cols:
         r = seen[k]
-        traffic[k] = (float(r[ir].replace(",", "")) * scale.get(units[ir], 1) +
-                      float(r[iw].replace(",", "")) * scale.get(units[iw], 1))
+        rd = float(r[ir].replace(",", "")) * scale.get(units[ir], 1)
+        wr = float(r[iw].replace(",", "")) * scale.get(units[iw], 1)
+        traffic[k] = {"read": rd, "write": wr, "total": rd + wr,
+                      "fp64_pipe_pct": float(r[ifp].replace(",", "")) if ifp is not None else None}
     return "\n".join(out), traffic
 
 
@@ -100,11 +104,24 @@ def main():
     shutil.copy(launches, os.path.join(PROF, f"{tag}_launches.csv"))
     lt, shares = launches_table(launches)
     ft, traffic = full_table(rep)
-    tp = os.path.join(PROF, "traffic.json")
-    old = json.load(open(tp)) if os.path.exists(tp) else {}
-    old.update(traffic)
-    old["_source"] = f"{tag}: ncu --set full, one launch per kernel, bench.py --scans 400 (2000 pairs)"
-    json.dump(old, open(tp, "w"), indent=1)
+    # traffic.json is rewritten from THIS capture only (no stale kernels of older builds)
+    n_tables = 400  # bench.py --scans 400: one table wave of 400 tables per launch
+    tab = [k for k in traffic if any(t in k for t in ("raster_kernel", "xpass_kernel", "ypass_kernel",
+                                                      "normalize_pool_kernel"))]
+    norm = [k for k in traffic if "normalize_pool_kernel" in k]
+    low = [k for k in traffic if "low_score_kernel" in k]
+    out = {"_source": f"{tag}: ncu --set full --clock-control none, one launch per kernel of "
+                      f"`python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline` "
+                      f"({n_tables} tables, {5 * n_tables} pairs per launch)",
+           "tables_per_launch": n_tables,
+           "kernels_bytes_per_launch": {k: v["total"] for k, v in traffic.items()},
+           "table_bytes_per_table": sum(traffic[k]["total"] for k in tab) / n_tables,
+           # every cell of every active rectangle is written exactly once by the normalise
+           # pass: its write bytes are the write-once minimum of this layout
+           "table_min_bytes_per_table": (traffic[norm[0]]["write"] / n_tables) if norm else None,
+           "low_score_kernel_bytes_per_launch": traffic[low[0]]["total"] if low else None,
+           "low_score_kernel_fp64_pipe_pct": traffic[low[0]]["fp64_pipe_pct"] if low else None}
+    json.dump(out, open(os.path.join(PROF, "traffic.json"), "w"), indent=1)
     md = [f"# ncu summary {tag}", "",
           "Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none` over "
           "`python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline` "

@@ -353,3 +353,44 @@ def test_concurrent_callers_on_one_handle():
         assert got[0] == want[0]
         assert got[1][0][0] == want[1][0][0] and got[1][0][1] == want[1][0][1] and got[1][1] == want[1][1]
     m.close()
+
+
+@pytest.mark.gpu
+def test_two_devices_in_one_process():
+    """Handles on two devices of one process, used from two threads at once.  The
+    >48 KB dynamic shared-memory opt-in of the low-res scorer, the refine kernels and
+    the NN kernel is a per-device attribute (csm_common.cuh SmemOptIn): the second
+    device's launches must not be refused, and both devices must return what one does."""
+    import threading
+    import torch
+    from nautilus_b200 import pose_transform
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    xy, offs = synth.make_scan_set(20, group=5, seed=11, n_beams=360)
+    pa, pb = synth.make_pair_list(20, group=5)
+    tr = np.stack([pose_transform((0.1, 0.0, 0.02), (0.0, 0.05, 0.0))] * len(pa))
+    out, errs = {}, []
+
+    def work(dev):
+        try:
+            m = CorrelativeScanMatcher(30, 2, 0.3, 0.03, device=dev)
+            m.upload_scans(xy, offs)
+            r = m.match_batch(pa, pb, -0.5, 0.5, with_stats=True)
+            m.nn_build(0.25)
+            idx, _ = m.nn_match_batch(pa, pb, tr, 0.25)
+            single = m.GetTransformation(xy[offs[0]:offs[1]], xy[offs[1]:offs[2]], -0.5, 0.5)
+            out[dev] = (r, idx, single)
+            m.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append((dev, e))
+
+    ts = [threading.Thread(target=work, args=(d,)) for d in (1, 0)]  # device 1 first
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for u, v in zip(out[0][0], out[1][0]):
+        assert np.array_equal(u, v)
+    assert np.array_equal(out[0][1], out[1][1])
+    assert out[0][2] == out[1][2]

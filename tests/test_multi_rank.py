@@ -12,6 +12,38 @@ from conftest import ROOT
 from nautilus_b200 import distributed as D
 
 
+def _np_partition(b_ids, weights, world):
+    """The partition rule restated in numpy: stable sort by target, cut at
+    the first position whose running weight reaches r / world of the total."""
+    b_ids = np.asarray(b_ids)
+    n = len(b_ids)
+    order = np.argsort(b_ids, kind="stable")
+    cum = np.cumsum(np.asarray(weights, np.float64)[order]) if n else np.zeros(0)
+    total = cum[-1] if n else 0.0
+    bounds = [0] + [int(np.searchsorted(cum, total * r / world, side="left")) if n else 0
+                    for r in range(1, world)] + [n]
+    return order, np.maximum.accumulate(np.asarray(bounds, np.int64))
+
+
+def test_c_partition_equals_numpy_rule():
+    """nautilus_csm_partition is host code of the library: it runs here without a GPU."""
+    rng = np.random.default_rng(0)
+    for trial in range(100):
+        n, world = int(rng.integers(0, 600)), int(rng.integers(1, 9))
+        b = rng.integers(0, rng.integers(1, 50) if trial % 3 else 10 ** 6, size=n)  # dense / sparse ids
+        w = rng.uniform(1, 5, size=n)
+        o1, b1 = _np_partition(b, w, world)
+        o2, b2 = D.partition_pairs(b, w, world)
+        assert np.array_equal(o1, o2) and np.array_equal(b1, b2), trial
+
+
+def test_c_pair_weights():
+    from nautilus_b200 import _lib
+    p = _lib.Params(30, 2, 0.3, 0.03, 0, 0, 0, 0, 0, 0, 0, 1)
+    w = D.pair_weights_c(p, [0, 1], [-0.5, 0.0], [0.5, 2 * np.pi], [0, 1080, 2000])
+    assert w.tolist() == [58 * 14 * 14 * 1080, 361 * 14 * 14 * 920]  # trip counts of cc:92-99
+
+
 def test_partition_properties():
     rng = np.random.default_rng(0)
     b = rng.integers(0, 40, size=500)
