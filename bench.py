@@ -355,6 +355,7 @@ def run_ours(args):
     def timed(leg, upload, steps):
         """K steps between CUDA events on the launching stream; max over ranks."""
         acc = {"tables": 0.0, "low": 0.0, "refine": 0.0, "gather": 0.0, "launches": 0, "cand": 0,
+               "host_plan": 0.0, "host_wait": 0.0, "host_collect": 0.0,
                "step_wall_ms": [], "gpu_span_ms": [], "upload_wall_ms": []}
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -370,6 +371,8 @@ def run_ours(args):
                 acc["upload_wall_ms"].append(leg.upload_ms)
             acc["tables"] += t["ms_tables"]; acc["low"] += t["ms_low"]; acc["refine"] += t["ms_refine"]
             acc["gather"] += t["ms_gather"]
+            acc["host_plan"] += t["ms_host_plan"]; acc["host_wait"] += t["ms_host_wait"]
+            acc["host_collect"] += t["ms_host_collect"]
             acc["launches"] += t["launches"] + (1 if world > 1 else 0)
             # every rank holds every result: the whole job's candidates, counted once
             acc["cand"] += int(st[:, 0].sum() + st[:, 1].sum())
@@ -440,6 +443,7 @@ def run_ours(args):
                          "ms_per_step": o_e2e / args.steps, "h2d_bytes_per_step": o_leg.h2d,
                          "d2h_bytes_per_step": int(48 * o_leg.n_pairs)},
                  "kernels_ms_per_step_rank0": {k: o_acc[k] / args.steps for k in ("tables", "low", "refine", "gather")},
+                 "host_ms_per_step_rank0": {k: o_acc["host_" + k] / args.steps for k in ("plan", "wait", "collect")},
                  "gather_check": o_check}
 
     if rank != 0:
@@ -544,6 +548,9 @@ def run_ours(args):
                              "point)) describes neither HBM (traffic ~ 0) nor shared memory: both views "
                              "exceed 1 and are informational only"},
         "kernels": kernels,
+        "host_ms_per_step": {"plan_until_last_launch": acc["host_plan"] / args.steps,
+                             "blocked_in_stream_sync": acc["host_wait"] / args.steps,
+                             "collect_after_sync": acc["host_collect"] / args.steps},
         "step_wall_ms": {"resident": acc["step_wall_ms"], "e2e": acc_e2e["step_wall_ms"],
                          "e2e_upload": acc_e2e["upload_wall_ms"],
                          "resident_gpu_span": acc["gpu_span_ms"], "e2e_gpu_span": acc_e2e["gpu_span_ms"]},

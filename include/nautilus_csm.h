@@ -90,6 +90,9 @@ typedef struct NautilusCsmTimings {
   int32_t waves;     /* table waves the call was split into                    */
   int32_t spec_windows; /* hi-res windows scored speculatively (K6 queue length) */
   float ms_gather;   /* NCCL all-gather of the result records (sharded calls)  */
+  float ms_host_plan;   /* host wall time from call entry to the last kernel launch */
+  float ms_host_collect; /* host wall time from the stream synchronise to return  */
+  float ms_host_wait;   /* host wall time blocked in the stream synchronise       */
 } NautilusCsmTimings;
 
 const char* nautilus_csm_last_error(void);
@@ -141,6 +144,15 @@ int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points
  * dimensions width x height and cell size `resolution`. out_low: w_low^2. */
 int nautilus_csm_lowres_from_table(NautilusCsm* h, const double* high, uint64_t width,
                                    uint64_t height, double resolution, double* out_low);
+
+/* LookupTable::GaussianBlur(sigma) (h:81-87 -> CImg::blur(sigma, sigma, 0, true, true),
+ * CImg.h:49337-49351) and LookupTable::normalize() (h:79 -> CImg::normalize(0, 1),
+ * CImg.h:39499-39517) on a caller-made table of width x height doubles, in place, on
+ * CUDA device `device`.  Same operations in the same order as CImg: bit-identical.
+ * For the drop-in header's LookupTable members; the batch path never calls them. */
+int nautilus_csm_table_blur(double* values, uint64_t width, uint64_t height, double sigma,
+                            int32_t device);
+int nautilus_csm_table_normalize(double* values, uint64_t width, uint64_t height, int32_t device);
 
 /* Builds (and discards) the tables of the given uploaded scans; the batch
  * form of the two calls above, used for the table-build configuration.

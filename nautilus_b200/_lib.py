@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
-SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "csm_comm.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu", "residuals.cu"]
+SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "csm_comm.cu", "csm_image_ops.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu", "residuals.cu"]
 HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
@@ -51,7 +51,8 @@ class Stats(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("ms_tables", C.c_float), ("ms_low", C.c_float),
                 ("ms_refine", C.c_float), ("launches", C.c_int32), ("waves", C.c_int32),
-                ("spec_windows", C.c_int32), ("ms_gather", C.c_float)]
+                ("spec_windows", C.c_int32), ("ms_gather", C.c_float),
+                ("ms_host_plan", C.c_float), ("ms_host_collect", C.c_float), ("ms_host_wait", C.c_float)]
 
 
 EXPORTS = [
@@ -65,6 +66,7 @@ EXPORTS = [
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_host_alloc", "nautilus_host_free",
     "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
+    "nautilus_csm_table_blur", "nautilus_csm_table_normalize",
     "nautilus_csm_partition", "nautilus_csm_pair_weights", "nautilus_csm_comm_unique_id",
     "nautilus_csm_comm_init", "nautilus_csm_comm_attach", "nautilus_csm_gather",
     "nautilus_csm_match_batch_sharded",
@@ -154,6 +156,8 @@ def lib():
     L.nautilus_csm_build_tables.argtypes = [vp, vp, i32, C.POINTER(d)]
     L.nautilus_csm_match_batch.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp]
     L.nautilus_csm_copy_results_dev.argtypes = [vp, vp, i32]
+    L.nautilus_csm_table_blur.argtypes = [vp, u64, u64, d, i32]
+    L.nautilus_csm_table_normalize.argtypes = [vp, u64, u64, i32]
     L.nautilus_csm_partition.argtypes = [vp, vp, i32, i32, vp, vp]
     L.nautilus_csm_pair_weights.argtypes = [C.POINTER(Params), vp, vp, vp, vp, i32, vp]
     L.nautilus_csm_comm_unique_id.argtypes = [vp]

@@ -1,10 +1,15 @@
 // Drop-in replacement for third_party/csm/src/CorrelativeScanMatcher.h of
 // ut-amrl/nautilus (reference lines cited per member): same include name, same
-// class and method names, argument meaning and error behaviour, but every
-// method forwards to libnautilus_csm_b200.so (include/nautilus_csm.h), i.e. to
-// the sm_100a kernels.  Header-only; link with -lnautilus_csm_b200.
+// struct / class and member names, argument meaning and error behaviour, but every
+// compute member forwards to libnautilus_csm_b200.so (include/nautilus_csm.h), i.e.
+// to the sm_100a kernels.  Header-only; link with -lnautilus_csm_b200.
 //
-// Every public member of the reference class is here (h:112-152).
+// Every public member of the reference's LookupTable (h:27-110) and
+// CorrelativeScanMatcher (h:112-152) is here, together with the header's global
+// `using` declarations (h:21-24), so that the reference's own unit tests
+// (third_party/csm/test/correlative_scan_matcher_tests.cc) and its callers
+// (src/optimization/solver.cc:56,633, bag_pair_matcher.cc, bag_avg_matcher.cc)
+// compile against it unchanged (tests/test_gpu_shim.py builds the former).
 #ifndef SRC_CORRELATIVESCANMATCHER_H_
 #define SRC_CORRELATIVESCANMATCHER_H_
 
@@ -12,14 +17,69 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <memory>
+#include <mutex>
+#include <string>
 #include <utility>
 #include <vector>
 
+#if defined(__has_include)
+#if __has_include("eigen3/Eigen/Dense")
+#include "eigen3/Eigen/Dense"
+#else
 #include "Eigen/Dense"
+#endif
+#else
+#include "eigen3/Eigen/Dense"
+#endif
 #include "nautilus_csm.h"
+
+// The reference stores a table in a CImg<double> (h:31, "./CImg.h", 79 805 lines).
+// A build that has CImg.h beside this header keeps the real class (so that
+// GetDebugImage() can be handed to CImgDisplay as bag_pair_matcher.cc:195-200 does);
+// otherwise the few CImg members the reference's LookupTable callers touch are
+// provided by the stand-in below.
+#if defined(__has_include) && !defined(NAUTILUS_CSM_NO_CIMG)
+#if __has_include("./CImg.h")
+#include "./CImg.h"
+#define NAUTILUS_CSM_HAVE_CIMG 1
+#endif
+#endif
+#ifndef NAUTILUS_CSM_HAVE_CIMG
+namespace cimg_library {
+template <typename T>
+struct CImg {
+  unsigned int _width = 0, _height = 0;
+  std::vector<T> _data;
+  CImg() {}
+  CImg(unsigned int w, unsigned int h, unsigned int = 1, unsigned int = 1, T fill = T(0))
+      : _width(w), _height(h), _data((size_t)w * h, fill) {}
+  T& operator()(unsigned int x, unsigned int y) { return _data[x + (size_t)y * _width]; }
+  const T& operator()(unsigned int x, unsigned int y) const { return _data[x + (size_t)y * _width]; }
+  T* data() { return _data.data(); }
+  const T* data() const { return _data.data(); }
+  int width() const { return (int)_width; }
+  int height() const { return (int)_height; }
+  size_t size() const { return _data.size(); }
+  bool is_empty() const { return _data.empty(); }
+  CImg<T>& fill(T v) { _data.assign(_data.size(), v); return *this; }
+  CImg<T>& clear() { _width = _height = 0; _data.clear(); return *this; }  // CImg::clear empties the image
+  T max() const {
+    T m = _data.empty() ? T(0) : _data[0];
+    for (const T& v : _data) m = v > m ? v : m;
+    return m;
+  }
+};
+}  // namespace cimg_library
+#endif
 
 #define DEFAULT_GAUSSIAN_SIGMA 4       // h:19
 #define MIN_VALUE_FOR_LOOKUP 1E-10     // h:20
+
+using cimg_library::CImg;              // h:21-24
+using Eigen::Vector2f;
+using std::pair;
+using std::vector;
 
 namespace nautilus_b200_detail {
 inline void Fatal(const char* what) {  // glog CHECK / LOG(FATAL): abort the process
@@ -29,35 +89,25 @@ inline void Fatal(const char* what) {  // glog CHECK / LOG(FATAL): abort the pro
 inline void Check(int rc, const char* what) {
   if (rc != NAUTILUS_OK) Fatal(what);
 }
-// The subset of CImg<double> the reference's callers touch on a LookupTable.
-struct Image {
-  uint64_t w = 0, h = 0;
-  std::vector<double> v;
-  Image() {}
-  Image(uint64_t w_, uint64_t h_) : w(w_), h(h_), v(w_ * h_, 0.0) {}
-  double& operator()(uint64_t x, uint64_t y) { return v[x + y * w]; }
-  const double& operator()(uint64_t x, uint64_t y) const { return v[x + y * w]; }
-  double* data() { return v.data(); }
-  const double* data() const { return v.data(); }
-  int width() const { return (int)w; }
-  int height() const { return (int)h; }
-  void clear() { v.assign(v.size(), 0.0); }
-};
+inline int Device() {  // CUDA device of handles and table operations made through this header
+  const char* dev = std::getenv("NAUTILUS_CSM_DEVICE");
+  return dev ? std::atoi(dev) : 0;
+}
 }  // namespace nautilus_b200_detail
 
 // struct LookupTable (h:27-110): a host copy of a table with the reference's
 // world<->cell maps.  Tables used for matching never leave the device; this
-// type only exists for callers that ask for a table.
+// type only exists for callers that ask for a table or make one by hand.
 struct LookupTable {
   uint64_t width;
   uint64_t height;
   double resolution;
-  nautilus_b200_detail::Image values;
+  CImg<double> values;
   LookupTable(const double range, const double resolution)
       : width(floor((range * 2.0) / resolution)),
         height(floor((range * 2.0) / resolution)),
         resolution(resolution) {  // h:32-39
-    values = nautilus_b200_detail::Image(width, height);
+    values = CImg<double>(width, height, 1, 1, 0);
   }
   LookupTable() : width(0), height(0), resolution(1) {}
 
@@ -84,12 +134,50 @@ struct LookupTable {
     if (x >= width || y >= height) return;
     values(x, y) = value;
   }
-  void clear() { values.clear(); }
-  nautilus_b200_detail::Image GetDebugImage() const { return values; }  // h:89
-  uint64_t AbsCoords(double x, double y) const {  // h:104-109
-    uint64_t row = (height / 2 + round(y / resolution)) * width;
-    uint64_t col = (width / 2 + round(x / resolution));
-    if (!(row + col <= width * height)) nautilus_b200_detail::Fatal("CHECK_LE(row + col, size)");
+  // h:79 -> CImg::normalize(0, 1) (CImg.h:39499-39517), on the device
+  void normalize() {
+    if (values.is_empty()) return;
+    nautilus_b200_detail::Check(
+        nautilus_csm_table_normalize(values.data(), (uint64_t)values.width(),
+                                     (uint64_t)values.height(), nautilus_b200_detail::Device()),
+        "LookupTable::normalize");
+  }
+  // h:81-83 -> CImg::blur(sigma, sigma, 0, true, true) (CImg.h:49337-49351), on the device
+  void GaussianBlur(const double sigma) {
+    if (values.is_empty()) return;
+    nautilus_b200_detail::Check(
+        nautilus_csm_table_blur(values.data(), (uint64_t)values.width(),
+                                (uint64_t)values.height(), sigma, nautilus_b200_detail::Device()),
+        "LookupTable::GaussianBlur");
+  }
+  void clear() { values = values.clear(); }                    // h:85
+  void GaussianBlur() { GaussianBlur(DEFAULT_GAUSSIAN_SIGMA); }  // h:87
+  CImg<double> GetDebugImage() const { return values; }        // h:89
+  // h:91-101: get_crop(sx, sy, ex - 1, ey - 1).max() with CImg's crop rules
+  // (CImg.h:45516-45564: int bounds, reversed bounds swapped, zero fill outside)
+  double MaxArea(double start_x, double start_y, double end_x, double end_y) const {
+    uint64_t sx = convertX(start_x);
+    uint64_t sy = convertY(start_y);
+    uint64_t ex = convertX(end_x);
+    uint64_t ey = convertY(end_y);
+    if (values.is_empty()) nautilus_b200_detail::Fatal("MaxArea: crop(): Empty instance");
+    const int x0 = (int)sx, y0 = (int)sy, x1 = (int)(ex - 1), y1 = (int)(ey - 1);
+    const int nx0 = x0 < x1 ? x0 : x1, nx1 = x0 < x1 ? x1 : x0;
+    const int ny0 = y0 < y1 ? y0 : y1, ny1 = y0 < y1 ? y1 : y0;
+    const int w = values.width(), h = values.height();
+    const bool outside = nx0 < 0 || ny0 < 0 || nx1 >= w || ny1 >= h;
+    bool have = outside;
+    double max_val = 0.0;  // the zero fill takes part in the maximum
+    for (int y = ny0 < 0 ? 0 : ny0; y <= (ny1 >= h ? h - 1 : ny1); ++y)
+      for (int x = nx0 < 0 ? 0 : nx0; x <= (nx1 >= w ? w - 1 : nx1); ++x) {
+        const double v = values(x, y);
+        if (!have || v > max_val) { max_val = v; have = true; }
+      }
+    return max_val;
+  }
+  size_t AbsCoords(double x, double y) const {  // h:104-109
+    size_t row = ((height / 2) + round(y / resolution)) * width;
+    size_t col = (width / 2) + round(x / resolution);
     return row + col;
   }
 };
@@ -103,7 +191,7 @@ class CorrelativeScanMatcher {
         high_res_(high_res), handle_(nullptr) {}
   CorrelativeScanMatcher(const CorrelativeScanMatcher& o)  // Solver holds it by value
       : range_(o.range_), trans_range_(o.trans_range_), low_res_(o.low_res_),
-        high_res_(o.high_res_), handle_(nullptr) {}
+        high_res_(o.high_res_), handle_(nullptr) {}  // a copy makes its own handle on first use
   CorrelativeScanMatcher& operator=(const CorrelativeScanMatcher& o) {
     Release();
     range_ = o.range_; trans_range_ = o.trans_range_; low_res_ = o.low_res_; high_res_ = o.high_res_;
@@ -206,15 +294,21 @@ class CorrelativeScanMatcher {
   }
 
   // New, batch-first: what a batched SolveAutoLC / AddLCConstraints calls
-  // (INTEGRATION.md).  The handle is created on first use.
+  // (INTEGRATION.md).  The handle is created on first use, under a lock: the
+  // reference object is shared by OpenMP threads (bag_avg_matcher.cc:104-111,
+  // CorrelativeScanMatcher.cc:381), so two first calls may arrive together.
   NautilusCsm* Handle() {
+    NautilusCsm* h = __atomic_load_n(&handle_, __ATOMIC_ACQUIRE);
+    if (h) return h;
+    std::lock_guard<std::mutex> lock(create_mu_);
     if (!handle_) {
       NautilusCsmParams p = {};
       p.scanner_range = range_; p.trans_range = trans_range_;
       p.low_res = low_res_; p.high_res = high_res_;
-      const char* dev = std::getenv("NAUTILUS_CSM_DEVICE");
-      p.device = dev ? std::atoi(dev) : 0;
-      nautilus_b200_detail::Check(nautilus_csm_create(&p, &handle_), "nautilus_csm_create");
+      p.device = nautilus_b200_detail::Device();
+      NautilusCsm* made = nullptr;
+      nautilus_b200_detail::Check(nautilus_csm_create(&p, &made), "nautilus_csm_create");
+      __atomic_store_n(&handle_, made, __ATOMIC_RELEASE);
     }
     return handle_;
   }
@@ -226,6 +320,7 @@ class CorrelativeScanMatcher {
     return c.empty() ? nullptr : reinterpret_cast<const float*>(c.data());
   }
   void Release() {
+    std::lock_guard<std::mutex> lock(create_mu_);
     if (handle_) nautilus_csm_destroy(handle_);
     handle_ = nullptr;
   }
@@ -234,6 +329,7 @@ class CorrelativeScanMatcher {
   double low_res_;
   double high_res_;
   NautilusCsm* handle_;
+  std::mutex create_mu_;
 };
 
 #endif  // SRC_CORRELATIVESCANMATCHER_H_

@@ -43,31 +43,6 @@ long long host_cell(float v, double res, uint64_t dim) {
   return (long long)c;
 }
 
-// CImg<T>::vanvliet coefficients (CImg.h:49267-49284) + Triggs matrix (49066-49081)
-void vanvliet_coeffs(double sigma, VanVliet* f) {
-  const double nnsigma = sigma < 0.5 ? 0.5 : sigma, m0 = 1.16680, m1 = 1.10783, m2 = 1.40586,
-               m1sq = m1 * m1, m2sq = m2 * m2,
-               q = (nnsigma < 3.556 ? -0.2568 + 0.5784 * nnsigma + 0.0561 * nnsigma * nnsigma
-                                    : 2.5091 + 0.9804 * (nnsigma - 3.556)),
-               qsq = q * q, scale = (m0 + q) * (m1sq + m2sq + 2 * m1 * q + qsq),
-               b1 = -q * (2 * m0 * m1 + m1sq + m2sq + (2 * m0 + 4 * m1) * q + 3 * qsq) / scale,
-               b2 = qsq * (m0 + 2 * m1 + 3 * q) / scale, b3 = -qsq * q / scale,
-               B = (m0 * (m1sq + m2sq)) / scale;
-  f->B = B; f->a1 = -b1; f->a2 = -b2; f->a3 = -b3;
-  const double a1 = f->a1, a2 = f->a2, a3 = f->a3,
-               scaleM = 1. / ((1. + a1 - a2 + a3) * (1. - a1 - a2 - a3) *
-                              (1. + a2 + (a1 - a3) * a3));
-  f->M[0] = scaleM * (-a3 * a1 + 1. - a3 * a3 - a2);
-  f->M[1] = scaleM * (a3 + a1) * (a2 + a3 * a1);
-  f->M[2] = scaleM * a3 * (a1 + a3 * a2);
-  f->M[3] = scaleM * (a1 + a3 * a2);
-  f->M[4] = -scaleM * (a2 - 1.) * (a2 + a3 * a1);
-  f->M[5] = -scaleM * a3 * (a3 * a1 + a3 * a3 + a2 - 1.);
-  f->M[6] = scaleM * (a3 * a1 + a2 + a1 * a1 - a2 * a2);
-  f->M[7] = scaleM * (a1 * a2 + a3 * a2 * a2 - a1 * a3 * a3 - a3 * a3 * a3 - a3 * a2 + a3);
-  f->M[8] = scaleM * a3 * (a1 + a3 * a2);
-}
-
 // Float thresholds of the cell map (see csm::CellMap): entry k is the smallest
 // float v with floor((double)v / res) >= qlo + k, found with the reference's
 // own expression (CorrelativeScanMatcher.h:43-49) by stepping nextafterf.
@@ -601,6 +576,7 @@ int nautilus_internal_match_launch(NautilusCsm* h, ScanSet& ss, const int32_t* a
                                    const double* rot_max, int32_t n_pairs,
                                    size_t result_capacity) {
   if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
+  const HostTimer plan_timer;
   h->timings = NautilusCsmTimings{};
   h->pending = PendingBatch{};
   if (n_pairs == 0) return NAUTILUS_OK;
@@ -734,10 +710,16 @@ int nautilus_internal_match_launch(NautilusCsm* h, ScanSet& ss, const int32_t* a
     max_wave_pairs = std::max(max_wave_pairs, first_pair[t1] - first_pair[t0]);
   }
 
-  // ---- theta chunking: enough blocks to fill the SMs even for a small batch
-  const int target_blocks = h->sm_count * 8;
-  int chunks = std::max(1, std::min(max_rot, (target_blocks + max_wave_pairs - 1) / max_wave_pairs));
-  const int rot_per_chunk = (max_rot + chunks - 1) / chunks;
+  // ---- theta chunking.  A block's warps take rotations round-robin, so a chunk is a
+  // whole number of rounds (low_score_warps() rotations each); a small batch is cut
+  // into more chunks until the grid is ~16 waves of resident blocks, which keeps the
+  // last partial wave short (1250 pairs on one of 8 GPUs: 3 chunks instead of 1).
+  const int ls_warps = low_score_warps();
+  const int rounds = (max_rot + ls_warps - 1) / ls_warps;
+  const long long want_blocks = 16LL * h->sm_count * 2;
+  int chunks = (int)std::max<long long>(1, std::min<long long>(rounds, (want_blocks + max_wave_pairs - 1) / max_wave_pairs));
+  while (chunks > 1 && (size_t)max_wave_pairs * chunks * n_tr * 12 > ((size_t)1 << 30)) --chunks;  // memo buffers
+  const int rot_per_chunk = ((rounds + chunks - 1) / chunks) * ls_warps;
   chunks = (max_rot + rot_per_chunk - 1) / rot_per_chunk;
   SearchBuffers sb;
   sb.chunks_per_pair = chunks;
@@ -803,6 +785,7 @@ int nautilus_internal_match_launch(NautilusCsm* h, ScanSet& ss, const int32_t* a
   h->pending.n_waves = n_waves;
   h->pending.launches = launches;
   h->pending.rf_serial = rf_serial;
+  h->pending.ms_host_plan = plan_timer.ms();
   h->last_n_pairs = n_pairs;
   return NAUTILUS_OK;
 }
@@ -814,6 +797,7 @@ int nautilus_internal_match_timings(NautilusCsm* h, const int* spec_counts) {
   auto evt = [&](int w, int k) { return get_event(h, 1 + 5 * (size_t)w + k); };
   h->timings.launches = h->pending.launches;
   h->timings.waves = n_waves;
+  h->timings.ms_host_plan += h->pending.ms_host_plan;
   for (int w = 0; w < n_waves; ++w) h->timings.spec_windows += spec_counts ? spec_counts[2 * w] : 0;
   for (int w = 0; w < n_waves; ++w) {
     float a = 0, b = 0, c = 0;
@@ -855,7 +839,10 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
   CU_TRY(cudaMemcpyAsync(res, h->results_dev.p, sizeof(PairResult) * n_pairs,
                          cudaMemcpyDeviceToHost, st));
   if ((rc = nautilus_internal_queue_spec_counts(h, &spec_counts))) return rc;
+  const HostTimer wait_timer;
   CU_TRY(cudaStreamSynchronize(st));
+  const float ms_wait = wait_timer.ms();
+  const HostTimer collect_timer;
   nautilus_internal_match_timings(h, spec_counts);
   int bad = 0;
   for (int p = 0; p < n_pairs; ++p) {
@@ -863,6 +850,8 @@ int match_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const in
     if (stats) { stats[p].n_low = res[p].n_low; stats[p].n_high = res[p].n_high; stats[p].n_pops = res[p].n_pops; }
     bad |= res[p].pad;
   }
+  h->timings.ms_host_wait = ms_wait;
+  h->timings.ms_host_collect = collect_timer.ms();
   if (bad) return fail(NAUTILUS_EEMPTY, "a pair had nothing to score");
   return NAUTILUS_OK;
 }

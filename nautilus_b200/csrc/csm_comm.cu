@@ -209,8 +209,9 @@ namespace {
 // h->results_dev, padded to the largest block) and unpacking of every rank's block
 // into caller order.  Synchronises the stream.
 int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, double* score,
-                float* x, float* y, float* theta, NautilusCsmStats* stats) {
+                float* x, float* y, float* theta, NautilusCsmStats* stats, float ms_plan_extra) {
   const int world = h->world_size, rank = h->world_rank;
+  float ms_wait = 0.f;
   const long long n_total = bounds[world];
   long long max_count = 0;
   for (int r = 0; r < world; ++r) {
@@ -248,7 +249,9 @@ int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, dou
                            cudaMemcpyDeviceToHost, st));
     int* spec_counts = nullptr;
     if ((rc = nautilus_internal_queue_spec_counts(h, &spec_counts))) return rc;
+    const HostTimer wait_timer;
     CU_TRY(cudaStreamSynchronize(st));
+    ms_wait = wait_timer.ms();
     nautilus_internal_match_timings(h, spec_counts);
     cudaEventElapsedTime(&h->timings.ms_gather, e0, e1);
   } else {
@@ -257,9 +260,14 @@ int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, dou
                            cudaMemcpyDeviceToHost, st));
     int* spec_counts = nullptr;
     if ((rc = nautilus_internal_queue_spec_counts(h, &spec_counts))) return rc;
+    const HostTimer wait_timer;
     CU_TRY(cudaStreamSynchronize(st));
+    ms_wait = wait_timer.ms();
     nautilus_internal_match_timings(h, spec_counts);
   }
+  const HostTimer collect_timer;
+  h->timings.ms_host_plan += ms_plan_extra;
+  h->timings.ms_host_wait = ms_wait;
   int bad = 0;
   for (int r = 0; r < world; ++r) {
     const PairResult* blk = h->gather_pin.p + (size_t)r * max_count;
@@ -271,6 +279,7 @@ int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, dou
       bad |= v.pad;
     }
   }
+  h->timings.ms_host_collect = collect_timer.ms();
   if (bad) return fail(NAUTILUS_EEMPTY, "a pair had nothing to score");
   return NAUTILUS_OK;
 }
@@ -283,7 +292,7 @@ int nautilus_csm_gather(NautilusCsm* h, const int32_t* order, const int64_t* bou
                         float* x, float* y, float* theta, NautilusCsmStats* stats) {
   if (!h || !bounds || !score || !x || !y || !theta) return fail(NAUTILUS_EINVAL, "null argument");
   NAUTILUS_GUARD(h);
-  return gather_impl(h, order, bounds, score, x, y, theta, stats);
+  return gather_impl(h, order, bounds, score, x, y, theta, stats, 0.f);
 }
 
 int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
@@ -292,6 +301,7 @@ int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const
                                      NautilusCsmStats* stats) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
   NAUTILUS_GUARD(h);
+  const HostTimer shard_timer;
   if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
   if (n_pairs == 0) { h->timings = NautilusCsmTimings{}; return NAUTILUS_OK; }
   if (!a_ids || !b_ids || !rot_min || !rot_max || !score || !x || !y || !theta)
@@ -326,6 +336,7 @@ int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const
   long long max_count = 0;
   for (int r = 0; r < world; ++r)
     max_count = std::max<long long>(max_count, h->shard_bounds[r + 1] - h->shard_bounds[r]);
+  const float ms_shard_plan = shard_timer.ms();
   rc = nautilus_internal_match_launch(h, ss, h->shard_a.data(), h->shard_b.data(),
                                       h->shard_rmin.data(), h->shard_rmax.data(), n_local,
                                       (size_t)max_count);
@@ -335,7 +346,7 @@ int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const
   if (rc && h->results_dev.reserve((size_t)std::max<long long>(max_count, 1))) return rc;
   const int grc = gather_impl(h, h->shard_order.data(),
                               reinterpret_cast<const int64_t*>(h->shard_bounds.data()), score, x, y,
-                              theta, stats);
+                              theta, stats, ms_shard_plan);
   if (rc) return fail(rc, launch_error);
   return grc;
 }

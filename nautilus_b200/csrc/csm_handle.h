@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -32,7 +33,31 @@ inline int fail(int code, const std::string& msg) {
     }                                                                             \
   } while (0)
 
-// Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
+// CImg<T>::vanvliet coefficients (CImg.h:49267-49284) + Triggs matrix (49066-49081)
+inline void vanvliet_coeffs(double sigma, VanVliet* f) {
+  const double nnsigma = sigma < 0.5 ? 0.5 : sigma, m0 = 1.16680, m1 = 1.10783, m2 = 1.40586,
+               m1sq = m1 * m1, m2sq = m2 * m2,
+               q = (nnsigma < 3.556 ? -0.2568 + 0.5784 * nnsigma + 0.0561 * nnsigma * nnsigma
+                                    : 2.5091 + 0.9804 * (nnsigma - 3.556)),
+               qsq = q * q, scale = (m0 + q) * (m1sq + m2sq + 2 * m1 * q + qsq),
+               b1 = -q * (2 * m0 * m1 + m1sq + m2sq + (2 * m0 + 4 * m1) * q + 3 * qsq) / scale,
+               b2 = qsq * (m0 + 2 * m1 + 3 * q) / scale, b3 = -qsq * q / scale,
+               B = (m0 * (m1sq + m2sq)) / scale;
+  f->B = B; f->a1 = -b1; f->a2 = -b2; f->a3 = -b3;
+  const double a1 = f->a1, a2 = f->a2, a3 = f->a3,
+               scaleM = 1. / ((1. + a1 - a2 + a3) * (1. - a1 - a2 - a3) *
+                              (1. + a2 + (a1 - a3) * a3));
+  f->M[0] = scaleM * (-a3 * a1 + 1. - a3 * a3 - a2);
+  f->M[1] = scaleM * (a3 + a1) * (a2 + a3 * a1);
+  f->M[2] = scaleM * a3 * (a1 + a3 * a2);
+  f->M[3] = scaleM * (a1 + a3 * a2);
+  f->M[4] = -scaleM * (a2 - 1.) * (a2 + a3 * a1);
+  f->M[5] = -scaleM * a3 * (a3 * a1 + a3 * a3 + a2 - 1.);
+  f->M[6] = scaleM * (a3 * a1 + a2 + a1 * a1 - a2 * a2);
+  f->M[7] = scaleM * (a1 * a2 + a3 * a2 * a2 - a1 * a3 * a3 - a3 * a3 * a3 - a3 * a2 + a3);
+  f->M[8] = scaleM * a3 * (a1 + a3 * a2);
+}
+
 // Pooling windows of one axis (CorrelativeScanMatcher.cc:37-45 + MaxArea h:91-101).
 struct PoolListHost {
   std::vector<int> s, e, dst;
@@ -144,6 +169,14 @@ using namespace csmh;
 struct PendingBatch {
   int n_pairs = 0, n_waves = 0, launches = 0;
   bool rf_serial = false;
+  float ms_host_plan = 0.f;
+};
+
+struct HostTimer {
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  float ms() const {
+    return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
 };
 
 struct NautilusCsm {

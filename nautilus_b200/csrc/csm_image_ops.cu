@@ -1,0 +1,141 @@
+// LookupTable::GaussianBlur and LookupTable::normalize on a CALLER-MADE table
+// (CorrelativeScanMatcher.h:79-87), for the drop-in C++ header: a table a caller
+// filled by hand with SetPointValue has arbitrary fp64 content, so the batch
+// kernels of csm_tables.cu (bitmap input, cropped rectangle) do not apply.  These
+// run the same arithmetic on a dense image, one thread per line:
+//   CImg::blur(sigma, sigma, 0, true, true)  -> vanvliet 'x' then 'y'
+//                                               (CImg.h:49337-49351, 49248-49314,
+//                                                _cimg_recursive_apply 49062-49115)
+//   CImg::normalize(0, 1)                       (CImg.h:39499-39517)
+// Same operations in the same order as the reference => bit-identical results
+// (tests/test_gpu_shim.py against oracle/_ref).  Not a hot path: the reference only
+// calls these from GetLookupTable, which the batch kernels replace.
+#include <math.h>
+
+#include "csm_handle.h"
+
+namespace {
+
+// One line of _cimg_recursive_apply, order 0, Neumann boundary, in place.
+__global__ void __launch_bounds__(128) blur_lines_kernel(double* __restrict__ data, int n_lines,
+                                                         int n, size_t line_stride, size_t off,
+                                                         VanVliet f) {
+  const int line = blockIdx.x * blockDim.x + threadIdx.x;
+  if (line >= n_lines) return;
+  double* p = data + (size_t)line * line_stride;
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3, sum = __dmul_rn(f.B, f.B);
+  const double iplus = p[(size_t)(n - 1) * off];             // read before the causal pass
+  double v1 = __ddiv_rn(p[0], f.B), v2 = v1, v3 = v1;        // val[1..3] = *data / sumsq
+  for (int k = 0; k < n; ++k) {
+    const double v0 = vv_step(p[(size_t)k * off], v1, v2, v3, a1, a2, a3);
+    p[(size_t)k * off] = v0;
+    v3 = v2; v2 = v1; v1 = v0;
+  }
+  double w0, w1, w2;
+  vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+  p[(size_t)(n - 1) * off] = w0;
+  v1 = w0; v2 = w1; v3 = w2;                                 // after the shift of CImg.h:49100
+  for (int k = n - 2; k >= 0; --k) {
+    const double v0 = vv_step(__dmul_rn(p[(size_t)k * off], sum), v1, v2, v3, a1, a2, a3);
+    p[(size_t)k * off] = v0;
+    v3 = v2; v2 = v1; v1 = v0;
+  }
+}
+
+__global__ void __launch_bounds__(256) minmax_kernel(const double* __restrict__ v, size_t n,
+                                                     unsigned long long* __restrict__ keys) {
+  double mx = -INFINITY, mn = INFINITY;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double x = v[i];
+    mx = x > mx ? x : mx;
+    mn = x < mn ? x : mn;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0 && mx >= mn) {
+    atomicMax(&keys[0], order_key(mx));
+    atomicMin(&keys[1], order_key(mn));
+  }
+}
+
+// (v - m) / (M - m) * (b - a) + a with a = 0, b = 1; fill with a when m == M; untouched
+// when the range already is [0, 1] (CImg.h:39505-39516)
+__global__ void __launch_bounds__(256) rescale_kernel(double* __restrict__ v, size_t n,
+                                                      const unsigned long long* __restrict__ keys) {
+  const double M = key_to_double(keys[0]), m = key_to_double(keys[1]);
+  if (m == 0.0 && M == 1.0) return;
+  const double range = __dsub_rn(M, m);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    v[i] = (m == M) ? 0.0 : __dadd_rn(__dmul_rn(__ddiv_rn(__dsub_rn(v[i], m), range), 1.0), 0.0);
+}
+
+struct DeviceImage {
+  double* p = nullptr;
+  unsigned long long* keys = nullptr;
+  cudaStream_t st = nullptr;
+  ~DeviceImage() {
+    cudaFree(p); cudaFree(keys);
+    if (st) cudaStreamDestroy(st);
+  }
+};
+
+int open_image(DeviceImage& d, const double* values, uint64_t w, uint64_t h, int32_t device) {
+  if (!values || w == 0 || h == 0 || w > 30000 || h > 30000) return fail(NAUTILUS_EINVAL, "bad table");
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+    return fail(NAUTILUS_ECUDA, "no CUDA device (there is no CPU fallback)");
+  if (device < 0 || device >= n_dev) return fail(NAUTILUS_EINVAL, "bad device ordinal");
+  CU_TRY(cudaSetDevice(device));
+  CU_TRY(cudaStreamCreateWithFlags(&d.st, cudaStreamNonBlocking));
+  CU_TRY(cudaMalloc(&d.p, sizeof(double) * w * h));
+  CU_TRY(cudaMalloc(&d.keys, 2 * sizeof(unsigned long long)));
+  CU_TRY(cudaMemcpyAsync(d.p, values, sizeof(double) * w * h, cudaMemcpyHostToDevice, d.st));
+  return NAUTILUS_OK;
+}
+
+int close_image(DeviceImage& d, double* values, uint64_t w, uint64_t h) {
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(values, d.p, sizeof(double) * w * h, cudaMemcpyDeviceToHost, d.st));
+  CU_TRY(cudaStreamSynchronize(d.st));
+  return NAUTILUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nautilus_csm_table_blur(double* values, uint64_t width, uint64_t height, double sigma,
+                            int32_t device) {
+  // blur() takes float sigmas; vanvliet() returns the image untouched for sigma < 0.5
+  const float fs = (float)sigma;
+  if (!(fs >= 0.5f)) {
+    if (fs < 0.f) return fail(NAUTILUS_EINVAL, "negative sigma (CImg: percentage of the size) is not supported");
+    return values ? NAUTILUS_OK : fail(NAUTILUS_EINVAL, "null table");
+  }
+  DeviceImage d;
+  int rc = open_image(d, values, width, height, device);
+  if (rc) return rc;
+  VanVliet f;
+  vanvliet_coeffs((double)fs, &f);
+  const int w = (int)width, h = (int)height;
+  if (w > 1) blur_lines_kernel<<<(h + 127) / 128, 128, 0, d.st>>>(d.p, h, w, (size_t)w, 1, f);
+  if (h > 1) blur_lines_kernel<<<(w + 127) / 128, 128, 0, d.st>>>(d.p, w, h, 1, (size_t)w, f);
+  return close_image(d, values, width, height);
+}
+
+int nautilus_csm_table_normalize(double* values, uint64_t width, uint64_t height, int32_t device) {
+  DeviceImage d;
+  int rc = open_image(d, values, width, height, device);
+  if (rc) return rc;
+  const unsigned long long init[2] = {0ULL, ~0ULL};
+  CU_TRY(cudaMemcpyAsync(d.keys, init, sizeof(init), cudaMemcpyHostToDevice, d.st));
+  const size_t n = (size_t)width * height;
+  const int blocks = (int)std::min<size_t>(1184, (n + 255) / 256);
+  minmax_kernel<<<blocks, 256, 0, d.st>>>(d.p, n, d.keys);
+  rescale_kernel<<<blocks, 256, 0, d.st>>>(d.p, n, d.keys);
+  return close_image(d, values, width, height);
+}
+
+}  // extern "C"

@@ -125,6 +125,7 @@ int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hig
                   int n_pairs, const SearchBuffers& sb, PairResult* results, bool serial,
                   int sm_count, cudaStream_t stream);
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells);
+int low_score_warps();  // warps of a low_score_kernel block = rotations it scores per round
 // GetUncertaintyMatrix (cc:267-373) after launch_low_score filled sb for the pair:
 // costs[n_rot][n_t*n_t] scratch, out = dims x dims floats (row-major).
 void launch_uncertainty(const SearchGrid& sg, const CellMap& cm_high, const float2* points,

@@ -99,6 +99,8 @@ constexpr unsigned LS_FLOOR = 1u << 30; // the patch lies outside the box: every
 constexpr unsigned LS_EDGE = 2u << 30;  // rows / columns clamped onto the floor padding (the patch word)
 constexpr unsigned LS_SLOW = 3u << 30;  // LS_ODD
 
+int low_score_warps() { return LS_WARPS; }
+
 size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   size_t b = sizeof(double) * (size_t)table_cells;                   // staged table
   b += sizeof(double) * (((size_t)n_t * n_t + 1) & ~(size_t)1);      // best score

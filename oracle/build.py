@@ -81,9 +81,50 @@ def build_ref(force: bool = False) -> str | None:
     return REF_LIB
 
 
+REF_GTESTS = os.path.join(REF_DIR, "ref_csm_gtests")
+
+
+def build_ref_gtests(force: bool = False) -> str | None:
+    """The reference's own unit-test file, third_party/csm/test/
+    correlative_scan_matcher_tests.cc, compiled UNCHANGED where it lies against the
+    product's drop-in header (nautilus_b200/cpp/CorrelativeScanMatcher.h) and linked with
+    libnautilus_csm_b200.so.  The file is fed to g++ on stdin from tests/cpp/dropin/test/
+    so that its `#include "../src/CorrelativeScanMatcher.h"` resolves to the drop-in
+    instead of the reference header beside it.  Returns the binary's path, or None when
+    the reference tree is absent and nothing is prebuilt."""
+    repo = os.path.dirname(HERE)
+    src = os.path.join(REF_ROOT, "third_party/csm/test/correlative_scan_matcher_tests.cc")
+    lib_dir = os.path.join(repo, "nautilus_b200", "lib")
+    if not os.path.exists(src):
+        return REF_GTESTS if os.path.exists(REF_GTESTS) else None
+    deps = [os.path.join(repo, "nautilus_b200", "cpp", "CorrelativeScanMatcher.h"),
+            os.path.join(repo, "include", "nautilus_csm.h"),
+            os.path.join(repo, "tests", "cpp", "gtest_shim", "gtest", "gtest.h")]
+    if not force and _newer(REF_GTESTS, deps):
+        return REF_GTESTS
+    os.makedirs(REF_DIR, exist_ok=True)
+    shim = os.path.join(repo, "tests", "cpp", "gtest_shim")
+    obj = os.path.join(REF_DIR, "ref_csm_gtests.o")
+    cmd = ["g++", "-std=c++17", "-O1", "-DNAUTILUS_CSM_NO_CIMG", "-x", "c++", "-c", "-", "-o", obj,
+           "-I" + shim, "-I" + os.path.join(HERE, "shim"), "-I" + os.path.join(repo, "include")]
+    with open(src, "rb") as f:
+        r = subprocess.run(cmd, stdin=f, capture_output=True, text=False,
+                           cwd=os.path.join(repo, "tests", "cpp", "dropin", "test"))
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stderr.decode())
+        raise RuntimeError("reference gtest build failed")
+    _run(["g++", "-std=c++17", "-O1", obj, os.path.join(shim, "gtest_main.cc"), "-I" + shim,
+          "-L" + lib_dir, "-lnautilus_csm_b200", "-Wl,-rpath," + lib_dir, "-o", REF_GTESTS])
+    os.remove(obj)
+    return REF_GTESTS
+
+
 def build_all(force: bool = False) -> None:
     build_port(force)
     build_ref(force)
+    if os.path.exists(os.path.join(os.path.dirname(HERE), "nautilus_b200", "lib",
+                                   "libnautilus_csm_b200.so")):
+        build_ref_gtests(force)
 
 
 if __name__ == "__main__":
