@@ -228,10 +228,19 @@ int nautilus_csm_match_batch_sharded(NautilusCsm* h, const int32_t* a_ids, const
                                      int32_t n_pairs, double* score, float* x, float* y,
                                      float* theta, NautilusCsmStats* stats);
 
-/* Single pair from host clouds = batch of one (upload + tables + search). */
+/* Single pair from host clouds (upload + tables + search).  Thread-safe and
+ * COMBINING: the reference object is called from OpenMP threads
+ * (bag_avg_matcher.cc:104-141, cc:381-386) and one pair cannot fill a B200, so calls
+ * that arrive while a batch is in flight are queued and matched together as the next
+ * batch by whichever caller is leading; every caller gets exactly the result a lone
+ * call returns.  Clouds passed by the same pointer and size by several queued calls
+ * are uploaded (and their tables built) once. */
 int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b,
                        int64_t nb, double rot_min, double rot_max, double* score,
                        float* x, float* y, float* theta, NautilusCsmStats* stats);
+
+/* How many nautilus_csm_match calls the handle has served and in how many batches. */
+int nautilus_csm_single_queue_stats(const NautilusCsm* h, int64_t* n_requests, int64_t* n_batches);
 
 /* GetUncertaintyMatrix: dims == 3 -> the 3x3 form over all rotations
  * (cc:267-319, `rotation` ignored); dims == 2 -> the 2x2 form at `rotation`

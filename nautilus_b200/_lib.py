@@ -66,7 +66,7 @@ EXPORTS = [
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_host_alloc", "nautilus_host_free",
     "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
-    "nautilus_csm_table_blur", "nautilus_csm_table_normalize",
+    "nautilus_csm_single_queue_stats", "nautilus_csm_table_blur", "nautilus_csm_table_normalize",
     "nautilus_csm_partition", "nautilus_csm_pair_weights", "nautilus_csm_comm_unique_id",
     "nautilus_csm_comm_init", "nautilus_csm_comm_attach", "nautilus_csm_gather",
     "nautilus_csm_match_batch_sharded",
@@ -156,6 +156,7 @@ def lib():
     L.nautilus_csm_build_tables.argtypes = [vp, vp, i32, C.POINTER(d)]
     L.nautilus_csm_match_batch.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp]
     L.nautilus_csm_copy_results_dev.argtypes = [vp, vp, i32]
+    L.nautilus_csm_single_queue_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64)]
     L.nautilus_csm_table_blur.argtypes = [vp, u64, u64, d, i32]
     L.nautilus_csm_table_normalize.argtypes = [vp, u64, u64, i32]
     L.nautilus_csm_partition.argtypes = [vp, vp, i32, i32, vp, vp]

@@ -268,8 +268,11 @@ int build_search_grid(NautilusCsm* h) {
   return NAUTILUS_OK;
 }
 
+// `pinned_source`: xy lives in the handle's own page-locked staging, so the copy is a
+// true asynchronous DMA and the stream need not be drained before returning (the
+// staging is not rewritten before the batch that uses it has been collected).
 int upload_scan_set(NautilusCsm* h, ScanSet& ss, const float* xy, const int64_t* offsets,
-                    int32_t n_scans) {
+                    int32_t n_scans, bool pinned_source = false) {
   if (n_scans < 0 || (n_scans > 0 && (!offsets))) return fail(NAUTILUS_EINVAL, "bad scan set");
   const long long total = n_scans > 0 ? offsets[n_scans] : 0;
   if (n_scans > 0 && offsets[0] != 0) return fail(NAUTILUS_EINVAL, "offsets[0] must be 0");
@@ -290,9 +293,17 @@ int upload_scan_set(NautilusCsm* h, ScanSet& ss, const float* xy, const int64_t*
   for (int i = 0; i <= n_scans && n_scans > 0; ++i) ss.host_offsets[i] = offsets[i];
   if (total > 0)
     CU_TRY(cudaMemcpyAsync(ss.points, xy, sizeof(float2) * total, cudaMemcpyHostToDevice, h->stream));
-  CU_TRY(cudaMemcpyAsync(ss.offsets, ss.host_offsets.data(), sizeof(long long) * (n_scans + 1),
-                         cudaMemcpyHostToDevice, h->stream));
-  CU_TRY(cudaStreamSynchronize(h->stream));
+  if (pinned_source) {
+    int rc = ss.offsets_pin.reserve((size_t)n_scans + 1);
+    if (rc) return rc;
+    for (int i = 0; i <= n_scans; ++i) ss.offsets_pin.p[i] = ss.host_offsets[i];
+    CU_TRY(cudaMemcpyAsync(ss.offsets, ss.offsets_pin.p, sizeof(long long) * (n_scans + 1),
+                           cudaMemcpyHostToDevice, h->stream));
+  } else {
+    CU_TRY(cudaMemcpyAsync(ss.offsets, ss.host_offsets.data(), sizeof(long long) * (n_scans + 1),
+                           cudaMemcpyHostToDevice, h->stream));
+    CU_TRY(cudaStreamSynchronize(h->stream));
+  }
   ss.n = n_scans;
   return NAUTILUS_OK;
 }
@@ -496,6 +507,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->results_dev.release(); h->chunk_best_dev.release(); h->chunk_rot_dev.release();
   h->residual_arena.release();
   h->spec_pairs_dev.release(); h->spec_items_dev.release(); h->spec_out_dev.release(); h->spec_counters_dev.release();
+  h->single_pin.release(); h->user_scans.offsets_pin.release(); h->tmp_scans.offsets_pin.release();
   h->targets_pin.release(); h->sorted_pin.release(); h->results_pin.release(); h->spec_counts_pin.release();
   for (cudaEvent_t ev : h->events) cudaEventDestroy(ev);
   if (h->table_stream) cudaStreamDestroy(h->table_stream);
@@ -882,23 +894,126 @@ int nautilus_csm_copy_results_dev(NautilusCsm* h, void* dst_dev, int32_t n_pairs
   return NAUTILUS_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+// Matches every queued single-pair request as ONE batch (the caller holds h->mu).
+// Clouds that several requests pass by the same pointer and size (one target against
+// many queries, GetLocalUncertaintyStats' pattern, cc:381-386) are uploaded once, so
+// their lookup tables are built once.
+void run_single_batch(NautilusCsm* h, std::vector<SingleRequest*>& reqs) {
+  const int n = (int)reqs.size();
+  std::vector<int32_t> a_ids, b_ids;
+  std::vector<double> rmin, rmax;
+  std::vector<int> live;
+  std::vector<int64_t> offs(1, 0);
+  std::vector<std::pair<const float*, int64_t>> clouds;  // distinct (pointer, size)
+  auto scan_of = [&](const float* p, int64_t cnt) {
+    for (size_t k = 0; k < clouds.size(); ++k)
+      if (clouds[k].first == p && clouds[k].second == cnt) return (int32_t)k;
+    clouds.emplace_back(p, cnt);
+    offs.push_back(offs.back() + cnt);
+    return (int32_t)(clouds.size() - 1);
+  };
+  for (int k = 0; k < n; ++k) {
+    SingleRequest& r = *reqs[k];
+    r.rc = NAUTILUS_OK;
+    if (r.na < 0 || r.nb < 0 || (r.na > 0 && !r.a) || (r.nb > 0 && !r.b)) {
+      r.rc = NAUTILUS_EINVAL; r.error = "bad cloud";
+    } else if (r.na == 0) {
+      r.rc = NAUTILUS_EEMPTY; r.error = "empty query cloud: the reference does not terminate on it";
+    } else if (!(r.rot_min < r.rot_max)) {
+      r.rc = NAUTILUS_EEMPTY; r.error = "empty rotation window: the reference does not terminate on it";
+    }
+    if (r.rc) continue;
+    live.push_back(k);
+    a_ids.push_back(scan_of(r.a, r.na));
+    b_ids.push_back(scan_of(r.b, r.nb));
+    rmin.push_back(r.rot_min);
+    rmax.push_back(r.rot_max);
+  }
+  if (live.empty()) return;
+  const int m = (int)live.size();
+  int rc = cudaSetDevice(h->device) == cudaSuccess ? NAUTILUS_OK : fail(NAUTILUS_ECUDA, "cudaSetDevice");
+  // clouds -> page-locked staging -> one H2D
+  if (!rc) rc = h->single_pin.reserve((size_t)2 * std::max<int64_t>(offs.back(), 1));
+  if (!rc) {
+    for (size_t k = 0; k < clouds.size(); ++k)
+      if (clouds[k].second)
+        memcpy(h->single_pin.p + 2 * offs[k], clouds[k].first, sizeof(float) * 2 * clouds[k].second);
+    rc = upload_scan_set(h, h->tmp_scans, h->single_pin.p, offs.data(), (int32_t)clouds.size(), true);
+  }
+  std::vector<double> score(m);
+  std::vector<float> x(m), y(m), th(m);
+  std::vector<NautilusCsmStats> st(m);
+  if (!rc)
+    rc = match_batch_impl(h, h->tmp_scans, a_ids.data(), b_ids.data(), rmin.data(), rmax.data(), m,
+                          score.data(), x.data(), y.data(), th.data(), st.data());
+  const std::string err = rc ? error_text() : std::string();
+  for (int j = 0; j < m; ++j) {
+    SingleRequest& r = *reqs[live[j]];
+    r.rc = rc;
+    r.error = err;
+    if (rc) continue;
+    if (r.score) *r.score = score[j];
+    if (r.x) *r.x = x[j];
+    if (r.y) *r.y = y[j];
+    if (r.theta) *r.theta = th[j];
+    if (r.stats) *r.stats = st[j];
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// GetTransformation for one pair of host clouds.  The reference object is shared by
+// OpenMP threads (bag_avg_matcher.cc:104-141, CorrelativeScanMatcher.cc:381-386) and a
+// single pair cannot fill a B200, so concurrent callers are COMBINED: a caller queues
+// its request; whoever finds no batch in flight becomes the leader, takes everything
+// queued so far and matches it as one batch, then hands the results back and repeats
+// while requests keep arriving.  A lone caller is a batch of one.
 int nautilus_csm_match(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,
                        double rot_min, double rot_max, double* score, float* x, float* y,
                        float* theta, NautilusCsmStats* stats) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
-  NAUTILUS_GUARD(h);
-  if (na < 0 || nb < 0) return fail(NAUTILUS_EINVAL, "negative point count");
-  if (na == 0) return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
-  CU_TRY(cudaSetDevice(h->device));
-  std::vector<float> xy((size_t)2 * (na + nb));
-  memcpy(xy.data(), a, sizeof(float) * 2 * na);
-  if (nb) memcpy(xy.data() + 2 * na, b, sizeof(float) * 2 * nb);
-  const int64_t offs[3] = {0, na, na + nb};
-  int rc = upload_scan_set(h, h->tmp_scans, xy.data(), offs, 2);
-  if (rc) return rc;
-  const int32_t ia = 0, ib = 1;
-  return match_batch_impl(h, h->tmp_scans, &ia, &ib, &rot_min, &rot_max, 1, score, x, y, theta,
-                          stats);
+  SingleRequest req;
+  req.a = a; req.na = na; req.b = b; req.nb = nb; req.rot_min = rot_min; req.rot_max = rot_max;
+  req.score = score; req.x = x; req.y = y; req.theta = theta; req.stats = stats;
+  std::unique_lock<std::mutex> q(h->single_mu);
+  h->single_queue.push_back(&req);
+  if (h->single_leader) {
+    h->single_cv.wait(q, [&] { return req.done; });
+  } else {
+    h->single_leader = true;
+    while (!h->single_queue.empty()) {
+      std::vector<SingleRequest*> batch;
+      batch.swap(h->single_queue);
+      q.unlock();
+      {
+        NAUTILUS_GUARD(h);
+        run_single_batch(h, batch);
+        h->single_batches += 1;
+        h->single_requests += (long long)batch.size();
+      }
+      q.lock();
+      for (SingleRequest* r : batch) r->done = true;
+      h->single_cv.notify_all();
+    }
+    h->single_leader = false;
+  }
+  q.unlock();
+  if (req.rc) return fail(req.rc, req.error);
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_single_queue_stats(const NautilusCsm* h, int64_t* n_requests, int64_t* n_batches) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  std::lock_guard<std::mutex> q(h->single_mu);
+  if (n_requests) *n_requests = h->single_requests;
+  if (n_batches) *n_batches = h->single_batches;
+  return NAUTILUS_OK;
 }
 
 int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const float* b, int64_t nb,

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -88,20 +89,6 @@ struct DevPool {
   }
 };
 
-// A set of clouds resident on the device.
-struct ScanSet {
-  float2* points = nullptr;
-  long long* offsets = nullptr;
-  std::vector<long long> host_offsets;
-  std::vector<float> host_xy;  // host copy of the clouds (KD-tree build of the NN path)
-  size_t cap_points = 0, cap_offsets = 0;
-  int n = 0;
-  void release() {
-    cudaFree(points); cudaFree(offsets);
-    points = nullptr; offsets = nullptr; cap_points = cap_offsets = 0; n = 0;
-  }
-};
-
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
@@ -135,6 +122,33 @@ struct PinBuf {
     return NAUTILUS_OK;
   }
   void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// A set of clouds resident on the device.
+struct ScanSet {
+  float2* points = nullptr;
+  long long* offsets = nullptr;
+  std::vector<long long> host_offsets;
+  std::vector<float> host_xy;  // host copy of the clouds (KD-tree build of the NN path)
+  PinBuf<long long> offsets_pin;  // staging of the offsets for uploads from pinned clouds
+  size_t cap_points = 0, cap_offsets = 0;
+  int n = 0;
+  void release() {
+    cudaFree(points); cudaFree(offsets);
+    points = nullptr; offsets = nullptr; cap_points = cap_offsets = 0; n = 0;
+  }
+};
+
+// One queued single-pair call (nautilus_csm_match): see the combining queue there.
+struct SingleRequest {
+  const float* a = nullptr; int64_t na = 0;
+  const float* b = nullptr; int64_t nb = 0;
+  double rot_min = 0, rot_max = 0;
+  double* score = nullptr; float* x = nullptr; float* y = nullptr; float* theta = nullptr;
+  NautilusCsmStats* stats = nullptr;
+  int rc = 0;
+  std::string error;
+  bool done = false;
 };
 
 }  // namespace csmh
@@ -251,6 +265,14 @@ struct NautilusCsm {
   std::vector<int> shard_order, shard_a, shard_b;
   std::vector<long long> shard_bounds;
   std::vector<double> shard_w, shard_rmin, shard_rmax;
+
+  // combining queue of concurrent single-pair callers (nautilus_csm_match)
+  mutable std::mutex single_mu;
+  std::condition_variable single_cv;
+  std::vector<SingleRequest*> single_queue;
+  bool single_leader = false;
+  long long single_requests = 0, single_batches = 0;
+  PinBuf<float> single_pin;
 
   // residual evaluation (residuals.cu)
   DevBuf<unsigned char> residual_arena;

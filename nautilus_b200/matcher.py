@@ -381,6 +381,12 @@ class CorrelativeScanMatcher:
         check(self._L.nautilus_nn_last_stats(self._h, C.byref(ms), C.byref(walked)))
         return {"ms_kernel": ms.value, "n_walked": int(walked.value)}
 
+    def single_queue_stats(self) -> tuple[int, int]:
+        """(single-pair calls served, batches they were combined into)."""
+        n, b = C.c_int64(), C.c_int64()
+        check(self._L.nautilus_csm_single_queue_stats(self._h, C.byref(n), C.byref(b)))
+        return n.value, b.value
+
     def last_timings(self) -> dict:
         t = Timings()
         check(self._L.nautilus_csm_last_timings(self._h, C.byref(t)))

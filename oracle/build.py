@@ -59,7 +59,8 @@ def build_ref(force: bool = False) -> str | None:
     """Returns the path, or None when /root/reference is absent and nothing is prebuilt."""
     csm_src = os.path.join(REF_ROOT, "third_party/csm/src/CorrelativeScanMatcher.cc")
     kd_src = os.path.join(REF_ROOT, "src/util/kdtree.cc")
-    wrap = [os.path.join(HERE, f) for f in ("ref_wrap.cc", "ref_nn_wrap.cc", "ref_frontend_wrap.cc")]
+    wrap = [os.path.join(HERE, f) for f in ("ref_wrap.cc", "ref_nn_wrap.cc", "ref_frontend_wrap.cc",
+                                            "ref_nautilus_wrap.cc", "ref_residual_wrap.cc")]
     wrap = [s for s in wrap if os.path.exists(s)]
     if not os.path.exists(csm_src):
         return REF_LIB if os.path.exists(REF_LIB) else None
@@ -72,6 +73,9 @@ def build_ref(force: bool = False) -> str | None:
         srcs.append(kd_src)
     if os.path.exists(os.path.join(HERE, "ref_frontend_wrap.cc")):
         srcs.append(os.path.join(REF_ROOT, "third_party/csm/src/pointcloud_helpers.cc"))
+    if os.path.exists(os.path.join(HERE, "ref_nautilus_wrap.cc")):
+        srcs.append(os.path.join(REF_ROOT, "src/input/pointcloud_helpers.cc"))
+        srcs.append(os.path.join(REF_ROOT, "src/loop_closure/lc_candidate_filter.cc"))
     _run(["g++", "-std=c++17", "-O3", "-DNDEBUG", "-fopenmp", "-Dcimg_display=0",
           "-fPIC", "-shared",
           "-I" + os.path.join(HERE, "shim"),

@@ -59,6 +59,17 @@ def lib():
     if hasattr(L, "ref_csm_laser_to_points"):  # front end (ref_frontend_wrap.cc)
         L.ref_csm_laser_to_points.restype = i64
         L.ref_csm_laser_to_points.argtypes = [_f32p, i64, f, f, f, f, d, C.c_int, _f32p]
+    if hasattr(L, "ref_nautilus_laser_to_points"):  # nautilus front end (ref_nautilus_wrap.cc)
+        L.ref_nautilus_laser_to_points.restype = i64
+        L.ref_nautilus_laser_to_points.argtypes = [_f32p, i64, f, f, f, f, d, _f32p]
+        L.ref_scatter_score.restype = d
+        L.ref_scatter_score.argtypes = [_f32p, i64]
+        L.ref_lc_candidates.restype = i64
+        L.ref_lc_candidates.argtypes = [_f32p, _i64p, C.c_int32, _f64p, _i64p]
+    if hasattr(L, "ref_residuals_eval"):  # residual functors (ref_residual_wrap.cc)
+        L.ref_residuals_eval.restype = C.c_int
+        L.ref_residuals_eval.argtypes = [C.c_int, _f64p, _f64p, _i64p, C.c_int32, _f32p, _f32p,
+                                         _f32p, _f32p, _f64p, vp, vp]
     if hasattr(L, "ref_kd_new"):  # KD-tree part (ref_nn_wrap.cc)
         L.ref_kd_new.restype = vp
         L.ref_kd_new.argtypes = [_f32p, i64]
@@ -262,3 +273,57 @@ def csm_laser_to_points(ranges, angle_min, angle_max, angle_increment, range_min
     n = lib().ref_csm_laser_to_points(r, len(r), angle_min, angle_max, angle_increment, range_min,
                                       max_range, int(bool(truncate_ends)), out.reshape(-1))
     return out[:n].copy()
+
+
+def nautilus_laser_to_points(ranges, angle_min, angle_max, angle_increment, range_min, max_range):
+    """The reference's nautilus::LaserScanToPointCloud (src/input/pointcloud_helpers.cc:28-48,
+    the variant the Nautilus node calls), compiled unchanged."""
+    r = np.ascontiguousarray(ranges, np.float32)
+    out = np.zeros((len(r), 2), np.float32)
+    n = lib().ref_nautilus_laser_to_points(r, len(r), angle_min, angle_max, angle_increment,
+                                           range_min, max_range, out.reshape(-1))
+    return out[:n].copy()
+
+
+def scatter_score(cloud) -> float:
+    """ComputeScatterMatrixScore (src/loop_closure/lc_candidate_filter.cc:34-52), compiled
+    unchanged; the 2x2 eigenvalues come from oracle/shim's closed form (Eigen absent)."""
+    c = np.ascontiguousarray(cloud, np.float32).reshape(-1, 2)
+    return float(lib().ref_scatter_score(c.reshape(-1), len(c)))
+
+
+def lc_candidates(xy, offsets, poses):
+    """LCCandidateFilter::GetLCCandidates (lc_candidate_filter.cc:66-81), compiled unchanged,
+    over a SLAMState2D made of the given clouds and (x, y, theta) poses."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+    out = np.zeros(len(offsets) - 1, np.int64)
+    n = lib().ref_lc_candidates(xy.reshape(-1), offsets, len(offsets) - 1, poses.reshape(-1), out)
+    return out[:n].copy()
+
+
+def residuals_eval(kind, source_poses, target_poses, offsets, sp, tp, sn=None, tn=None,
+                   jacobians=True):
+    """The reference's LIDARPointResidual (kind 0) / LIDARNormalResidual (kind 1) functors
+    (src/optimization/slam_residuals.h:64-177), compiled unchanged and evaluated through
+    AutoDiffCostFunction::Evaluate.  -> (residuals [n, 2], jac_source [n, 2, 3],
+    jac_target [n, 2, 3]) like nautilus_residuals_eval."""
+    sp = np.ascontiguousarray(sp, np.float32).reshape(-1, 2)
+    tp = np.ascontiguousarray(tp, np.float32).reshape(-1, 2)
+    n = len(sp)
+    sn = np.zeros((n, 2), np.float32) if sn is None else np.ascontiguousarray(sn, np.float32).reshape(-1, 2)
+    tn = np.zeros((n, 2), np.float32) if tn is None else np.ascontiguousarray(tn, np.float32).reshape(-1, 2)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    a = np.ascontiguousarray(source_poses, np.float64).reshape(-1, 3)
+    b = np.ascontiguousarray(target_poses, np.float64).reshape(-1, 3)
+    res = np.zeros((n, 2), np.float64)
+    js = np.zeros((n, 2, 3), np.float64)
+    jt = np.zeros((n, 2, 3), np.float64)
+    rc = lib().ref_residuals_eval(kind, a.reshape(-1), b.reshape(-1), offsets, len(offsets) - 1,
+                                  sp.reshape(-1), tp.reshape(-1), sn.reshape(-1), tn.reshape(-1),
+                                  res.reshape(-1),
+                                  js.ctypes.data_as(C.c_void_p) if jacobians else None,
+                                  jt.ctypes.data_as(C.c_void_p) if jacobians else None)
+    assert rc == 0
+    return (res, js, jt) if jacobians else res

@@ -5,8 +5,8 @@
 #      type-checks against the reference's REAL headers (slam_types.h, slam_util.h,
 #      data_structures.h, kdtree.h, math_util.h, feature_extracter.h) and the product's
 #      include/nautilus_csm.h, with stand-ins only for the un-vendored third parties
-#      (Eigen, glog, ROS message types: oracle/shim; Eigen geometry + Ceres names:
-#      patches/check/include).
+#      (Eigen, glog, ROS message types, the Ceres names data_structures.h mentions:
+#      oracle/shim).
 # solver.cc itself needs Ceres, ROS, Boost.Math and vector_maps to parse and is not
 # compiled here; its hunks are thin calls into csm_batch.
 set -e
@@ -21,6 +21,6 @@ cp "$REF/CMakeLists.txt" "$TMP/"
 (cd "$TMP" && patch -p1 --quiet < "$HERE/solver_batched.patch")
 echo "patch applies"
 g++ -std=c++17 -fsyntax-only \
-  -I"$HERE/check/include" -I"$HERE/../oracle/shim" -I"$HERE/../include" \
+  -I"$HERE/../oracle/shim" -I"$HERE/../include" \
   "$TMP/src/optimization/csm_batch.cc"
 echo "csm_batch.cc type-checks against the reference headers"

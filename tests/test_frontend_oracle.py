@@ -34,6 +34,23 @@ def test_port_vs_reference_golden(fe_golden, tr):
     assert offs[4] - offs[3] == 0          # the scan without a valid return is empty
 
 
+def test_port_nautilus_variant_and_scatter_vs_reference_golden(fe_golden):
+    """The variant the Nautilus node calls (src/input/pointcloud_helpers.cc:28-48) and
+    the keyframe filter (lc_candidate_filter.cc:34-81): port against fixtures made by the
+    reference's own translation units."""
+    g = fe_golden
+    r, offs, xy = g["ranges"], g["nautilus_offsets"], g["nautilus_xy"]
+    for s in range(len(r)):
+        got = fp.laser_to_points_nautilus(r[s], sr.ANGLE_MIN, sr.ANGLE_INC, sr.RANGE_MIN, sr.MAX_RANGE)
+        want = xy[offs[s]:offs[s + 1]]
+        assert got.shape == want.shape and np.array_equal(bits(got), bits(want)), s
+    lo = g["lc_offsets"]
+    scores = np.asarray([fp.scatter_score(g["lc_xy"][lo[k]:lo[k + 1]]) for k in range(len(lo) - 1)])
+    assert np.array_equal(scores, g["lc_scores"])
+    cand = fp.lc_candidates(g["lc_poses"][:, :2].astype(np.float32), scores)
+    assert cand.tolist() == g["lc_candidates"].tolist() and len(cand) >= 3
+
+
 def test_port_vs_compiled_reference(ref_lib):
     r = sr.make_ranges(40, seed=11)
     for s in range(len(r)):
@@ -43,6 +60,12 @@ def test_port_vs_compiled_reference(ref_lib):
             got = fp.laser_to_points_csm(r[s], sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC,
                                          sr.RANGE_MIN, sr.MAX_RANGE, tr)
             assert got.shape == want.shape and np.array_equal(bits(got), bits(want))
+        want = ref_lib.nautilus_laser_to_points(r[s], sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC,
+                                                sr.RANGE_MIN, sr.MAX_RANGE)
+        got = fp.laser_to_points_nautilus(r[s], sr.ANGLE_MIN, sr.ANGLE_INC, sr.RANGE_MIN, sr.MAX_RANGE)
+        assert got.shape == want.shape and np.array_equal(bits(got), bits(want))
+        if len(want) > 1:
+            assert fp.scatter_score(want) == ref_lib.scatter_score(want)
 
 
 def test_nautilus_variant_shares_the_arithmetic():

@@ -35,6 +35,23 @@ def test_csm_variant_vs_reference_golden(matcher, tr):
     assert np.array_equal(bits(xy), bits(g[f"csm_t{tr}_xy"]))
 
 
+def test_nautilus_variant_and_keyframes_vs_reference_golden(matcher):
+    """nautilus::LaserScanToPointCloud (src/input/pointcloud_helpers.cc:28-48), the scatter
+    score and GetLCCandidates (lc_candidate_filter.cc:34-81) against fixtures produced by
+    the reference's own translation units: points bit-exact, candidates identical, scores
+    to 1e-6 (float sums in the reference's order; eigenvalues in closed form)."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "frontend_golden.npz"))
+    matcher.upload_ranges(g["ranges"], sr.ANGLE_MIN, sr.ANGLE_MAX, sr.ANGLE_INC, sr.RANGE_MIN,
+                          sr.MAX_RANGE, variant=0)
+    xy, offs = matcher.download_scans()
+    assert np.array_equal(offs, g["nautilus_offsets"])
+    assert np.array_equal(bits(xy), bits(g["nautilus_xy"]))
+    matcher.upload_scans(g["lc_xy"], g["lc_offsets"])
+    assert np.allclose(matcher.scatter_scores(), g["lc_scores"], rtol=1e-6, atol=0)
+    cand = matcher.GetLCCandidates(g["lc_poses"][:, :2].astype(np.float32))
+    assert cand.tolist() == g["lc_candidates"].tolist()
+
+
 @pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("n_beams", [1080, 37, 1])
 def test_vs_port_seeded(matcher, variant, n_beams):

@@ -1,6 +1,10 @@
-"""Residual blocks (residuals.cu): CPU checks of the oracle's dual-number restatement
-against finite differences, GPU parity of the analytic-Jacobian kernel against it.
-Tolerance (floating point): 1e-12 relative to max(1, |value|)."""
+"""Residual blocks (residuals.cu).  The checker is pinned to the reference's own functor
+source: slam_residuals.h:64-177 compiled UNCHANGED into oracle/_ref and evaluated through
+AutoDiffCostFunction::Evaluate (fixtures: tests/golden/residual_golden.npz); the numpy
+dual-number port (oracle/residual_port.py) must reproduce those fixtures bit for bit and is
+itself checked against finite differences.  GPU parity of the analytic-Jacobian kernel
+against both.  Tolerance (floating point): 1e-12 relative to max(1, |value|)."""
+import os
 import numpy as np
 import pytest
 
@@ -25,6 +29,47 @@ def make_blocks(n_blocks, seed=0, max_corr=40):
     ns = np.stack([np.cos(ang[0]), np.sin(ang[0])], 1).astype(np.float32)
     nt = np.stack([np.cos(ang[1]), np.sin(ang[1])], 1).astype(np.float32)
     return sp, tp, offs, p, q, ns, nt
+
+
+def residual_golden():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "residual_golden.npz"))
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_port_vs_reference_functor_golden(kind):
+    g = residual_golden()
+    k = f"k{kind}_"
+    got = rp.evaluate(kind, g[k + "sp"], g[k + "tp"], g[k + "offs"], g[k + "p"], g[k + "q"],
+                      g[k + "ns"], g[k + "nt"])
+    for a, name in zip(got, ("res", "js", "jt")):
+        assert np.array_equal(a, g[k + name]), name
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_port_vs_compiled_reference_functors(ref_lib, kind):
+    sp, tp, offs, p, q, ns, nt = make_blocks(30, seed=21 + kind)
+    want = ref_lib.residuals_eval(kind, sp, tp, offs, p, q, ns, nt)
+    got = rp.evaluate(kind, sp, tp, offs, p, q, ns, nt)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    only = ref_lib.residuals_eval(kind, sp, tp, offs, p, q, ns, nt, jacobians=False)
+    assert np.array_equal(only, want[0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", [0, 1])
+def test_gpu_vs_reference_functor_golden(kind):
+    from nautilus_b200 import CorrelativeScanMatcher
+    from nautilus_b200.residuals import evaluate_residual_blocks
+    g = residual_golden()
+    k = f"k{kind}_"
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    got = evaluate_residual_blocks(m, kind, g[k + "sp"], g[k + "tp"], g[k + "offs"], g[k + "p"],
+                                   g[k + "q"], g[k + "ns"], g[k + "nt"])
+    for a, name in zip(got, ("res", "js", "jt")):
+        want = g[k + name]
+        assert np.all(np.abs(a - want) <= TOL * np.maximum(1.0, np.abs(want))), name
+    m.close()
 
 
 @pytest.mark.parametrize("kind", [0, 1])
