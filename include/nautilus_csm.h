@@ -326,6 +326,12 @@ int nautilus_residuals_last_ms(const NautilusCsm* h, float* kernel_ms);
  * cell_size = the largest threshold later calls will use, e.g.
  * outlier_threshold (config/default_config.lua:66). */
 int nautilus_nn_build(NautilusCsm* h, double cell_size);
+/* Starts the host half of nautilus_nn_build (the KD-tree layout, the slow part: 0.4 s
+ * for 20 000 scans) on library threads and returns at once, so that it overlaps what
+ * the caller does next on the GPU - typically the CSM batch, which does not need the
+ * index.  A later nautilus_nn_build with the same cell_size joins it and finishes on
+ * the device.  Replacing the scan set cancels it. */
+int nautilus_nn_build_begin(NautilusCsm* h, double cell_size);
 
 /* target_to_world.inverse() * source_to_world as a row-major 2x3 float matrix
  * from two (x, y, theta) poses: GetPoseAsAffine<float> (src/util/slam_util.h:

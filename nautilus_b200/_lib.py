@@ -62,7 +62,7 @@ EXPORTS = [
     "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
     "nautilus_csm_match_batch", "nautilus_csm_copy_results_dev", "nautilus_csm_match", "nautilus_csm_rotation_window",
     "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_regular_check",
-    "nautilus_nn_build", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
+    "nautilus_nn_build", "nautilus_nn_build_begin", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_host_alloc", "nautilus_host_free",
     "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
@@ -179,6 +179,7 @@ def lib():
     L.nautilus_nn_match_resident.argtypes = [vp, vp, vp, vp, d, i32, vp]
     L.nautilus_residuals_eval_resident.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.nautilus_nn_build.argtypes = [vp, d]
+    L.nautilus_nn_build_begin.argtypes = [vp, d]
     L.nautilus_nn_pose_transform.restype = None
     L.nautilus_nn_pose_transform.argtypes = [vp, vp, vp]
     L.nautilus_nn_match_batch.argtypes = [vp, vp, vp, vp, d, i32, vp, vp, vp]

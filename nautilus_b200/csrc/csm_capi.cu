@@ -493,6 +493,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
+  nautilus_internal_nn_cancel(h);
   nautilus_internal_comm_release(h);
   h->gather_dev.release(); h->gather_pin.release();
   free_slots(h);
@@ -536,6 +537,7 @@ int nautilus_csm_upload_scans(NautilusCsm* h, const float* xy, const int64_t* of
   NAUTILUS_GUARD(h);
   CU_TRY(cudaSetDevice(h->device));
   h->nn.built = false;  // the NN index belongs to the previous scan set
+  nautilus_internal_nn_cancel(h);  // a begun host build reads the set that is being replaced
   int rc = upload_scan_set(h, h->user_scans, xy, offsets, n_scans);
   if (rc) return rc;
   // the host copy the NN path needs for its KD-tree layout is fetched from the

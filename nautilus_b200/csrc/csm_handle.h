@@ -160,6 +160,8 @@ int nautilus_internal_match_launch(NautilusCsm* h, csmh::ScanSet& ss, const int3
                                    const double* rot_max, int32_t n_pairs, size_t result_capacity);
 int nautilus_internal_queue_spec_counts(NautilusCsm* h, int** out);
 int nautilus_internal_match_timings(NautilusCsm* h, const int* spec_counts);
+// nn_capi.cu: joins and drops a host index build begun by nautilus_nn_build_begin
+void nautilus_internal_nn_cancel(NautilusCsm* h);
 // csm_comm.cu: releases the handle's communicator
 void nautilus_internal_comm_release(NautilusCsm* h);
 // frontend.cu: makes ScanSet::host_xy of the user scans valid (D2H when the clouds
@@ -281,4 +283,5 @@ struct NautilusCsm {
 
   // nearest-neighbour matching (nn_capi.cu)
   csmh::NnState nn;
+  void* nn_host_build = nullptr;  // NnHostBuild of nautilus_nn_build_begin (nn_capi.cu)
 };

@@ -225,6 +225,7 @@ int nautilus_csm_upload_ranges(NautilusCsm* h, const float* ranges, int32_t n_sc
   if (smem > 200 * 1024) return fail(NAUTILUS_EINVAL, "too many beams per scan for the glancing filter");
   CU_TRY(cudaSetDevice(h->device));
   h->nn.built = false;  // the NN index belongs to the previous scan set
+  nautilus_internal_nn_cancel(h);
   ScanSet& ss = h->user_scans;
   cudaStream_t st = h->stream;
 

@@ -180,6 +180,65 @@ void nautilus_nn_pose_transform(const double* source_pose, const double* target_
   m[5] = (il[2] * st[0] + il[3] * st[1]) + it[1];
 }
 
+}  // extern "C"
+
+// Host half of the index build: the reference's trees (kdtree.cc:114-150) for every
+// scan, scans spread over threads.  nautilus_nn_build_begin runs it on a library
+// thread so that it overlaps whatever the caller does next on the GPU (the CSM batch
+// does not touch it); nautilus_nn_build joins it, or runs it inline.
+struct NnHostBuild {
+  std::vector<KdNode> nodes;
+  std::vector<float> skip_val;
+  std::vector<int> skip_dim;
+  double cell_size = 0.0;
+  std::thread worker;
+  bool running = false;
+  void run(const float* xy_host, const std::vector<long long>* offs, int n_scans) {
+    const long long total = (*offs)[n_scans];
+    nodes.assign((size_t)std::max<long long>(total, 1), KdNode());
+    skip_val.assign((size_t)std::max<long long>(total, 1), 0.f);
+    skip_dim.assign((size_t)std::max<long long>(total, 1), 0);
+    unsigned nt = std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
+    nt = std::min<unsigned>(nt, (unsigned)std::max(1, n_scans));
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < nt; ++t) {
+      const int s0 = (int)((long long)n_scans * t / nt), s1 = (int)((long long)n_scans * (t + 1) / nt);
+      pool.emplace_back(build_trees, xy_host, std::cref(*offs), s0, s1, nodes.data(),
+                        skip_val.data(), skip_dim.data());
+    }
+    for (auto& th : pool) th.join();
+  }
+};
+
+void nautilus_internal_nn_cancel(NautilusCsm* h) {
+  NnHostBuild* hb = static_cast<NnHostBuild*>(h->nn_host_build);
+  if (!hb) return;
+  if (hb->running) hb->worker.join();
+  delete hb;
+  h->nn_host_build = nullptr;
+}
+
+extern "C" {
+
+int nautilus_nn_build_begin(NautilusCsm* h, double cell_size) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
+  if (!(cell_size > 0)) return fail(NAUTILUS_EINVAL, "cell_size must be positive");
+  ScanSet& ss = h->user_scans;
+  if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
+  CU_TRY(cudaSetDevice(h->device));
+  nautilus_internal_nn_cancel(h);
+  const int rc_xy = nautilus_internal_host_xy(h);  // clouds made on the device are fetched once
+  if (rc_xy) return rc_xy;
+  NnHostBuild* hb = new NnHostBuild();
+  hb->cell_size = cell_size;
+  hb->running = true;
+  // the scan set may not be replaced while this runs: upload_scans cancels (joins) first
+  hb->worker = std::thread(&NnHostBuild::run, hb, ss.host_xy.data(), &ss.host_offsets, ss.n);
+  h->nn_host_build = hb;
+  return NAUTILUS_OK;
+}
+
 int nautilus_nn_build(NautilusCsm* h, double cell_size) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");
   NAUTILUS_GUARD(h);
@@ -190,11 +249,24 @@ int nautilus_nn_build(NautilusCsm* h, double cell_size) {
   NnState& nn = h->nn;
   nn.release();
   const long long total = ss.host_offsets[ss.n];
-  {  // clouds converted on the device (nautilus_csm_upload_ranges) are fetched once
+  NnHostBuild* hb = static_cast<NnHostBuild*>(h->nn_host_build);
+  if (hb && hb->cell_size != cell_size) {  // a begun build for another threshold: drop it
+    nautilus_internal_nn_cancel(h);
+    hb = nullptr;
+  }
+  if (hb) {
+    if (hb->running) { hb->worker.join(); hb->running = false; }
+  } else {
     const int rc_xy = nautilus_internal_host_xy(h);
     if (rc_xy) return rc_xy;
+    hb = new NnHostBuild();
+    hb->cell_size = cell_size;
+    h->nn_host_build = hb;
+    hb->run(ss.host_xy.data(), &ss.host_offsets, ss.n);
   }
-  const float* xy_host = ss.host_xy.data();
+  std::vector<KdNode>& nodes = hb->nodes;
+  std::vector<float>& skip_val = hb->skip_val;
+  std::vector<int>& skip_dim = hb->skip_dim;
   int max_pts = 0;
   for (int s = 0; s < ss.n; ++s)
     max_pts = std::max<long long>(max_pts, ss.host_offsets[s + 1] - ss.host_offsets[s]);
@@ -206,22 +278,6 @@ int nautilus_nn_build(NautilusCsm* h, double cell_size) {
   // a hair above the threshold so that float rounding never separates two points
   // closer than the threshold by more than one cell
   nn.cell = cell_size * (1.0 + 1e-6);
-
-  // ---- host: the reference's trees (kdtree.cc:114-150), scans across threads
-  std::vector<KdNode> nodes((size_t)std::max<long long>(total, 1));
-  std::vector<float> skip_val((size_t)std::max<long long>(total, 1), 0.f);
-  std::vector<int> skip_dim((size_t)std::max<long long>(total, 1), 0);
-  {
-    unsigned nt = std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
-    nt = std::min<unsigned>(nt, (unsigned)ss.n);
-    std::vector<std::thread> pool;
-    for (unsigned t = 0; t < nt; ++t) {
-      const int s0 = (int)((long long)ss.n * t / nt), s1 = (int)((long long)ss.n * (t + 1) / nt);
-      pool.emplace_back(build_trees, xy_host, std::cref(ss.host_offsets), s0, s1, nodes.data(),
-                        skip_val.data(), skip_dim.data());
-    }
-    for (auto& th : pool) th.join();
-  }
   nn.pad_off_host = ss.host_offsets;  // GridPoint is 16 bytes: no padding needed
 
   const size_t tot = (size_t)std::max<long long>(total, 1);
@@ -261,6 +317,7 @@ int nautilus_nn_build(NautilusCsm* h, double cell_size) {
                   nullptr, nn.counters, st);
   CU_TRY(cudaGetLastError());
   CU_TRY(cudaStreamSynchronize(st));
+  nautilus_internal_nn_cancel(h);  // the host arrays are on the device now
   return NAUTILUS_OK;
 }
 

@@ -333,6 +333,11 @@ class CorrelativeScanMatcher:
         largest threshold later calls use (outlier_threshold)."""
         check(self._L.nautilus_nn_build(self._h, float(cell_size)))
 
+    def nn_build_begin(self, cell_size: float) -> None:
+        """Start the host KD-tree layout of nn_build on library threads (returns at once);
+        a later nn_build(cell_size) joins it."""
+        check(self._L.nautilus_nn_build_begin(self._h, float(cell_size)))
+
     def nn_match_batch(self, src_ids, tgt_ids, transforms, threshold: float, *,
                        with_dist: bool = False):
         """-> (match_idx int32 [sum of source sizes], offsets int64 [n_pairs+1][, dist])."""

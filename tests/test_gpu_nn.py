@@ -248,3 +248,30 @@ def test_planar_subsets_through_resident_chain():
         assert np.array_equal(g, w)
     m.close()
     full.close()
+
+
+def test_async_index_build_overlapping_a_csm_batch():
+    """nautilus_nn_build_begin runs the host KD-tree layout on library threads while the
+    caller matches a CSM batch; the joined index gives the matches a plain build gives,
+    and replacing the scan set while a build is in flight is safe."""
+    xy, offs, poses = synth.make_scan_set(40, group=5, seed=13, n_beams=360, return_poses=True)
+    pa, pb = synth.make_pair_list(40, group=5)
+    tr = np.stack([pose_transform(poses[a], poses[b]) for a, b in zip(pa, pb)])
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    m.nn_build(0.25)
+    want_idx, want_off = m.nn_match_batch(pa, pb, tr, 0.25)
+    want_self = m.nn_self_index()
+    m.upload_scans(xy, offs)          # drops the index
+    m.nn_build_begin(0.25)
+    csm = m.match_batch(pa, pb, -0.5, 0.5)   # overlaps the host build
+    m.nn_build(0.25)                  # joins
+    idx, off = m.nn_match_batch(pa, pb, tr, 0.25)
+    assert np.array_equal(idx, want_idx) and np.array_equal(off, want_off)
+    assert np.array_equal(m.nn_self_index(), want_self)
+    m.nn_build_begin(0.25)
+    m.upload_scans(xy[:offs[10]], offs[:11])  # cancels the build in flight
+    m.nn_build(0.5)
+    assert len(m.nn_self_index()) == offs[10]
+    assert len(csm[0]) == len(pa)
+    m.close()

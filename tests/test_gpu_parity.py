@@ -349,6 +349,8 @@ def test_concurrent_callers_on_one_handle():
     for t in ts:
         t.join()
     assert not errs, errs
+    served, batches = m.single_queue_stats()
+    assert served == len(pairs) * 4 and 1 <= batches <= served  # combined, never dropped
     for got, want in zip(out, serial):
         assert got[0] == want[0]
         assert got[1][0][0] == want[1][0][0] and got[1][0][1] == want[1][0][1] and got[1][1] == want[1][1]
