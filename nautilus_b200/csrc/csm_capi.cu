@@ -43,6 +43,34 @@ long long host_cell(float v, double res, uint64_t dim) {
   return (long long)c;
 }
 
+// tail[d] = sup_{d' >= d} g(d') / g(0) for the 1-D impulse response g of the blur
+// (order-0 Van Vliet recursion, forward then backward, CImg.h:49084-49114, on a line
+// long enough that both ends hold zeros).  The raster kernel uses it to bound how far
+// from a scan a table can exceed the lookup floor (csm_tables.cu).
+std::vector<double> blur_tail(const VanVliet& f, int margin) {
+  const int n = 4 * margin + 65, c = n / 2;
+  std::vector<double> x((size_t)n, 0.0);
+  x[c] = 1.0;
+  double v1 = 0, v2 = 0, v3 = 0;
+  for (int i = 0; i < n; ++i) {
+    const double v0 = ((x[i] + v1 * f.a1) + v2 * f.a2) + v3 * f.a3;
+    x[i] = v0; v3 = v2; v2 = v1; v1 = v0;
+  }
+  const double sum = f.B * f.B;
+  v1 = v2 = v3 = 0;  // zero state at the far end (the Triggs term of a zero tail)
+  for (int i = n - 1; i >= 0; --i) {
+    const double v0 = ((x[i] * sum + v1 * f.a1) + v2 * f.a2) + v3 * f.a3;
+    x[i] = v0; v3 = v2; v2 = v1; v1 = v0;
+  }
+  std::vector<double> tail((size_t)margin + 1, 0.0);
+  double run = 0.0;
+  for (int d = n - 1 - c; d >= 0; --d) {
+    run = std::max(run, std::max(fabs(x[c + d]), fabs(x[c - d])));
+    if (d <= margin) tail[d] = x[c] > 0 ? run / x[c] : 1.0;
+  }
+  return tail;
+}
+
 // Float thresholds of the cell map (see csm::CellMap): entry k is the smallest
 // float v with floor((double)v / res) >= qlo + k, found with the reference's
 // own expression (CorrelativeScanMatcher.h:43-49) by stepping nextafterf.
@@ -113,7 +141,7 @@ void free_slots(NautilusCsm* h) {
 size_t slot_bytes(const Geometry& g) {
   const size_t w = g.w, wl = g.wl;
   return sizeof(double) * ((w + 3) & ~(size_t)3) * w + sizeof(unsigned) * g.bm_stride * w + w +
-         sizeof(double) * (wl * wl + (wl + 2) * (size_t)lowlog_stride((int)wl));
+         sizeof(double) * (wl * wl + lowlog_cells((int)wl));
 }
 
 // Makes at least `want` table slots resident (bounded by params.max_tables and
@@ -136,7 +164,7 @@ int ensure_slots(NautilusCsm* h, int want) {
   CU_TRY(cudaMalloc(&h->slab_bitmap, sizeof(unsigned) * (size_t)g.bm_stride * w * want));
   CU_TRY(cudaMalloc(&h->slab_rowflag, w * (size_t)want));
   CU_TRY(cudaMalloc(&h->slab_low, sizeof(double) * wl * wl * want));
-  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * (wl + 2) * lowlog_stride((int)wl) * want));
+  CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * lowlog_cells((int)wl) * want));
   h->slots_host.resize(want);
   for (int i = 0; i < want; ++i) {
     TableSlot& s = h->slots_host[i];
@@ -144,7 +172,7 @@ int ensure_slots(NautilusCsm* h, int want) {
     s.bitmap = h->slab_bitmap + (size_t)g.bm_stride * w * i;
     s.rowflag = h->slab_rowflag + w * (size_t)i;
     s.low = h->slab_low + wl * wl * (size_t)i;
-    s.lowlog = h->slab_lowlog + (wl + 2) * lowlog_stride((int)wl) * (size_t)i;
+    s.lowlog = h->slab_lowlog + lowlog_cells((int)wl) * (size_t)i;
   }
   int rc = h->slots_dev.reserve(want);
   if (rc) return rc;
@@ -471,6 +499,17 @@ int nautilus_csm_create(const NautilusCsmParams* p, NautilusCsm** out) {
     if (cudaStreamCreateWithPriority(&h->table_stream, cudaStreamNonBlocking, hi) != cudaSuccess)
       h->table_stream = nullptr;
   }
+  h->geo.tail = nullptr;
+  h->geo.tight = 0;
+  if (h->geo.margin >= 0) {
+    const std::vector<double> tail = blur_tail(h->vv, h->geo.margin);
+    if (h->tail_dev.reserve(tail.size()) ||
+        cudaMemcpy(h->tail_dev.p, tail.data(), sizeof(double) * tail.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+      nautilus_csm_destroy(h);
+      return fail(NAUTILUS_ECUDA, "upload of the blur tail failed");
+    }
+    h->geo.tail = h->tail_dev.p;
+  }
   h->pool_host = make_pool_list(p->scanner_range, p->low_res, p->high_res, (uint64_t)h->geo.w,
                                 (uint64_t)h->geo.wl);
   h->geo.n_pool = (int)h->pool_host.s.size();
@@ -501,7 +540,7 @@ void nautilus_csm_destroy(NautilusCsm* h) {
   h->pool_dev.release();
   h->slots_dev.release(); h->metas_dev.release(); h->dense_scratch.release();
   h->scalar_scratch.release();
-  h->thr_low_dev.release(); h->thr_high_dev.release();
+  h->thr_low_dev.release(); h->thr_high_dev.release(); h->tail_dev.release();
   h->t_low_dev.release(); h->t_high_dev.release(); h->slot_rank_dev.release(); h->n_h_dev.release();
   h->user_scans.release(); h->tmp_scans.release();
   h->table_scan_dev.release(); h->pairs_dev.release(); h->rots_dev.release();

@@ -24,10 +24,21 @@ __device__ __forceinline__ double lookup_log(double v) {
   return v > CSM_MIN_VALUE_FOR_LOOKUP ? log(v) : CSM_FLOOR_LOG;
 }
 
-// Floor columns on either side of a lowlog row = x translations one lane of the
-// low-res scorer owns (csm_search.cu LS_IU).
-#define CSM_LOW_PAD 7
-__host__ __device__ __forceinline__ int lowlog_stride(int wl) { return (wl + 2 * CSM_LOW_PAD) | 1; }
+// Floor padding of the pooled log table: a full tile of the low-res scorer (14 x
+// translations by 16 y translations, csm_search.cu LS_TI x LS_TJ) on every side, so that
+// the 14 x 16 patch of cells any (point, rotation) addresses lies inside the padded
+// array wherever it falls relative to the table - entirely outside patches are clamped
+// onto the padding - and needs no bounds test.
+#define CSM_LOW_PADX 14
+#define CSM_LOW_PADY 16
+__host__ __device__ __forceinline__ int lowlog_stride(int wl) { return (wl + 2 * CSM_LOW_PADX) | 1; }
+__host__ __device__ __forceinline__ int lowlog_rows(int wl) { return wl + 2 * CSM_LOW_PADY; }
+__host__ __device__ __forceinline__ size_t lowlog_cells(int wl) {
+  return (size_t)lowlog_rows(wl) * (size_t)lowlog_stride(wl);
+}
+__host__ __device__ __forceinline__ size_t lowlog_index(int wl, int x, int y) {
+  return (size_t)(y + CSM_LOW_PADY) * (size_t)lowlog_stride(wl) + (size_t)(x + CSM_LOW_PADX);
+}
 
 // Van Vliet-Young order-0 coefficients + Triggs-Sdika matrix
 // (CImg.h:49267-49284, 49066-49081); filled on the host.
@@ -40,9 +51,14 @@ struct VanVliet {
 struct TableMeta {
   // occupied box of the scan, in hi-res cells, inclusive; cx1 < cx0 => no point
   int cx0, cx1, cy0, cy1;
-  // active rectangle the blurred table is computed on (inclusive); the cells
-  // outside it hold values below 1e-20 of the maximum and read as 0
+  // active rectangle the blurred table is STORED on (inclusive): what the normalise
+  // pass, the search kernels and the table download see; cells outside it read as 0 /
+  // the lookup floor
   int ax0, ax1, ay0, ay1;
+  // last column / row the recursions are COMPUTED on (>= ax1 / ay1): the anti-causal
+  // passes start here.  Tables built for matching store less than they compute, see
+  // raster_kernel.
+  int bx1, by1;
   int stride;    // row stride of the slot's value buffer, in doubles
   int cropped;   // 1 when the active rectangle is not the whole grid
   int n_inside;  // points that fell inside the grid
@@ -63,9 +79,9 @@ struct TableSlot {
   unsigned char* rowflag;  // 1 per occupied-box row that has a point
   double* low;         // wl*wl low-res values (max-pool of the normalised table)
   double* lowlog;      // lookup_log of the low-res table in the padded layout the
-                       // scorer reads: (wl+2) rows of lowlog_stride(wl) doubles,
-                       // cell (x, y) at [(y + 1) * stride + x + CSM_LOW_PAD]; the
-                       // pad columns on either side, row 0 and row wl+1 hold the floor
+                       // scorer reads: lowlog_rows(wl) rows of lowlog_stride(wl)
+                       // doubles, cell (x, y) at lowlog_index(wl, x, y); the padding
+                       // (CSM_LOW_PADX columns / CSM_LOW_PADY rows each side) holds the floor
 };
 
 // Grid geometry shared by all kernels.
@@ -77,6 +93,11 @@ struct Geometry {
   int bm_stride;  // bitmap words per row = ceil(w/32)
   int margin;     // crop margin in cells; <0 => never crop
   int n_pool;     // number of pooling windows per axis (loop trips of cc:37)
+  // tail[d] = sup over d' >= d of g(d') / g(0), g = 1-D impulse response of the blur
+  // (device array of margin + 1 doubles, null when margin < 0): lets the raster kernel
+  // bound how far from a scan its table can exceed the lookup floor
+  const double* tail;
+  int tight;      // 1: tables of this wave store only what can exceed the floor
 };
 
 // Exact cell lookup without a double division.  cell(v) = dim/2 + floor((double)v / res)

@@ -218,6 +218,7 @@ struct NautilusCsm {
   unsigned char* slab_rowflag = nullptr;
   double* slab_low = nullptr;
   double* slab_lowlog = nullptr;
+  DevBuf<double> tail_dev;  // Geometry::tail
   DevBuf<double> dense_scratch;
   DevBuf<double> scalar_scratch;
 

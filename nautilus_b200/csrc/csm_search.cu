@@ -52,35 +52,38 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // tile).  Because the translation step equals the cell size (both are low_res_,
 // cc:96-99), the 7 cells a lane needs for one point are 7 CONSECUTIVE doubles of
 // one table row and the 16 lanes of a half-warp read 16 consecutive rows: a
-// point's 14 x 16 patch is addressed by one word (first row, first column of
-// either half), computed once per (rotation, point) in phase A (lane = point).
-// The rare sum that lands within float rounding of a cell edge is flagged there
-// and looked up cell by cell (cell_fast) instead.
+// point's 14 x 16 patch is addressed by ONE cell index (its first row and column),
+// computed once per (rotation, point) in phase A (lane = point) from one float
+// quotient per axis; the host proves the margin (SearchGrid::reg_eps) within which
+// "translation k lands k cells further" is exact for all 16 translations of a tile.
+// The rare sum that lands within that margin of a cell edge is flagged and looked up
+// cell by cell (cell_fast) instead.
+//
+// Table.  The scorer reads the pooled log table through a copy that is padded with a
+// whole tile of lookup-floor cells on every side (CSM_LOW_PADX / CSM_LOW_PADY): a patch
+// that straddles the table edge reads real cells and floor cells from the same
+// addresses as an inner one, and a patch entirely outside is clamped onto the padding.
+// Every regular point is therefore the same case - no edge / floor / inner kinds, no
+// clamps in the inner loop.  The copy is the above-floor box of the table
+// (TableMeta::lx0..ly1, everything outside it reads the floor anyway) staged in shared
+// memory once per block, odd row stride so that the 16 rows of a half-warp hit 16
+// different bank pairs; tables whose box does not fit the budget are read from the
+// global array, which has the same padded layout, through L1.
 //
 // Runs.  Consecutive beams of a scan land 1-5 cm apart, far less than a 0.3 m
 // cell, so consecutive points mostly address the SAME patch (82 % on the bench
-// scans).  Phase A run-length encodes the patch words of a 32-point chunk
+// scans).  Phase A run-length encodes the patch indices of a 32-point chunk
 // (shuffle + ballot); phase B loads the 7 values of a run once and adds them
 // once per point of the run.  Every sum still takes its terms in point order,
 // one lane per candidate, like cc:66-77 -- only the loads are shared -- and the
 // kernel is bound by the fp64 add pipe instead of shared-memory bandwidth.
 // A warp owns a rotation; the warps of a block take rotations round-robin.
-//
-// Table.  The part of the pooled log table above the lookup floor (TableMeta::
-// lx0..ly1) is staged in shared memory once per block with 7 floor columns on
-// either side and a floor row above and below, so patches that leave the box
-// need no special case; the row stride is odd, so the 16 rows of a half-warp
-// hit 16 different bank pairs.  Tables whose box does not fit the budget are
-// read from global memory (same padded layout) through L1.
 // ---------------------------------------------------------------------------
 #ifndef LS_WARPS_N
 #define LS_WARPS_N 12
 #endif
-#ifndef LS_PREF      // 1: fetch the next run's descriptor before the adds of the current run
-#define LS_PREF 0
-#endif
-#ifndef LS_RUNLOOP   // points per iteration of the add loop (4 + tails, or 2 + tail)
-#define LS_RUNLOOP 2
+#ifndef LS_MINB_N      // resident blocks per SM the register budget is set for
+#define LS_MINB_N 2
 #endif
 constexpr int LS_WARPS = LS_WARPS_N;
 constexpr int LS_THREADS = LS_WARPS * 32;
@@ -88,16 +91,14 @@ constexpr int LS_PC = 32;            // points per chunk = one per lane in phase
 constexpr int LS_TJ = 16;            // y translations per tile
 constexpr int LS_IU = 7;             // x translations per lane
 constexpr int LS_TI = 2 * LS_IU;     // x translations per tile
-constexpr int LS_XPAD = CSM_LOW_PAD;  // floor columns on either side of the staged box
-static_assert(CSM_LOW_PAD == LS_IU, "a lane's window must fit the floor padding");
-// patch word: bits 0-9 first row + LS_YB, bits 10-20 / 21-31 first column of half 0 / 1
-constexpr int LS_YB = 32;
-constexpr unsigned LS_ODD = 0xffffffffu;  // look every cell up on its own
-// run info: bits 0-23 first cell of the patch (inner runs), 24-29 points in the run, 30-31 kind
-constexpr unsigned LS_INNER = 0u;       // the 16 x 14 patch lies inside the staged rows / columns: no clamps
-constexpr unsigned LS_FLOOR = 1u << 30; // the patch lies outside the box: every value is the lookup floor
-constexpr unsigned LS_EDGE = 2u << 30;  // rows / columns clamped onto the floor padding (the patch word)
-constexpr unsigned LS_SLOW = 3u << 30;  // LS_ODD
+static_assert(CSM_LOW_PADX == LS_TI && CSM_LOW_PADY == LS_TJ, "the padding is one tile");
+// run descriptor: bits 0-23 the patch, 24-29 points in the run, 31 slow.  The patch is
+// the index of its first cell in the padded array, or - when the staged copy keeps only
+// ONE floor row above and below its box to fit the shared-memory budget (ROWCLAMP) -
+// its first row + LS_TJ in bits 0-9 and its first column in bits 10-20; the lanes then
+// clamp their own row onto the two floor rows.
+constexpr unsigned LS_SLOW = 0x80000000u;   // look every cell up on its own (always a run of one)
+constexpr unsigned LS_CELL_MASK = 0x00ffffffu;
 
 int low_score_warps() { return LS_WARPS; }
 
@@ -109,16 +110,16 @@ size_t low_score_smem_bytes(int n_t, int wl, int table_cells) {
   return b;
 }
 
-// Geometry of the table a block scores against (staged box or the whole table).
+// Geometry of the padded table a block scores against (staged box or the global array).
 struct LowTab {
   const double* tab;  // shared (staged) or global (lowlog)
   unsigned tab_s;     // shared-window address of tab when it is staged
   int ox, oy;         // low-res cell of box column / row 0
   int tw, th;         // box width / height in cells
   int ts;             // row stride in doubles
-  int xpad;           // floor columns left of the box (column 0 always reads the floor)
-  // rows of tab: 0 = floor, 1 .. th = box rows, th + 1 = floor
-  int row_below;      // th + 1
+  int pady;           // floor rows above / below the box: CSM_LOW_PADY, or 1 with ROWCLAMP
+  // padded rows: [0, pady) floor, [pady, pady + th) box, [pady + th, th + 2 pady) floor;
+  // columns likewise with CSM_LOW_PADX
 };
 
 template <bool SMEM>
@@ -127,8 +128,7 @@ __device__ __forceinline__ double tab_load(const double* p) {
   return __ldg(p);
 }
 
-// The 7 consecutive values at cell index `cell` of the table.  Shared memory is
-// addressed by its 32-bit window address (tab_s), which spares the generic ->
+// Shared memory is addressed by its 32-bit window address, which spares the generic ->
 // shared conversion per access.
 template <int OFF>
 __device__ __forceinline__ double lds_f64(unsigned addr) {
@@ -137,18 +137,17 @@ __device__ __forceinline__ double lds_f64(unsigned addr) {
   return v;
 }
 
-// `base` = shared-window byte address (staged table) or unused; `cell` = index of
-// the first of the 7 cells.
+// The 7 consecutive values a lane adds for one run: `ad` = shared-window byte address
+// of the first (staged table), `gp` = its global address otherwise.
 template <bool SMEM>
-__device__ __forceinline__ void tab_load7(const double* tab, unsigned base, int cell, double* t) {
+__device__ __forceinline__ void tab_load7(const double* gp, unsigned ad, double* t) {
   static_assert(LS_IU == 7, "seven loads below");
   if (SMEM) {
-    const unsigned ad = base + (unsigned)cell * 8u;
     t[0] = lds_f64<0>(ad);  t[1] = lds_f64<8>(ad);  t[2] = lds_f64<16>(ad); t[3] = lds_f64<24>(ad);
     t[4] = lds_f64<32>(ad); t[5] = lds_f64<40>(ad); t[6] = lds_f64<48>(ad);
   } else {
 #pragma unroll
-    for (int u = 0; u < LS_IU; ++u) t[u] = __ldg(tab + cell + u);
+    for (int u = 0; u < LS_IU; ++u) t[u] = __ldg(gp + u);
   }
 }
 
@@ -160,29 +159,30 @@ __device__ __forceinline__ unsigned pinned(unsigned v) {
 }
 
 // The 7 table values of one lane for one (rotation, point), every cell looked up
-// on its own (cell_fast): the path of a point flagged LS_ODD.
+// on its own (cell_fast): the path of a point flagged LS_SLOW.
 template <bool SMEM>
 __device__ __noinline__ void low_patch_slow(const CellMap& cm, const float* s_tlow, const LowTab& lt,
                                             float2 q, int n_t, int jj, int i0, double* t) {
-  int row = lt.row_below;
+  int row = 0;  // padded row 0 reads the floor
   if (jj < n_t) {
     const int cg = cell_fast(cm, __fadd_rn(q.y, s_tlow[jj]));  // Vector2f(., y_trans)
     const int cy = cg - lt.oy;
-    row = cg < 0 ? lt.row_below : min(max(cy + 1, 0), lt.row_below);
+    if (cg >= 0 && (unsigned)cy < (unsigned)lt.th) row = cy + lt.pady;
   }
   const int ro = row * lt.ts;
 #pragma unroll
   for (int u = 0; u < LS_IU; ++u) {
-    int col = 0;  // column 0 reads the floor
+    int col = 0;  // padded column 0 reads the floor
     if (i0 + u < n_t) {
-      const int cx = cell_fast(cm, __fadd_rn(q.x, s_tlow[i0 + u])) - lt.ox;  // Vector2f(x_trans, .)
-      if ((unsigned)cx < (unsigned)lt.tw) col = cx + lt.xpad;
+      const int cg = cell_fast(cm, __fadd_rn(q.x, s_tlow[i0 + u]));  // Vector2f(x_trans, .)
+      const int cx = cg - lt.ox;
+      if (cg >= 0 && (unsigned)cx < (unsigned)lt.tw) col = cx + CSM_LOW_PADX;
     }
     t[u] = tab_load<SMEM>(lt.tab + ro + col);
   }
 }
 
-template <bool SMEM>
+template <bool SMEM, bool ROWCLAMP>
 __device__ __forceinline__ void low_score_rounds(
     const SearchGrid& sg, const CellMap& cm, const float* s_tlow, const LowTab lt,
     const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
@@ -191,19 +191,23 @@ __device__ __forceinline__ void low_score_rounds(
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
   const int lj = lane & 15, half = lane >> 4;
-  const int xshift = half ? 21 : 10;
-  const int ljc = lj - LS_YB + 1;  // row of a patch word = clamp(word row + ljc, floor row above, floor row below)
-  const unsigned above = lane == 31 ? 0u : ~((2u << lane) - 1u);  // lanes after this one
+  const unsigned above = lane == 31 ? 0u : ~((2u << lane) - 1u);     // lanes after this one
+  // this lane's cell within a patch: row lj, columns half * 7 .. half * 7 + 6
+  const int lane_cell = (ROWCLAMP ? 0 : lj * lt.ts) + half * LS_IU;
+  const unsigned lane_s = pinned(lt.tab_s + 8u * (unsigned)lane_cell);
+  const double* lane_g = lt.tab + lane_cell;
+  // clamps of a patch's first row / column: 0 and the maxima lie entirely in the padding
+  // (ROWCLAMP: rows are kept relative to LS_TJ rows above the box and clamped per lane)
+  const int r_max = lt.th + CSM_LOW_PADY, c_max = lt.tw + CSM_LOW_PADX;
+  const int r_off = CSM_LOW_PADY - lt.oy, c_off = CSM_LOW_PADX - lt.ox;
+  const int lane_row = lj - (CSM_LOW_PADY - 1);  // ROWCLAMP: staged row = clamp(first row + lane_row, 0, th + 1)
+  const int row_last = lt.th + 1;
 
   for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
     const int ti = tile % tiles_x, tj = tile / tiles_x;
     const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
     const int jj = tj * LS_TJ + lj;             // this lane's y translation
     const float ty0 = s_tlow[tj * LS_TJ], tx0 = s_tlow[ti * LS_TI];
-    const bool two = ti * LS_TI + LS_IU < n_t;  // the tile has a second group of x translations
-    const float tx1 = s_tlow[two ? ti * LS_TI + LS_IU : ti * LS_TI];
-    const int lane_cell = lj * lt.ts + (two ? half * LS_IU : 0);  // this lane's cell within an inner patch
-    const unsigned tab_s = pinned(lt.tab_s), lane_s = pinned(lt.tab_s + 8u * (unsigned)lane_cell);
     double rbest[LS_IU];  // best of this warp's rotations, which ascend: '>' keeps the earliest
     int rbest_rot[LS_IU];
 #pragma unroll
@@ -219,68 +223,51 @@ __device__ __forceinline__ void low_score_rounds(
 #pragma unroll 1
       for (int p0 = 0; p0 < n_pts; p0 += LS_PC) {
         const int pc = min(LS_PC, n_pts - p0);
-        // phase A (lane = point): the patch word of the point.  The translations
+        // phase A (lane = point): first cell of the point's patch.  The translations
         // step by exactly one cell, so when the first sum of an axis lies clear of a
-        // cell edge (cell_clear, margin SearchGrid::reg_eps proven on the host) the
-        // other translations hit the next cells.
-        unsigned word = LS_ODD, info = LS_SLOW;
+        // cell edge (cell_clear, margin SearchGrid::reg_eps proven on the host for the 16
+        // translations that follow) translation k hits cell + k on that axis.
+        unsigned info = LS_SLOW | (unsigned)lane;  // distinct per lane: a slow point is its own run
         if (lane < pc) {
           const float2 q = rotate_point(a[p0 + lane], rot.c, rot.s);
-          int cy0, cx0, cx1;
+          int cy0, cx0;
           bool ok = packable;
           ok = cell_clear(cm, __fadd_rn(q.y, ty0), sg.reg_eps, sg.reg_qmax, &cy0) && ok;
           ok = cell_clear(cm, __fadd_rn(q.x, tx0), sg.reg_eps, sg.reg_qmax, &cx0) && ok;
-          ok = cell_clear(cm, __fadd_rn(q.x, tx1), sg.reg_eps, sg.reg_qmax, &cx1) && ok;
           if (ok) {
-            // lane lj reads staged row r0 + lj clamped to the floor rows, so r0 only
-            // matters within [-16, th + 1]; columns c .. c+6 of the padded box, a
-            // window entirely outside moved onto the floor padding
-            const int r0 = cy0 - lt.oy + 1, ca = cx0 - lt.ox + lt.xpad, cb = cx1 - lt.ox + lt.xpad;
-            const int xmax = lt.tw + lt.xpad;
-            const int yb = max(-LS_TJ, min(r0, lt.row_below)) + LS_YB - 1;
-            const int xa = max(0, min(ca, xmax)), xb = max(0, min(cb, xmax));
-            word = (unsigned)yb | ((unsigned)xa << 10) | ((unsigned)xb << 21);
-            const bool rows_out = r0 + LS_TJ - 1 <= 0 || r0 >= lt.row_below;
-            const bool a_out = xa + LS_IU <= lt.xpad || xa >= xmax;
-            const bool b_out = xb + LS_IU <= lt.xpad || xb >= xmax;
-            const bool inner = r0 >= 0 && r0 + LS_TJ - 1 <= lt.row_below && ca == xa &&
-                               (two ? cb == ca + LS_IU && cb <= xmax : true);
-            info = rows_out || (a_out && b_out) ? LS_FLOOR
-                   : inner ? LS_INNER | (unsigned)(r0 * lt.ts + ca) : LS_EDGE;
+            const int r0 = max(0, min(cy0 + r_off, r_max));
+            const int c0 = max(0, min(cx0 + c_off, c_max));
+            info = ROWCLAMP ? (unsigned)r0 | ((unsigned)c0 << 10) : (unsigned)(r0 * lt.ts + c0);
           }
         }
         // run-length encode: a point whose patch equals the previous point's adds
         // the values already in registers.  Run starts come from a ballot; each start
-        // lane works out the length of its run; phase B fetches {kind, cell, length}
-        // of a run from its first lane by shuffle and steps from start to start.
-        const unsigned prevw = __shfl_up_sync(0xffffffffu, word, 1);
-        const unsigned starts = __ballot_sync(
-            0xffffffffu, lane < pc && (lane == 0 || word != prevw || word == LS_ODD));
+        // lane works out the length of its run; phase B fetches {patch, length} of a run
+        // from its first lane by shuffle and steps from start to start.
+        const unsigned prev = __shfl_up_sync(0xffffffffu, info, 1);
+        const unsigned starts = __ballot_sync(0xffffffffu, lane < pc && (lane == 0 || info != prev));
         {
           const unsigned later = starts & above;
           info |= (unsigned)((later ? __ffs(later) - 1 : pc) - lane) << 24;
         }
         // phase B (lane = candidate column): per run 7 consecutive cells, added once
         // per point of the run -- each sum still takes its terms in point order
-#if LS_PREF
-        unsigned inf = __shfl_sync(0xffffffffu, info, 0);
-#endif
 #pragma unroll 1
         for (int pl = 0; pl < pc;) {
-#if !LS_PREF
           const unsigned inf = __shfl_sync(0xffffffffu, info, pl);
-#endif
-          int c = (int)((inf >> 24) & 63u);  // points in the run
           double t[LS_IU];
-          if (inf < LS_FLOOR) {
-            tab_load7<SMEM>(lt.tab + lane_cell, lane_s, (int)(inf & 0xffffffu), t);
-          } else if (inf < LS_EDGE) {
-#pragma unroll
-            for (int u = 0; u < LS_IU; ++u) t[u] = CSM_FLOOR_LOG;
-          } else if (inf < LS_SLOW) {
-            const unsigned w = __shfl_sync(0xffffffffu, word, pl);
-            const int row = min(max((int)(w & 1023u) + ljc, 0), lt.row_below);
-            tab_load7<SMEM>(lt.tab, tab_s, row * lt.ts + (int)((w >> xshift) & 2047u), t);
+          int c = 1;
+          if ((int)inf >= 0) {
+            unsigned cell8;
+            if (ROWCLAMP) {
+              const int row = min(max((int)(inf & 1023u) + lane_row, 0), row_last);
+              cell8 = (unsigned)(row * lt.ts + (int)((inf >> 10) & 2047u)) << 3;
+            } else {
+              cell8 = (inf & LS_CELL_MASK) << 3;
+            }
+            tab_load7<SMEM>(reinterpret_cast<const double*>(reinterpret_cast<const char*>(lane_g) + cell8),
+                            lane_s + cell8, t);
+            c = (int)(inf >> 24);
           } else {
             double ts[LS_IU];  // (a local array: keeps t itself in registers)
             low_patch_slow<SMEM>(cm, s_tlow, lt, rotate_point(a[p0 + pl], rot.c, rot.s), n_t, jj, i0, ts);
@@ -288,11 +275,6 @@ __device__ __forceinline__ void low_score_rounds(
             for (int u = 0; u < LS_IU; ++u) t[u] = ts[u];
           }
           pl += c;
-#if LS_PREF
-          // the next run's descriptor travels while this run's adds issue
-          inf = __shfl_sync(0xffffffffu, info, pl & 31);
-#endif
-#if LS_RUNLOOP == 2
 #pragma unroll 1
           for (; c >= 2; c -= 2) {
 #pragma unroll
@@ -304,25 +286,6 @@ __device__ __forceinline__ void low_score_rounds(
 #pragma unroll
             for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
           }
-#else
-#pragma unroll 1
-          for (; c >= 4; c -= 4) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-              for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
-          }
-          if (c & 2) {
-#pragma unroll
-            for (int k = 0; k < 2; ++k)
-#pragma unroll
-              for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
-          }
-          if (c & 1) {
-#pragma unroll
-            for (int u = 0; u < LS_IU; ++u) acc[u] = __dadd_rn(acc[u], t[u]);
-          }
-#endif
         }
       }
 #pragma unroll
@@ -352,7 +315,7 @@ __device__ __forceinline__ void low_score_rounds(
   }
 }
 
-__global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
+__global__ void __launch_bounds__(LS_THREADS, LS_MINB_N) low_score_kernel(
     Geometry g, SearchGrid sg, CellMap cm_global, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
@@ -374,7 +337,6 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
   const int n_pts = (int)(offsets[pw.a_scan + 1] - offsets[pw.a_scan]);
   const TableMeta tm = metas[pw.table];
   const double* __restrict__ lowlog = slots[pw.table].lowlog;
-  const int lstride = lowlog_stride(g.wl);
 
   for (int k = threadIdx.x; k < g.wl + 1; k += LS_THREADS) s_thr[k] = cm_global.lowf[k];  // make_thresholds: dim + 1 entries
   for (int k = threadIdx.x; k < n_t; k += LS_THREADS) s_tlow[k] = sg.t_low[k];
@@ -392,27 +354,35 @@ __global__ void __launch_bounds__(LS_THREADS, 2) low_score_kernel(
   lt.th = empty ? 0 : tm.ly1 - tm.ly0 + 1;
   lt.ox = empty ? 0 : tm.lx0;
   lt.oy = empty ? 0 : tm.ly0;
-  const int ts = (lt.tw + 2 * LS_XPAD) | 1;  // odd stride: see the bank note above
-  const bool fits = ts * (lt.th + 2) <= table_cells && lt.th < 65533;
-  if (fits) {
-    // staged rows: 0 = floor, 1 .. th = box, th + 1 = floor
-    lt.tab = s_tab; lt.ts = ts; lt.xpad = LS_XPAD; lt.row_below = lt.th + 1;
+  const int ts = (lt.tw + 2 * CSM_LOW_PADX) | 1;  // odd stride: see the bank note above
+  const bool full_pad = (long long)ts * (lt.th + 2 * CSM_LOW_PADY) <= table_cells;
+  const bool one_pad = (long long)ts * (lt.th + 2) <= table_cells;
+  if (full_pad || one_pad) {
+    lt.tab = s_tab; lt.ts = ts; lt.pady = full_pad ? CSM_LOW_PADY : 1;
     lt.tab_s = (unsigned)__cvta_generic_to_shared(s_tab);
-    for (int k = threadIdx.x; k < ts * (lt.th + 2); k += LS_THREADS) {
-      const int r = k / ts - 1, c = k - (r + 1) * ts - LS_XPAD;
+    const int rows = lt.th + 2 * lt.pady;
+    const double* src = lowlog + lowlog_index(g.wl, lt.ox, lt.oy);  // box cell (0, 0)
+    const int lstride = lowlog_stride(g.wl);
+    for (int k = threadIdx.x; k < ts * rows; k += LS_THREADS) {
+      const int r = k / ts - lt.pady, c = k - (r + lt.pady) * ts - CSM_LOW_PADX;
       s_tab[k] = ((unsigned)r < (unsigned)lt.th && (unsigned)c < (unsigned)lt.tw)
-                     ? lowlog[(size_t)(lt.oy + r + 1) * lstride + lt.ox + c + CSM_LOW_PAD] : CSM_FLOOR_LOG;
+                     ? src[(size_t)r * lstride + c] : CSM_FLOOR_LOG;
     }
     __syncthreads();
-    low_score_rounds<true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
-                           s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
+    if (full_pad)
+      low_score_rounds<true, false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
+                                    s_best, s_best_rot, (long long)ts * rows <= (long long)LS_CELL_MASK);
+    else  // one floor row above and below: rows packed in 10 bits, columns in 11
+      low_score_rounds<true, true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
+                                   s_best, s_best_rot,
+                                   lt.th + 2 * CSM_LOW_PADY < 1024 && lt.tw + 2 * CSM_LOW_PADX < 2048);
   } else {
-    // whole table from global memory: lowlog has the same padded layout
-    lt.tab = lowlog; lt.tab_s = 0; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl; lt.ts = lstride;
-    lt.xpad = CSM_LOW_PAD; lt.row_below = g.wl + 1;
+    // whole table from global memory: lowlog has the fully padded layout
+    lt.tab = lowlog; lt.tab_s = 0; lt.ox = 0; lt.oy = 0; lt.tw = g.wl; lt.th = g.wl;
+    lt.ts = lowlog_stride(g.wl); lt.pady = CSM_LOW_PADY;
     __syncthreads();
-    low_score_rounds<false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
-                            s_best, s_best_rot, lt.th + LS_YB < 1023 && lt.tw + LS_XPAD < 2048);
+    low_score_rounds<false, false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
+                                   s_best, s_best_rot, lowlog_cells(g.wl) <= (size_t)LS_CELL_MASK);
   }
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {

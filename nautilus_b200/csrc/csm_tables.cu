@@ -76,14 +76,30 @@ __global__ void __launch_bounds__(256) raster_kernel(
     if (n == 0) {  // no point inside the grid: the table is all zeros
       m.cx0 = 0; m.cx1 = -1; m.cy0 = 0; m.cy1 = -1;
       m.ax0 = 0; m.ax1 = -1; m.ay0 = 0; m.ay1 = -1;
+      m.bx1 = -1; m.by1 = -1;
       m.stride = 0; m.cropped = 1;
     } else {
       m.cx0 = lo_x; m.cx1 = hi_x; m.cy0 = lo_y; m.cy1 = hi_y;
       if (g.margin < 0) {
         m.ax0 = 0; m.ax1 = g.w - 1; m.ay0 = 0; m.ay1 = g.w - 1;
+        m.bx1 = m.ax1; m.by1 = m.ay1;
       } else {
-        m.ax0 = max(0, lo_x - g.margin); m.ax1 = min(g.w - 1, hi_x + g.margin);
-        m.ay0 = max(0, lo_y - g.margin); m.ay1 = min(g.w - 1, hi_y + g.margin);
+        // The recursions run margin cells past the occupied box so that the anti-causal
+        // passes start from a negligible state.  What has to be STORED for matching is
+        // less: the blur's impulse response g is positive and decreasing, so a cell more
+        // than L cells outside the box holds at most n g(L) g(0) while the table maximum
+        // is at least g(0)^2 (a point's own cell): with n tail[L] <= 0.25e-10 (factor 4
+        // for the mirrored mass of a Neumann edge) it reads as the lookup floor, exactly
+        // as in the reference.  The top / left margins feed nothing (the causal passes
+        // start at the box), so they shrink to L outright; below / right only the stores do.
+        int keep = g.margin;
+        if (g.tight && g.tail) {
+          for (int d = 0; d <= g.margin; ++d)
+            if ((double)n * g.tail[d] <= 0.25e-10) { keep = d; break; }
+        }
+        m.ax0 = max(0, lo_x - keep); m.ax1 = min(g.w - 1, hi_x + keep);
+        m.ay0 = max(0, lo_y - keep); m.ay1 = min(g.w - 1, hi_y + keep);
+        m.bx1 = min(g.w - 1, hi_x + g.margin); m.by1 = min(g.w - 1, hi_y + g.margin);
       }
       m.cropped = !(m.ax0 == 0 && m.ay0 == 0 && m.ax1 == g.w - 1 && m.ay1 == g.w - 1);
       m.stride = (m.ax1 - m.ax0 + 1 + 3) & ~3;
@@ -101,7 +117,7 @@ __global__ void __launch_bounds__(256) raster_kernel(
   // the cells its windows reach.
   const double floor_log = CSM_FLOOR_LOG;
   for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
-  for (int i = threadIdx.x; i < (g.wl + 2) * lowlog_stride(g.wl); i += blockDim.x)
+  for (int i = threadIdx.x; i < (int)lowlog_cells(g.wl); i += blockDim.x)
     slot.lowlog[i] = floor_log;
   if (s_box[4] == 0) return;
 
@@ -450,8 +466,8 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     if ((bm[b >> 5] >> (b & 31)) & 1u) iplus = 1.0;
   }
 
-  // ---- causal pass, columns cx0 .. ax1: states only
-  const int n_fwd = m.ax1 - m.cx0 + 1;
+  // ---- causal pass, columns cx0 .. bx1: states only
+  const int n_fwd = m.bx1 - m.cx0 + 1;
   for (int c0 = 0, ci = 0; c0 < n_fwd; c0 += 32, ++ci) {
     ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
     const int nk = min(32, n_fwd - c0);
@@ -464,7 +480,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     }
   }
 
-  const bool at_edge = (m.ax1 == g.w - 1);
+  const bool at_edge = (m.bx1 == g.w - 1);
   double w0 = 0.0;
   if (at_edge) {
     double w1, w2;
@@ -474,9 +490,10 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     v1 = v2 = v3 = 0.0;
   }
 
-  // ---- anti-causal pass, columns ax1 .. ax0, chunks aligned to cx0
-  const int rel_hi = m.ax1 - m.cx0;
+  // ---- anti-causal pass, columns bx1 .. ax0 (stored from ax1 down), chunks aligned to cx0
+  const int rel_hi = m.bx1 - m.cx0;
   const int rel_lo = m.ax0 - m.cx0;
+  const int rel_st = m.ax1 - m.cx0;  // last stored column
   const int ch_hi = rel_hi >> 5;
   const int ch_lo = (rel_lo >= 0) ? (rel_lo >> 5) : -((-rel_lo + 31) >> 5);
   for (int ch = ch_hi; ch >= ch_lo; --ch) {
@@ -504,7 +521,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
       v3 = v2; v2 = v1; v1 = v0;
     }
     __syncwarp();
-    if (lane >= k_lo && lane <= k_hi) {
+    if (lane >= k_lo && lane <= k_hi && r0 + lane <= rel_st) {
       double* dst = base + (m.cx0 + r0 + lane - m.ax0);
       for (int rr = 0; rr < 32; ++rr)
         if ((mask >> rr) & 1u) st_gbl(dst + (size_t)rowidx[rr] * m.stride, tile[rr][lane]);
@@ -538,10 +555,10 @@ __device__ __forceinline__ void y_causal(double (&a)[YC], int nrow, double& v1, 
 }
 
 // Anti-causal steps over a[hi .. lo] (causal outputs in, final values stored to
-// p + u * stride); edge_u = index whose value is the Triggs w0 (state already
-// set), -1 when none.
+// p + u * stride for u <= hs); edge_u = index whose value is the Triggs w0 (state
+// already set), -1 when none.
 template <int YC, bool FULL, bool NEEDMIN>
-__device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int hi, int edge_u,
+__device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int hi, int hs, int edge_u,
                                              double w0, double* p, size_t stride, double sum,
                                              double& v1, double& v2, double& v3, double a1,
                                              double a2, double a3, double& vmax, double& vmin) {
@@ -555,7 +572,7 @@ __device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int 
         v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
         v3 = v2; v2 = v1; v1 = v0;
       }
-      st_gbl(p + (size_t)u * stride, v0);
+      if (FULL || u <= hs) st_gbl(p + (size_t)u * stride, v0);  // rows past ay1 are computed only
       vmax = v0 > vmax ? v0 : vmax;  // no NaNs here: a compare and a select instead of fmax
       if (NEEDMIN) vmin = v0 < vmin ? v0 : vmin;
     }
@@ -610,8 +627,9 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
       iplus = ld_gbl(colp + (size_t)(g.w - 1 - m.ay0) * stride);
 
-    // causal pass, rows cy0 .. ay1: states only
-    const int n_fwd = m.ay1 - m.cy0 + 1;
+    // causal pass, rows cy0 .. by1: states only
+    const int n_fwd = m.by1 - m.cy0 + 1;
+    const int rel_st = m.ay1 - m.cy0;  // last stored row
     const int nch = (n_fwd + YC - 1) / YC;
     {
       const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
@@ -626,7 +644,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
         else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
       }
     }
-    const bool at_edge = (m.ay1 == g.w - 1);
+    const bool at_edge = (m.by1 == g.w - 1);
     double w0 = 0.0;
     if (at_edge) {  // Triggs boundary at the grid edge
       double w1, w2;
@@ -654,17 +672,18 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
         for (int u = 0; u < YC; ++u) a[u] = 0.0;  // exact zeros above the box
       }
       const int lo = max(0, rel_lo - b0), hi = min(YC - 1, n_fwd - 1 - b0);
+      const int hs = min(hi, rel_st - b0);  // rows of this chunk that are stored: lo .. hs
       const bool last = at_edge && ch == nch - 1;  // the chunk that holds the grid's last row
-      if (lo == 0 && hi == YC - 1 && !last) {
+      if (lo == 0 && hs == YC - 1 && !last) {
         if (needmin)
-          y_anticausal<YC, true, true>(a, 0, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1, a2, a3,
-                                       vmax, vmin);
+          y_anticausal<YC, true, true>(a, 0, YC - 1, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1,
+                                       a2, a3, vmax, vmin);
         else
-          y_anticausal<YC, true, false>(a, 0, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1, a2,
-                                        a3, vmax, vmin);
+          y_anticausal<YC, true, false>(a, 0, YC - 1, YC - 1, -1, w0, p, stride, sum, v1, v2, v3, a1,
+                                        a2, a3, vmax, vmin);
       } else {
-        y_anticausal<YC, false, true>(a, lo, hi, last ? hi : -1, w0, p, stride, sum, v1, v2, v3, a1,
-                                      a2, a3, vmax, vmin);
+        y_anticausal<YC, false, true>(a, lo, hi, hs, last ? hi : -1, w0, p, stride, sum, v1, v2, v3,
+                                      a1, a2, a3, vmax, vmin);
       }
     }
   }
@@ -756,7 +775,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
     for (int c = cs; c <= ce; ++c) mx = fmax(mx, s_colmax[c - m.ax0]);
     slot.low[(size_t)dy * g.wl + dx] = mx;
     const bool above = mx > CSM_MIN_VALUE_FOR_LOOKUP;
-    slot.lowlog[(size_t)(dy + 1) * lowlog_stride(g.wl) + dx + CSM_LOW_PAD] = lookup_log(mx);
+    slot.lowlog[lowlog_index(g.wl, dx, dy)] = lookup_log(mx);
     if (above) { bx0 = min(bx0, dx); bx1 = max(bx1, dx); }
   }
   // box of low-res cells above the lookup floor (the search stages it in smem)
@@ -839,13 +858,21 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
                        TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
                        cudaStream_t stream, int* launches) {
   if (n_tables <= 0) return;
-  raster_kernel<<<n_tables, 256, 0, stream>>>(g, points, offsets, scan_ids, slots, metas);
-  dim3 gx((g.w + XP_WARPS * 32 - 1) / (XP_WARPS * 32), n_tables);
-  dim3 gy((g.w + YP_THREADS - 1) / YP_THREADS, n_tables);
   bool stored = false;
-  int np_threads = 128;  // 256 / 192 / 128 / 96 / 64 threads -> 10.24 / 10.30 / 10.04 / 10.24 / 10.59 ms table stage (r1)
 #ifdef NAUTILUS_CSM_TUNING
   stored = tuning_int("NAUTILUS_CSM_TABLE_STORED", 0) != 0;
+#endif
+  const bool checkpointed = g.w <= 32 * RC_MAXCH_LARGE && !stored;
+  Geometry gr = g;  // matching tables store only what can exceed the lookup floor
+  gr.tight = (store_log && checkpointed && g.margin >= 0 && g.tail) ? 1 : 0;
+#ifdef NAUTILUS_CSM_TUNING
+  if (tuning_int("NAUTILUS_CSM_TABLE_TIGHT", 1) == 0) gr.tight = 0;
+#endif
+  raster_kernel<<<n_tables, 256, 0, stream>>>(gr, points, offsets, scan_ids, slots, metas);
+  dim3 gx((g.w + XP_WARPS * 32 - 1) / (XP_WARPS * 32), n_tables);
+  dim3 gy((g.w + YP_THREADS - 1) / YP_THREADS, n_tables);
+  int np_threads = 128;  // 256 / 192 / 128 / 96 / 64 threads -> 10.24 / 10.30 / 10.04 / 10.24 / 10.59 ms table stage (r1)
+#ifdef NAUTILUS_CSM_TUNING
   np_threads = tuning_int("NAUTILUS_CSM_NP_THREADS", np_threads);
 #endif
   if (g.w <= 32 * RC_MAXCH_SMALL && !stored) {
