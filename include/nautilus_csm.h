@@ -250,6 +250,26 @@ int nautilus_csm_single_queue_stats(const NautilusCsm* h, int64_t* n_requests, i
 int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const float* b,
                              int64_t nb, int32_t dims, double rotation, float* out);
 
+/* The 2x2 form for a batch of pairs of uploaded scans, pair p at rotation[p]: what
+ * GetLocalUncertaintyStats (cc:375-398) asks for after its GetTransformation calls,
+ * for all comparison clouds at once - and for all base clouds of a bag at once, the way
+ * bag_avg_matcher.cc:104-141 loops.  Tables are built once per distinct target.
+ * out: 4 floats per pair, row-major. */
+int nautilus_csm_uncertainty_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
+                                   const double* rotation, int32_t n_pairs, float* out);
+
+/* The device part of GetLocalUncertaintyStats (cc:375-398) for host clouds: every
+ * comparison cloud is matched against the target cloud over the full rotation
+ * (GetTransformation(targetCloud, comparisonCloud), cc:384-385) and the 2x2 matrix is
+ * taken at the matched rotation (cc:386-387), all comparison clouds in two batched
+ * passes.  comp_offsets: n_comp + 1 entries, in points.  u_out: 4 floats per
+ * comparison cloud; theta_out (optional): the matched rotations.  The eigenvalue
+ * averages of cc:388-396 are left to the caller (the C++ shim uses Eigen like the
+ * reference).  Does not touch the uploaded scan set. */
+int nautilus_csm_local_uncertainty(NautilusCsm* h, const float* target_xy, int64_t n_target,
+                                   const float* comp_xy, const int64_t* comp_offsets,
+                                   int32_t n_comp, float* u_out, float* theta_out);
+
 /* The rotation window of the 5-argument GetTransformation (cc:247-264). */
 void nautilus_csm_rotation_window(double rot_a, double rot_b, double restriction,
                                   double* rot_min, double* rot_max);

@@ -61,7 +61,7 @@ EXPORTS = [
     "nautilus_csm_cell", "nautilus_csm_cell_fast", "nautilus_csm_upload_scans", "nautilus_csm_highres_table",
     "nautilus_csm_lowres_from_table", "nautilus_csm_build_tables",
     "nautilus_csm_match_batch", "nautilus_csm_copy_results_dev", "nautilus_csm_match", "nautilus_csm_rotation_window",
-    "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_regular_check",
+    "nautilus_csm_last_timings", "nautilus_csm_uncertainty", "nautilus_csm_uncertainty_batch", "nautilus_csm_local_uncertainty", "nautilus_csm_regular_check",
     "nautilus_nn_build", "nautilus_nn_build_begin", "nautilus_nn_pose_transform", "nautilus_nn_match_batch",
     "nautilus_nn_self_index", "nautilus_nn_last_stats",
     "nautilus_host_alloc", "nautilus_host_free",
@@ -172,6 +172,8 @@ def lib():
     L.nautilus_csm_rotation_window.argtypes = [d, d, d, C.POINTER(d), C.POINTER(d)]
     L.nautilus_csm_last_timings.argtypes = [vp, C.POINTER(Timings)]
     L.nautilus_csm_uncertainty.argtypes = [vp, vp, i64, vp, i64, i32, d, vp]
+    L.nautilus_csm_uncertainty_batch.argtypes = [vp, vp, vp, vp, i32, vp]
+    L.nautilus_csm_local_uncertainty.argtypes = [vp, vp, i64, vp, vp, i32, vp, vp]
     L.nautilus_csm_regular_check.argtypes = [vp, i64, u64, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     L.nautilus_host_alloc.argtypes = [u64, C.POINTER(vp)]
     L.nautilus_host_free.argtypes = [vp]

@@ -272,17 +272,30 @@ class CorrelativeScanMatcher {
       for (int j = 0; j < 2; ++j) u(i, j) = out[i * 2 + j];
     return u;
   }
-  // cc:375-398 (the per-cloud loop runs serially here: every call already fills the GPU)
+  // cc:375-398.  The reference loops over the comparison clouds (OpenMP); here all of
+  // them go to the device in two batched passes (every match, then every covariance),
+  // and the eigenvalue averages are taken on the host with Eigen as in cc:388-396.
   std::pair<double, double> GetLocalUncertaintyStats(
       const std::vector<std::vector<Eigen::Vector2f>>& comparisonClouds,
       const std::vector<Eigen::Vector2f> targetCloud) {
+    const size_t n = comparisonClouds.size();
+    std::vector<Eigen::Vector2f> all;
+    std::vector<int64_t> offs(n + 1, 0);
+    for (size_t i = 0; i < n; i++) {
+      all.insert(all.end(), comparisonClouds[i].begin(), comparisonClouds[i].end());
+      offs[i + 1] = (int64_t)all.size();
+    }
+    std::vector<float> u(4 * n);
+    nautilus_b200_detail::Check(
+        nautilus_csm_local_uncertainty(Handle(), Data(targetCloud), (int64_t)targetCloud.size(),
+                                       Data(all), offs.data(), (int32_t)n, u.data(), nullptr),
+        "GetLocalUncertaintyStats");
     double condition_avg = 0.0;
     double scale_avg = 0.0;
-    for (size_t i = 0; i < comparisonClouds.size(); i++) {
-      std::pair<double, std::pair<Eigen::Vector2f, float>> result =
-          GetTransformation(targetCloud, comparisonClouds[i]);
-      Eigen::Matrix2f uncertainty =
-          GetUncertaintyMatrix(targetCloud, comparisonClouds[i], result.second.second);
+    for (size_t i = 0; i < n; i++) {
+      Eigen::Matrix2f uncertainty;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) uncertainty(a, b) = u[4 * i + 2 * a + b];
       Eigen::EigenSolver<Eigen::Matrix2f> es(uncertainty);
       Eigen::Vector2f eigenvalues = es.eigenvalues().real();
       condition_avg += eigenvalues.maxCoeff() / eigenvalues.minCoeff();

@@ -1127,6 +1127,140 @@ int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const f
   return NAUTILUS_OK;
 }
 
+}  // extern "C"
+
+namespace {
+int uncertainty_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, const int32_t* b_ids,
+                           const double* rotation, int32_t n_pairs, float* out) {
+  if (n_pairs < 0) return fail(NAUTILUS_EINVAL, "n_pairs < 0");
+  if (n_pairs == 0) return NAUTILUS_OK;
+  if (!a_ids || !b_ids || !rotation || !out) return fail(NAUTILUS_EINVAL, "null argument");
+  if (ss.n == 0) return fail(NAUTILUS_ESTATE, "no scans uploaded");
+  if (h->grid_rc) return fail(h->grid_rc, h->grid_error);
+  CU_TRY(cudaSetDevice(h->device));
+  int rc = require_tiling(h);
+  if (rc) return rc;
+  const int n_t = h->grid.n_t, n_tr = n_t * n_t;
+  // distinct targets, ascending; pairs grouped by target (stable)
+  std::vector<int> tindex(ss.n, -1), targets;
+  for (int p = 0; p < n_pairs; ++p) {
+    if (a_ids[p] < 0 || a_ids[p] >= ss.n || b_ids[p] < 0 || b_ids[p] >= ss.n)
+      return fail(NAUTILUS_EINVAL, "scan id out of range");
+    if (ss.host_offsets[a_ids[p] + 1] == ss.host_offsets[a_ids[p]])
+      return fail(NAUTILUS_EEMPTY, "empty query cloud");
+    tindex[b_ids[p]] = 0;
+  }
+  for (int s = 0; s < ss.n; ++s)
+    if (tindex[s] == 0) { tindex[s] = (int)targets.size(); targets.push_back(s); }
+  const int n_targets = (int)targets.size();
+  if ((rc = ensure_slots(h, n_targets))) return rc;
+  const int wave_tables = std::min(h->n_slots, n_targets);
+  std::vector<int> first(n_targets + 1, 0);
+  for (int p = 0; p < n_pairs; ++p) ++first[tindex[b_ids[p]] + 1];
+  for (int t = 0; t < n_targets; ++t) first[t + 1] += first[t];
+  std::vector<PairWork> sorted(n_pairs);
+  std::vector<Rotation> rots(n_pairs);
+  {
+    std::vector<int> fill(first.begin(), first.end() - 1);
+    for (int p = 0; p < n_pairs; ++p) {
+      const int t = tindex[b_ids[p]];
+      const int k = fill[t]++;
+      PairWork& w = sorted[k];
+      w.a_scan = a_ids[p]; w.table = t % wave_tables; w.rot_begin = k; w.n_rot = 1;
+      w.out_index = p; w.pad = 0;
+      // MemoizeLowRes(rotation, rotation + EPSILON) (cc:341-343): the one rotation, as float
+      rots[k].theta = (float)rotation[p]; rots[k].c = cosf(rots[k].theta);
+      rots[k].s = sinf(rots[k].theta); rots[k].pad = 0.f;
+    }
+  }
+  int max_wave_pairs = 0;
+  for (int t0 = 0; t0 < n_targets; t0 += wave_tables)
+    max_wave_pairs = std::max(max_wave_pairs, first[std::min(n_targets, t0 + wave_tables)] - first[t0]);
+  SearchBuffers sb{};
+  sb.chunks_per_pair = 1;
+  sb.rot_per_chunk = low_score_warps();
+  if ((rc = h->chunk_best_dev.reserve((size_t)max_wave_pairs * n_tr))) return rc;
+  if ((rc = h->chunk_rot_dev.reserve((size_t)max_wave_pairs * n_tr))) return rc;
+  sb.chunk_best = h->chunk_best_dev.p;
+  sb.chunk_rot = h->chunk_rot_dev.p;
+  int table_cells = h->params.stage_cells > 0 ? h->params.stage_cells : 11776;
+  while (table_cells > 1024 && low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
+    table_cells -= 512;
+  if (low_score_smem_bytes(n_t, h->geo.wl, table_cells) > 220 * 1024)
+    return fail(NAUTILUS_EINVAL, "translation grid too large for shared memory");
+  if ((rc = h->table_scan_dev.reserve(n_targets))) return rc;
+  if ((rc = h->pairs_dev.reserve(n_pairs))) return rc;
+  if ((rc = h->rots_dev.reserve(n_pairs))) return rc;
+  if ((rc = h->dense_scratch.reserve((size_t)max_wave_pairs * n_tr + 2 * (size_t)n_pairs + 16))) return rc;
+  cudaStream_t st = h->stream;
+  CU_TRY(cudaMemcpyAsync(h->table_scan_dev.p, targets.data(), sizeof(int) * n_targets, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->pairs_dev.p, sorted.data(), sizeof(PairWork) * n_pairs, cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * n_pairs, cudaMemcpyHostToDevice, st));
+  double* costs = h->dense_scratch.p;
+  float* out_dev = reinterpret_cast<float*>(costs + (size_t)max_wave_pairs * n_tr);
+  for (int t0 = 0; t0 < n_targets; t0 += wave_tables) {
+    const int t1 = std::min(n_targets, t0 + wave_tables);
+    const int k0 = first[t0], k1 = first[t1];
+    launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0, h->slots_dev.p,
+                      h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, nullptr);
+    launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p, h->metas_dev.p,
+                     h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, table_cells, st);
+    launch_uncertainty_batch(h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p, h->metas_dev.p,
+                             h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb,
+                             log(1e-4) /* UNCERTAINTY_USELESS_THRESHOLD, cc:12 */, costs, out_dev, st);
+  }
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(out, out_dev, sizeof(float) * 4 * (size_t)n_pairs, cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  return NAUTILUS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int nautilus_csm_uncertainty_batch(NautilusCsm* h, const int32_t* a_ids, const int32_t* b_ids,
+                                   const double* rotation, int32_t n_pairs, float* out) {
+  if (!h) return fail(NAUTILUS_EINVAL, "null handle");
+  NAUTILUS_GUARD(h);
+  return uncertainty_batch_impl(h, h->user_scans, a_ids, b_ids, rotation, n_pairs, out);
+}
+
+int nautilus_csm_local_uncertainty(NautilusCsm* h, const float* target_xy, int64_t n_target,
+                                   const float* comp_xy, const int64_t* comp_offsets,
+                                   int32_t n_comp, float* u_out, float* theta_out) {
+  if (!h || !u_out) return fail(NAUTILUS_EINVAL, "null argument");
+  NAUTILUS_GUARD(h);
+  if (n_comp < 0 || n_target < 0 || (n_comp > 0 && !comp_offsets))
+    return fail(NAUTILUS_EINVAL, "bad cloud list");
+  if (n_comp == 0) return NAUTILUS_OK;
+  if (n_target == 0) return fail(NAUTILUS_EEMPTY, "empty query cloud: the reference does not terminate on it");
+  CU_TRY(cudaSetDevice(h->device));
+  // scan 0 = the target cloud (the query of every match, cc:384-385), 1.. = the comparison clouds
+  const int64_t n_cpts = comp_offsets[n_comp];
+  std::vector<float> xy((size_t)2 * (n_target + n_cpts));
+  memcpy(xy.data(), target_xy, sizeof(float) * 2 * n_target);
+  if (n_cpts) memcpy(xy.data() + 2 * n_target, comp_xy, sizeof(float) * 2 * n_cpts);
+  std::vector<int64_t> offs((size_t)n_comp + 2);
+  offs[0] = 0;
+  for (int k = 0; k <= n_comp; ++k) offs[k + 1] = n_target + comp_offsets[k];
+  int rc = upload_scan_set(h, h->tmp_scans, xy.data(), offs.data(), n_comp + 1);
+  if (rc) return rc;
+  std::vector<int32_t> a_ids(n_comp, 0), b_ids(n_comp);
+  std::vector<double> rmin(n_comp, 0.0), rmax(n_comp, 2 * M_PI), score(n_comp), rot(n_comp);
+  std::vector<float> x(n_comp), y(n_comp), th(n_comp);
+  for (int k = 0; k < n_comp; ++k) b_ids[k] = k + 1;
+  // GetTransformation(targetCloud, comparisonCloud) over the full rotation (cc:384-385) ...
+  rc = match_batch_impl(h, h->tmp_scans, a_ids.data(), b_ids.data(), rmin.data(), rmax.data(), n_comp,
+                        score.data(), x.data(), y.data(), th.data(), nullptr);
+  if (rc) return rc;
+  // ... then GetUncertaintyMatrix(targetCloud, comparisonCloud, result.second.second) (cc:386-387)
+  for (int k = 0; k < n_comp; ++k) rot[k] = (double)th[k];
+  rc = uncertainty_batch_impl(h, h->tmp_scans, a_ids.data(), b_ids.data(), rot.data(), n_comp, u_out);
+  if (rc) return rc;
+  if (theta_out) memcpy(theta_out, th.data(), sizeof(float) * n_comp);
+  return NAUTILUS_OK;
+}
+
 int nautilus_csm_highres_table(NautilusCsm* h, const float* xy, int64_t n_points, double* out_high,
                                double* out_low) {
   if (!h) return fail(NAUTILUS_EINVAL, "null handle");

@@ -134,4 +134,13 @@ void launch_uncertainty(const SearchGrid& sg, const CellMap& cm_high, const floa
                         double useless_threshold, double* costs, int dims, float* out,
                         cudaStream_t stream);
 
+// The 2x2 form for a batch of pairs, one rotation each (pairs[k].rot_begin), after
+// launch_low_score filled sb with chunks_per_pair chunks per pair: costs[n_pairs][n_t*n_t]
+// scratch, out = 4 floats per pair at pairs[k].out_index.
+void launch_uncertainty_batch(const SearchGrid& sg, const CellMap& cm_high, const float2* points,
+                              const long long* offsets, const TableSlot* slots,
+                              const TableMeta* metas, const PairWork* pairs, const Rotation* rots,
+                              int n_pairs, const SearchBuffers& sb, double useless_threshold,
+                              double* costs, float* out, cudaStream_t stream);
+
 }  // namespace csm

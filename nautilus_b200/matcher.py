@@ -180,19 +180,37 @@ class CorrelativeScanMatcher:
                                                ptr(out)))
         return out.reshape(dims, dims)
 
+    def uncertainty_batch(self, a_ids, b_ids, rotation) -> np.ndarray:
+        """2x2 GetUncertaintyMatrix of many pairs of uploaded scans, pair p at rotation[p]
+        (nautilus_csm_uncertainty_batch).  -> float32 [n, 2, 2]."""
+        a_ids = np.ascontiguousarray(a_ids, dtype=np.int32)
+        b_ids = np.ascontiguousarray(b_ids, dtype=np.int32)
+        rot = np.ascontiguousarray(rotation, dtype=np.float64)
+        out = np.zeros((len(a_ids), 2, 2), np.float32)
+        check(self._L.nautilus_csm_uncertainty_batch(self._h, ptr(a_ids), ptr(b_ids), ptr(rot),
+                                                     len(a_ids), ptr(out)))
+        return out
+
     def GetLocalUncertaintyStats(self, comparison_clouds, target_cloud):
         """cc:375-398: mean condition number and mean largest eigenvalue of the 2x2
-        covariance of target_cloud matched against every comparison cloud."""
+        covariance of target_cloud matched against every comparison cloud.  Two batch
+        calls (all matches, then all covariances) instead of the reference's loop."""
+        tgt = _cloud(target_cloud)
+        comps = [_cloud(c) for c in comparison_clouds]
+        n = len(comps)
+        offs = np.zeros(n + 1, np.int64)
+        offs[1:] = np.cumsum([len(c) for c in comps])
+        cxy = np.ascontiguousarray(np.concatenate(comps)) if n else np.zeros((0, 2), np.float32)
+        us = np.zeros((n, 2, 2), np.float32)
+        check(self._L.nautilus_csm_local_uncertainty(self._h, ptr(tgt), len(tgt), ptr(cxy), ptr(offs),
+                                                     n, ptr(us), None))
         cond, scale = 0.0, 0.0
-        for c in comparison_clouds:
-            res = self.GetTransformation(target_cloud, c)
-            u = self.GetUncertaintyMatrix(target_cloud, c, float(res[1][1])).astype(np.float64)
+        for u in us.astype(np.float64):
             tr, det = u[0, 0] + u[1, 1], u[0, 0] * u[1, 1] - u[0, 1] * u[1, 0]
             root = math.sqrt(max(tr * tr / 4.0 - det, 0.0))
             ev = np.asarray([tr / 2.0 + root, tr / 2.0 - root], np.float32)
             cond += float(ev.max() / ev.min())
             scale += float(ev.max())
-        n = len(comparison_clouds)
         return cond / n, scale / n
 
     # ---- batch API (new; what a batched SolveAutoLC would call) -------------

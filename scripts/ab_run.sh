@@ -1,5 +1,6 @@
-run() { # name lib stagecells
-  NAUTILUS_CSM_LIB=$2 python bench.py --steps 5 --no-cpu-baseline --stage-cells $3 > gpurun_out/ab_$1.json 2> gpurun_out/ab_$1.err
+# A/B runs on the GPU box (scratch helper)
+run() { # name lib
+  NAUTILUS_CSM_LIB=$2 python bench.py --steps 5 --no-cpu-baseline > gpurun_out/ab_$1.json 2> gpurun_out/ab_$1.err
   python - <<PY
 import json
 try:
@@ -9,9 +10,7 @@ except Exception as e:
     print("$1 failed", e, open("gpurun_out/ab_$1.err").read()[-400:])
 PY
 }
-python -m pytest tests/test_gpu_parity.py tests/test_gpu_wide.py -x -q -m gpu 2>&1 | tail -2
-run main "" 0
-run w10b3 nautilus_b200/lib/variants/w10b3.so 8600
-run w10b3_d nautilus_b200/lib/variants/w10b3.so 0
-run w16b2 nautilus_b200/lib/variants/w16b2.so 0
-run w8b4 nautilus_b200/lib/variants/w8b4.so 6400
+run main ""
+run w14b2 nautilus_b200/lib/variants/w14b2.so
+run w15b2 nautilus_b200/lib/variants/w15b2.so
+run w16b2 nautilus_b200/lib/variants/w16b2.so

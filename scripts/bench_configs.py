@@ -4,7 +4,7 @@ point-to-point NN path (configs[4]).  One JSON line per config, CUDA-event times
 from the library, the reference's CPU code (oracle/_ref) timed beside it on a
 bounded sample.  Usage (on a B200):
 
-  python scripts/bench_configs.py [tables] [wide] [solver] [nn] [frontend] [residuals] [--cpu]
+  python scripts/bench_configs.py [tables] [wide] [solver] [uncertainty] [nn] [frontend] [residuals] [--cpu]
 """
 import json
 import os
@@ -152,6 +152,55 @@ def bench_solver(cpu):
     return line
 
 
+def bench_uncertainty(cpu):
+    """bag_avg_matcher.cc:104-141's pattern: every base cloud against its previous clouds,
+    GetTransformation over the full rotation + the 2x2 GetUncertaintyMatrix at the matched
+    rotation (GetLocalUncertaintyStats, cc:375-398), as two batched device passes."""
+    n_scans, prev = 200, 10
+    xy, offs = synth.make_scan_set(n_scans, group=20, seed=7, trans_range=2.0, max_rot=0.3)
+    a_ids, b_ids = [], []
+    for s in range(n_scans):
+        g0 = (s // 20) * 20
+        for q in range(max(g0, s - prev), s):
+            a_ids.append(s); b_ids.append(q)
+    a_ids, b_ids = np.asarray(a_ids, np.int32), np.asarray(b_ids, np.int32)
+    m = CorrelativeScanMatcher(30, 2, 0.3, 0.03)
+    m.upload_scans(xy, offs)
+    m.match_batch(a_ids[:20], b_ids[:20], 0.0, 2 * np.pi)
+    t0 = time.perf_counter()
+    _, _, _, th = m.match_batch(a_ids, b_ids, 0.0, 2 * np.pi)
+    t1 = time.perf_counter()
+    us = m.uncertainty_batch(a_ids, b_ids, th.astype(np.float64))
+    t2 = time.perf_counter()
+    line = {"config": f"local uncertainty stats, bag_avg_matcher pattern: {n_scans} base clouds x <= {prev} "
+                      f"previous clouds = {len(a_ids)} pairs, full rotation + 2x2 covariance",
+            "metric": "pairs_per_sec", "value": len(a_ids) / (t2 - t0), "ms_match": 1e3 * (t1 - t0),
+            "ms_uncertainty": 1e3 * (t2 - t1), "n_pairs": int(len(a_ids))}
+    if cpu:
+        from concurrent.futures import ThreadPoolExecutor
+        from oracle import ref
+        rm = ref.RefMatcher(30, 2, 0.3, 0.03)
+        k = cores()
+        idx = np.linspace(0, len(a_ids) - 1, k).astype(np.int64)
+
+        def one(i):
+            a = xy[offs[a_ids[i]]:offs[a_ids[i] + 1]]
+            b = xy[offs[b_ids[i]]:offs[b_ids[i] + 1]]
+            r = rm.match(a, b)
+            return r[3], rm.uncertainty2(a, b, float(r[3]))
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(max_workers=k) as ex:
+            res = list(ex.map(one, idx))
+        secs = time.perf_counter() - t0
+        worst = max(float(np.abs(us[i] - u).max() / np.abs(u).max()) for i, (_, u) in zip(idx, res))
+        line["cpu_baseline"] = {"value": k / secs, "unit": "pairs/s", "cores": k, "kind": "reference",
+                                "sample": f"{k} pairs, one pair per thread, {secs:.1f} s",
+                                "rotations_identical_to_gpu": bool(all(np.float32(r) == th[i] for i, (r, _) in zip(idx, res))),
+                                "worst_matrix_rel_err": worst}
+    m.close()
+    return line
+
+
 def bench_nn(cpu):
     n_scans, window = 2000, 10
     xy, offs, poses = synth.make_scan_set(n_scans, group=40, seed=6, trans_range=4.0, max_rot=0.5,
@@ -291,10 +340,10 @@ def bench_residuals(cpu):
 
 
 def main():
-    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "solver", "nn", "frontend", "residuals"]
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["tables", "wide", "solver", "uncertainty", "nn", "frontend", "residuals"]
     cpu = "--cpu" in sys.argv
     for w in which:
-        out = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn, "solver": bench_solver,
+        out = {"tables": bench_tables, "wide": bench_wide, "nn": bench_nn, "solver": bench_solver, "uncertainty": bench_uncertainty,
                "frontend": bench_frontend, "residuals": bench_residuals}[w](cpu)
         for line in (out if isinstance(out, list) else [out]):
             print(json.dumps(line), flush=True)

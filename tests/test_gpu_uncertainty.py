@@ -67,3 +67,19 @@ def test_uncertainty_errors():
     with pytest.raises(CsmError):
         m.GetUncertaintyMatrix(np.zeros((0, 2), np.float32), np.ones((3, 2), np.float32), 0.0)
     m.close()
+
+
+def test_uncertainty_batch_equals_single(unc):
+    """nautilus_csm_uncertainty_batch over uploaded scans = the single-pair call, pair by
+    pair (same kernels' arithmetic, tables built once per target), incl. several table waves."""
+    xy, offs = synth.make_scan_set(12, group=4, seed=8, n_beams=360)
+    pa, pb = synth.make_pair_list(12, group=4)
+    rot = np.linspace(-0.4, 0.4, len(pa))
+    for max_tables in (0, 2):
+        m = CorrelativeScanMatcher(30, 2, 0.3, 0.03, max_tables=max_tables)
+        m.upload_scans(xy, offs)
+        got = m.uncertainty_batch(pa, pb, rot)
+        for k in range(0, len(pa), 5):
+            a, b = xy[offs[pa[k]]:offs[pa[k] + 1]], xy[offs[pb[k]]:offs[pb[k] + 1]]
+            assert np.array_equal(got[k], m.GetUncertaintyMatrix(a, b, float(rot[k]))), k
+        m.close()
