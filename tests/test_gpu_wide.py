@@ -44,10 +44,10 @@ def test_wide_quarter_degree_vs_oracle(g):
     step = np.pi / 720
     pm = port.PortMatcher(*g["params"], rot_step=step)
     n = len(g["match_1deg"])
+    clouds = [g[f"a_{k}"] for k in range(n)] + [g[f"b_{k}"] for k in range(n)]  # (npz reads are not thread-safe)
     with ThreadPoolExecutor(max_workers=n) as ex:  # ctypes releases the GIL
-        want = list(ex.map(lambda k: pm.match(g[f"a_{k}"], g[f"b_{k}"], -np.pi, np.pi,
+        want = list(ex.map(lambda k: pm.match(clouds[k], clouds[n + k], -np.pi, np.pi,
                                               with_stats=True), range(n)))
-    clouds = [g[f"a_{k}"] for k in range(n)] + [g[f"b_{k}"] for k in range(n)]
     offs = np.zeros(2 * n + 1, np.int64)
     offs[1:] = np.cumsum([len(c) for c in clouds])
     m = CorrelativeScanMatcher(*g["params"], rot_step=step)
