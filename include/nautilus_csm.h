@@ -154,6 +154,23 @@ int nautilus_csm_table_blur(double* values, uint64_t width, uint64_t height, dou
                             int32_t device);
 int nautilus_csm_table_normalize(double* values, uint64_t width, uint64_t height, int32_t device);
 
+/* No counterpart in the reference: added for
+ * callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  nautilus_csm_table_normalize's arithmetic on
+ * DEVICE buffers: values_dev -> out_dev (width x height doubles each, out_dev may equal
+ * values_dev), launched on `cuda_stream` (NULL = the default stream) of CUDA device
+ * `device`; asynchronous, the caller synchronises the stream.  Calls no cudaMalloc /
+ * cudaFree / stream creation: the min/max scratch is a static __device__ array
+ * (256 KB per GPU that loads the library, held until exit), which bounds the table at
+ * NAUTILUS_NOALLOC_MAX_CELLS cells; larger tables return NAUTILUS_EINVAL with a message
+ * naming the limit.  Every call on a device shares that array: calls that overlap on
+ * the GPU (different streams, no ordering between them) race; calls ordered on one
+ * stream, or by events, are safe, and nothing in the array has to be cleared between
+ * them (each call writes every slot it later reads). */
+#define NAUTILUS_NOALLOC_MAX_CELLS 67108864ULL
+int nautilus_csm_table_normalize_noalloc(const double* values_dev, double* out_dev, uint64_t width,
+                                         uint64_t height, int32_t device, void* cuda_stream);
+
 /* Builds (and discards) the tables of the given uploaded scans; the batch
  * form of the two calls above, used for the table-build configuration.
  * checksum (optional) receives the sum over all low-res tables. */

@@ -102,9 +102,127 @@ int close_image(DeviceImage& d, double* values, uint64_t w, uint64_t h) {
   return NAUTILUS_OK;
 }
 
+// ---- allocation-free normalize (no counterpart in the reference) ---------------------
+// For callers that cannot cudaMalloc (graph capture, serving loops): the min/max
+// scratch of normalize lives in a file-scope device array instead of a per-call
+// allocation.  One (max, min) pair per block of NA_CELLS_PER_BLOCK cells, so the array
+// bounds the table: NA_MAX_BLOCKS * NA_CELLS_PER_BLOCK = 67 108 864 cells (a 6000 x 6000
+// solver table is 36 000 000).  256 KB + 16 B per GPU that loads the library, held
+// until exit.  Every slot a launch reads was written by the same call (the pass-1 grid
+// writes slots [0, blocks), pass 2 reads exactly those), so nothing has to start at
+// zero and a smaller table after a larger one never sees the larger one's partials.
+constexpr int NA_CELLS_PER_BLOCK = 4096;
+constexpr int NA_MAX_BLOCKS = 16384;
+constexpr unsigned long long NA_MAX_CELLS = (unsigned long long)NA_CELLS_PER_BLOCK * NA_MAX_BLOCKS;
+// [2b] = max, [2b+1] = min of block b; the last two slots hold the table's (max, min)
+static __device__ __align__(256) double na_scratch[2 * NA_MAX_BLOCKS + 2];
+
+__global__ void __launch_bounds__(256) na_partial_kernel(const double* __restrict__ v, size_t n,
+                                                         double* __restrict__ part) {
+  __shared__ double s_mx[8], s_mn[8];
+  const size_t base = (size_t)blockIdx.x * NA_CELLS_PER_BLOCK;
+  const size_t end = base + NA_CELLS_PER_BLOCK < n ? base + NA_CELLS_PER_BLOCK : n;
+  double mx = -INFINITY, mn = INFINITY;
+  for (size_t i = base + threadIdx.x; i < end; i += 256) {
+    const double x = v[i];
+    mx = x > mx ? x : mx;
+    mn = x < mn ? x : mn;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0) { s_mx[threadIdx.x >> 5] = mx; s_mn[threadIdx.x >> 5] = mn; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < 8; ++k) { mx = fmax(mx, s_mx[k]); mn = fmin(mn, s_mn[k]); }
+    part[2 * blockIdx.x] = mx;
+    part[2 * blockIdx.x + 1] = mn;
+  }
+}
+
+// one block folds the partials of THIS call into the last two slots
+__global__ void __launch_bounds__(1024) na_final_kernel(double* __restrict__ part, int blocks) {
+  __shared__ double s_mx[32], s_mn[32];
+  double mx = -INFINITY, mn = INFINITY;
+  for (int b = threadIdx.x; b < blocks; b += 1024) {
+    mx = fmax(mx, part[2 * b]);
+    mn = fmin(mn, part[2 * b + 1]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0) { s_mx[threadIdx.x >> 5] = mx; s_mn[threadIdx.x >> 5] = mn; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < 32; ++k) { mx = fmax(mx, s_mx[k]); mn = fmin(mn, s_mn[k]); }
+    part[2 * NA_MAX_BLOCKS] = mx;
+    part[2 * NA_MAX_BLOCKS + 1] = mn;
+  }
+}
+
+// rescale_kernel's arithmetic, out of place (out may alias in)
+__global__ void __launch_bounds__(256) na_rescale_kernel(const double* __restrict__ in,
+                                                         double* __restrict__ out, size_t n,
+                                                         const double* __restrict__ part) {
+  const double M = part[2 * NA_MAX_BLOCKS], m = part[2 * NA_MAX_BLOCKS + 1];
+  const bool keep = (m == 0.0 && M == 1.0);
+  const double range = __dsub_rn(M, m);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const double x = in[i];
+    out[i] = keep ? x
+                  : (m == M) ? 0.0 : __dadd_rn(__dmul_rn(__ddiv_rn(__dsub_rn(x, m), range), 1.0), 0.0);
+  }
+}
+
+// Device address of na_scratch, looked up once per device with that device current
+// (in host code `na_scratch` is only the symbol's host-side stand-in).
+int na_scratch_ptr(int device, double** out) {
+  static std::mutex mu;
+  static double* ptr[64] = {};
+  if (device < 0 || device >= 64) return fail(NAUTILUS_EINVAL, "bad device ordinal");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[device]) {
+    double* p = nullptr;
+    CU_TRY(cudaGetSymbolAddress((void**)&p, na_scratch));
+    if (!p) return fail(NAUTILUS_ECUDA, "cudaGetSymbolAddress returned a null scratch address");
+    ptr[device] = p;
+  }
+  *out = ptr[device];
+  return NAUTILUS_OK;
+}
+
 }  // namespace
 
 extern "C" {
+
+int nautilus_csm_table_normalize_noalloc(const double* values_dev, double* out_dev, uint64_t width,
+                                         uint64_t height, int32_t device, void* cuda_stream) {
+  if (!values_dev || !out_dev || width == 0 || height == 0) return fail(NAUTILUS_EINVAL, "bad table");
+  if (width > NA_MAX_CELLS || height > NA_MAX_CELLS || width * height > NA_MAX_CELLS)
+    return fail(NAUTILUS_EINVAL,
+                "nautilus_csm_table_normalize_noalloc: table of " + std::to_string(width) + " x " +
+                    std::to_string(height) + " cells exceeds the static scratch's maximum of " +
+                    std::to_string(NA_MAX_CELLS) + " cells; use nautilus_csm_table_normalize");
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+    return fail(NAUTILUS_ECUDA, "no CUDA device (there is no CPU fallback)");
+  if (device < 0 || device >= n_dev) return fail(NAUTILUS_EINVAL, "bad device ordinal");
+  CU_TRY(cudaSetDevice(device));
+  double* scratch = nullptr;
+  int rc = na_scratch_ptr(device, &scratch);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const size_t n = (size_t)width * height;
+  const int blocks = (int)((n + NA_CELLS_PER_BLOCK - 1) / NA_CELLS_PER_BLOCK);
+  na_partial_kernel<<<blocks, 256, 0, st>>>(values_dev, n, scratch);
+  na_final_kernel<<<1, 1024, 0, st>>>(scratch, blocks);
+  const int rblocks = (int)std::min<size_t>(1184, (n + 255) / 256);
+  na_rescale_kernel<<<rblocks, 256, 0, st>>>(values_dev, out_dev, n, scratch);
+  CU_TRY(cudaGetLastError());
+  return NAUTILUS_OK;
+}
 
 int nautilus_csm_table_blur(double* values, uint64_t width, uint64_t height, double sigma,
                             int32_t device) {
