@@ -154,6 +154,15 @@ int nautilus_csm_table_blur(double* values, uint64_t width, uint64_t height, dou
                             int32_t device);
 int nautilus_csm_table_normalize(double* values, uint64_t width, uint64_t height, int32_t device);
 
+/* Self-check of the two arithmetic helpers of the table kernels (csm_common.cuh), like
+ * nautilus_csm_regular_check for the cell rule: the table-driven logarithm the kernels
+ * take of every cell above the lookup floor (cc:72 takes log() per lookup) against
+ * CUDA's log(), worst distance in units in the last place, and the reciprocal-based
+ * division of the normalisation (CImg.h:39515) against the IEEE division, number of
+ * quotients that differ, over n_samples seeded samples of the tables' value range. */
+int nautilus_csm_math_check(int64_t n_samples, uint64_t seed, int32_t device, int64_t* log_max_ulps,
+                            int64_t* div_mismatches);
+
 /* No counterpart in the reference: added for
  * callers that cannot allocate (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid cudaMalloc).  nautilus_csm_table_normalize's arithmetic on

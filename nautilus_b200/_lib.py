@@ -67,7 +67,7 @@ EXPORTS = [
     "nautilus_host_alloc", "nautilus_host_free",
     "nautilus_nn_upload_normals", "nautilus_nn_match_resident", "nautilus_residuals_eval_resident",
     "nautilus_csm_single_queue_stats", "nautilus_csm_table_blur", "nautilus_csm_table_normalize",
-    "nautilus_csm_table_normalize_noalloc",
+    "nautilus_csm_table_normalize_noalloc", "nautilus_csm_math_check",
     "nautilus_csm_partition", "nautilus_csm_pair_weights", "nautilus_csm_comm_unique_id",
     "nautilus_csm_comm_init", "nautilus_csm_comm_attach", "nautilus_csm_gather",
     "nautilus_csm_match_batch_sharded",
@@ -161,6 +161,7 @@ def lib():
     L.nautilus_csm_table_blur.argtypes = [vp, u64, u64, d, i32]
     L.nautilus_csm_table_normalize.argtypes = [vp, u64, u64, i32]
     L.nautilus_csm_table_normalize_noalloc.argtypes = [vp, vp, u64, u64, i32, vp]
+    L.nautilus_csm_math_check.argtypes = [i64, u64, i32, C.POINTER(i64), C.POINTER(i64)]
     L.nautilus_csm_partition.argtypes = [vp, vp, i32, i32, vp, vp]
     L.nautilus_csm_pair_weights.argtypes = [C.POINTER(Params), vp, vp, vp, vp, i32, vp]
     L.nautilus_csm_comm_unique_id.argtypes = [vp]

@@ -132,16 +132,25 @@ namespace {
 
 void free_slots(NautilusCsm* h) {
   cudaFree(h->slab_values); cudaFree(h->slab_bitmap); cudaFree(h->slab_rowflag);
-  cudaFree(h->slab_low); cudaFree(h->slab_lowlog);
+  cudaFree(h->slab_low); cudaFree(h->slab_lowlog); cudaFree(h->slab_ck);
   h->slab_values = nullptr; h->slab_bitmap = nullptr; h->slab_rowflag = nullptr;
-  h->slab_low = nullptr; h->slab_lowlog = nullptr;
+  h->slab_low = nullptr; h->slab_lowlog = nullptr; h->slab_ck = nullptr;
   h->n_slots = 0;
 }
 
-size_t slot_bytes(const Geometry& g) {
+// Whether the handle's matching tables can take the two-run y-pass (csm_tables.cu): only
+// then do the slots carry its checkpoint scratch.
+bool wants_ck(const NautilusCsm* h) {
+  return h->geo.margin >= 0 && h->geo.tail && table_two_run_supported(h->geo.w) &&
+         h->pool_dev.d.two_run_ok;
+}
+
+size_t slot_bytes(const NautilusCsm* h) {
+  const Geometry& g = h->geo;
   const size_t w = g.w, wl = g.wl;
   return sizeof(double) * ((w + 3) & ~(size_t)3) * w + sizeof(unsigned) * g.bm_stride * w + w +
-         sizeof(double) * (wl * wl + lowlog_cells((int)wl));
+         sizeof(double) * (wl * wl + lowlog_cells((int)wl)) +
+         (wants_ck(h) ? sizeof(double) * ck_doubles(w) : 0);
 }
 
 // Makes at least `want` table slots resident (bounded by params.max_tables and
@@ -152,7 +161,7 @@ int ensure_slots(NautilusCsm* h, int want) {
   if (std::max(1, std::min(want, cap)) <= h->n_slots) return NAUTILUS_OK;  // steady state: no driver query
   size_t free_b = 0, total_b = 0;
   CU_TRY(cudaMemGetInfo(&free_b, &total_b));
-  const size_t per = slot_bytes(g);
+  const size_t per = slot_bytes(h);
   const size_t have = (size_t)h->n_slots * per;
   const size_t budget = (free_b + have) / 2;  // leave half of what is free to the caller
   cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)cap, budget / per));
@@ -165,6 +174,8 @@ int ensure_slots(NautilusCsm* h, int want) {
   CU_TRY(cudaMalloc(&h->slab_rowflag, w * (size_t)want));
   CU_TRY(cudaMalloc(&h->slab_low, sizeof(double) * wl * wl * want));
   CU_TRY(cudaMalloc(&h->slab_lowlog, sizeof(double) * lowlog_cells((int)wl) * want));
+  const bool with_ck = wants_ck(h);
+  if (with_ck) CU_TRY(cudaMalloc(&h->slab_ck, sizeof(double) * ck_doubles(w) * want));
   h->slots_host.resize(want);
   for (int i = 0; i < want; ++i) {
     TableSlot& s = h->slots_host[i];
@@ -173,6 +184,7 @@ int ensure_slots(NautilusCsm* h, int want) {
     s.rowflag = h->slab_rowflag + w * (size_t)i;
     s.low = h->slab_low + wl * wl * (size_t)i;
     s.lowlog = h->slab_lowlog + lowlog_cells((int)wl) * (size_t)i;
+    s.ck = with_ck ? h->slab_ck + ck_doubles(w) * (size_t)i : nullptr;
   }
   int rc = h->slots_dev.reserve(want);
   if (rc) return rc;
@@ -701,7 +713,7 @@ int nautilus_internal_match_launch(NautilusCsm* h, ScanSet& ss, const int32_t* a
     CU_TRY(cudaEventRecord(evt(w, 0), tst));
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0,
                       h->slots_dev.p + base, h->metas_dev.p + base, h->pool_dev.d, t1 - t0, true,
-                      tst, &launches);
+                      tst, &launches, h->slab_ck != nullptr);
     CU_TRY(cudaEventRecord(evt(w, 1), tst));
     return NAUTILUS_OK;
   };
@@ -1113,7 +1125,7 @@ int nautilus_csm_uncertainty(NautilusCsm* h, const float* a, int64_t na, const f
   CU_TRY(cudaMemcpyAsync(h->rots_dev.p, rots.data(), sizeof(Rotation) * rots.size(),
                          cudaMemcpyHostToDevice, st));
   launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p, h->slots_dev.p,
-                    h->metas_dev.p, h->pool_dev.d, 1, true, st, nullptr);
+                    h->metas_dev.p, h->pool_dev.d, 1, true, st, nullptr, h->slab_ck != nullptr);
   launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p,
                    h->metas_dev.p, h->pairs_dev.p, h->rots_dev.p, 1, sb, table_cells, st);
   double* costs = h->dense_scratch.p;
@@ -1202,7 +1214,7 @@ int uncertainty_batch_impl(NautilusCsm* h, ScanSet& ss, const int32_t* a_ids, co
     const int t1 = std::min(n_targets, t0 + wave_tables);
     const int k0 = first[t0], k1 = first[t1];
     launch_table_wave(h->geo, h->vv, ss.points, ss.offsets, h->table_scan_dev.p + t0, h->slots_dev.p,
-                      h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, nullptr);
+                      h->metas_dev.p, h->pool_dev.d, t1 - t0, true, st, nullptr, h->slab_ck != nullptr);
     launch_low_score(h->geo, h->grid, h->cm_low, ss.points, ss.offsets, h->slots_dev.p, h->metas_dev.p,
                      h->pairs_dev.p + k0, h->rots_dev.p, k1 - k0, sb, table_cells, st);
     launch_uncertainty_batch(h->grid, h->cm_high, ss.points, ss.offsets, h->slots_dev.p, h->metas_dev.p,

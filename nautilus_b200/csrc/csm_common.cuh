@@ -19,9 +19,57 @@ namespace csm {
 // one constant everywhere so that every floor lookup adds the same bits.
 #define CSM_FLOOR_LOG (-23.025850929940457)
 
+// Natural logarithm for the table kernels, which take it once per cell above the lookup
+// floor (a third of a table): ~30 instructions instead of the ~65 of CUDA's log().
+// Table-driven like the log of current C libraries (128 intervals of the mantissa range
+// [0.6875, 1.375), z = x 2^-k, r = z / c_i - 1 by one FMA, |r| < 2^-7):
+//   log(x) = k ln2 + log(c_i) + (r - r^2/2 + ... + r^7/7)
+// with k ln2 + log(c_i) carried as a double-double, so the result is within 1 ulp like
+// log()'s (tests/test_gpu_log.py compares the two over the table's range).  Arguments near
+// 1, where the leading terms cancel, and anything not a positive normal number go to log().
+#include "log_table.inc"
+struct CsmLogEntry { double invc, logc_hi, logc_lo; };
+static __device__ const CsmLogEntry csm_log_table[128] = {CSM_LOG_TABLE};
+
+__device__ __forceinline__ double csm_log(double x) {
+  if (!(x >= 1e-300 && x < 0.9375)) return log(x);
+  const long long ix = __double_as_longlong(x);
+  const long long tmp = ix - 0x3fe6000000000000LL;
+  const int i = (int)(tmp >> 45) & 127;
+  const int k = (int)(tmp >> 52);  // arithmetic: floor
+  const double z = __longlong_as_double(ix - (tmp & (long long)0xfff0000000000000ULL));
+  const CsmLogEntry* e = csm_log_table + i;
+  const double invc = __ldg(&e->invc), lc_hi = __ldg(&e->logc_hi), lc_lo = __ldg(&e->logc_lo);
+  const double r = __fma_rn(z, invc, -1.0);
+  const double kd = (double)k;
+  const double t = __dmul_rn(kd, CSM_LN2_HI);           // exact: LN2_HI has 42 bits
+  const double w = __dadd_rn(t, lc_hi);
+  const double w_err = __dadd_rn(__dsub_rn(t, w), lc_hi);  // |t| >= |lc_hi| or t == 0
+  const double hi = __dadd_rn(w, r);
+  double lo = __dadd_rn(__dsub_rn(w, hi), r);             // |w| >= |r| below 0.9375
+  lo = __dadd_rn(lo, __dadd_rn(w_err, __fma_rn(kd, CSM_LN2_LO, lc_lo)));
+  const double r2 = __dmul_rn(r, r);
+  double p = __fma_rn(r, 1.0 / 7.0, -1.0 / 6.0);
+  p = __fma_rn(r, p, 1.0 / 5.0);
+  p = __fma_rn(r, p, -1.0 / 4.0);
+  p = __fma_rn(r, p, 1.0 / 3.0);
+  p = __fma_rn(r, p, -0.5);
+  return __dadd_rn(hi, __fma_rn(r2, p, lo));
+}
+
+// d / b for many d and one b (the normalisation divides a table by its range): with
+// binv = RN(1 / b), two residual corrections by FMA give the correctly rounded quotient
+// (Markstein: q1 is faithful, hence q2 = RN(q1 + rem binv) = RN(d / b)) in 5 operations
+// instead of the ~20 of a full division.  For normal d, b, d / b.
+__device__ __forceinline__ double div_by(double d, double b, double binv) {
+  const double q0 = __dmul_rn(d, binv);
+  const double q1 = __fma_rn(__fma_rn(-q0, b, d), binv, q0);
+  return __fma_rn(__fma_rn(-q1, b, d), binv, q1);
+}
+
 // log(GetPointValue) of a table cell value (h:51-59 + cc:72).
 __device__ __forceinline__ double lookup_log(double v) {
-  return v > CSM_MIN_VALUE_FOR_LOOKUP ? log(v) : CSM_FLOOR_LOG;
+  return v > CSM_MIN_VALUE_FOR_LOOKUP ? csm_log(v) : CSM_FLOOR_LOG;
 }
 
 // Floor padding of the pooled log table: a full tile of the low-res scorer (14 x
@@ -82,7 +130,15 @@ struct TableSlot {
                        // scorer reads: lowlog_rows(wl) rows of lowlog_stride(wl)
                        // doubles, cell (x, y) at lowlog_index(wl, x, y); the padding
                        // (CSM_LOW_PADX columns / CSM_LOW_PADY rows each side) holds the floor
+  double* ck;          // scratch of the two-run y-pass: causal states per 16-row chunk,
+                       // [chunk][3][column], ck_doubles(w) doubles; null when the grid takes
+                       // the stored kernels
 };
+
+// chunks of 16 rows + the final state, three doubles per column
+__host__ __device__ inline size_t ck_doubles(size_t w) {
+  return ((w + 15) / 16 + 1) * 3 * ((w + 3) & ~(size_t)3);
+}
 
 // Grid geometry shared by all kernels.
 struct Geometry {

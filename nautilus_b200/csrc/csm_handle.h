@@ -85,6 +85,9 @@ struct DevPool {
     CU_TRY(cudaMemcpy(d.e, h.e.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
     CU_TRY(cudaMemcpy(d.dst, h.dst.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
     CU_TRY(cudaMemcpy(d.win, h.win.data(), n, cudaMemcpyHostToDevice));
+    bool ok = h.tiles && n <= 1024;
+    for (int k = 0; ok && k < n; ++k) ok = h.e[k] - h.s[k] + 1 >= 8;
+    d.two_run_ok = ok ? 1 : 0;
     return NAUTILUS_OK;
   }
 };
@@ -218,6 +221,7 @@ struct NautilusCsm {
   unsigned char* slab_rowflag = nullptr;
   double* slab_low = nullptr;
   double* slab_lowlog = nullptr;
+  double* slab_ck = nullptr;  // y-pass checkpoints of the two-run table build (TableSlot::ck)
   DevBuf<double> tail_dev;  // Geometry::tail
   DevBuf<double> dense_scratch;
   DevBuf<double> scalar_scratch;

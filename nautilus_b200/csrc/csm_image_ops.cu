@@ -102,6 +102,37 @@ int close_image(DeviceImage& d, double* values, uint64_t w, uint64_t h) {
   return NAUTILUS_OK;
 }
 
+// ---- self-check of the table kernels' arithmetic helpers ------------------------------
+// csm_log against log() in units in the last place, div_by against __ddiv_rn bit for bit,
+// on seeded samples of the ranges the table kernels use (values in (1e-10, 1], ranges in
+// [1e-3, 1e3]).
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(256) math_check_kernel(long long n, unsigned long long seed,
+                                                         unsigned long long* __restrict__ out) {
+  unsigned long long worst = 0, bad_div = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const unsigned long long a = mix64(seed + 2 * (unsigned long long)i), b = mix64(seed + 2 * (unsigned long long)i + 1);
+    const double u = (double)(a >> 11) * 0x1p-53, v = (double)(b >> 11) * 0x1p-53;
+    const double x = exp(-23.02585092994046 * u);           // log-uniform in (1e-10, 1]
+    const double range = exp(13.815510557964274 * (v - 0.5));  // log-uniform in [1e-3, 1e3]
+    const double want = log(x), got = csm_log(x);
+    const long long wa = __double_as_longlong(want), ga = __double_as_longlong(got);
+    const unsigned long long ulps = (unsigned long long)(wa > ga ? wa - ga : ga - wa);  // same sign
+    worst = ulps > worst ? ulps : worst;
+    const double d = __dmul_rn(x, range);
+    if (__double_as_longlong(div_by(d, range, __ddiv_rn(1.0, range))) != __double_as_longlong(__ddiv_rn(d, range)))
+      ++bad_div;
+  }
+  atomicMax(&out[0], worst);
+  atomicAdd(&out[1], bad_div);
+}
+
 // ---- allocation-free normalize (no counterpart in the reference) ---------------------
 // For callers that cannot cudaMalloc (graph capture, serving loops): the min/max
 // scratch of normalize lives in a file-scope device array instead of a per-call
@@ -221,6 +252,27 @@ int nautilus_csm_table_normalize_noalloc(const double* values_dev, double* out_d
   const int rblocks = (int)std::min<size_t>(1184, (n + 255) / 256);
   na_rescale_kernel<<<rblocks, 256, 0, st>>>(values_dev, out_dev, n, scratch);
   CU_TRY(cudaGetLastError());
+  return NAUTILUS_OK;
+}
+
+int nautilus_csm_math_check(int64_t n_samples, uint64_t seed, int32_t device, int64_t* log_max_ulps,
+                            int64_t* div_mismatches) {
+  if (n_samples <= 0 || !log_max_ulps || !div_mismatches) return fail(NAUTILUS_EINVAL, "bad arguments");
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+    return fail(NAUTILUS_ECUDA, "no CUDA device (there is no CPU fallback)");
+  if (device < 0 || device >= n_dev) return fail(NAUTILUS_EINVAL, "bad device ordinal");
+  CU_TRY(cudaSetDevice(device));
+  unsigned long long* out = nullptr;
+  CU_TRY(cudaMalloc(&out, 2 * sizeof(unsigned long long)));
+  cudaMemset(out, 0, 2 * sizeof(unsigned long long));
+  math_check_kernel<<<1184, 256>>>((long long)n_samples, (unsigned long long)seed, out);
+  unsigned long long host[2] = {0, 0};
+  const cudaError_t e = cudaMemcpy(host, out, sizeof(host), cudaMemcpyDeviceToHost);
+  cudaFree(out);
+  if (e != cudaSuccess) return fail(NAUTILUS_ECUDA, std::string("math check: ") + cudaGetErrorString(e));
+  *log_max_ulps = (int64_t)host[0];
+  *div_mismatches = (int64_t)host[1];
   return NAUTILUS_OK;
 }
 

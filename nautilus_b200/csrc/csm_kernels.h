@@ -15,12 +15,15 @@ struct PoolListDev {
   int* dst;
   unsigned char* win;
   int n;
+  int two_run_ok;  // windows tile the axis, every one >= 8 cells, n <= 1024: ypass2_kernel applies
 };
 
 void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
                        TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
-                       cudaStream_t stream, int* launches);
+                       cudaStream_t stream, int* launches, bool has_ck = false);
+// grids the checkpointed (and therefore the two-run) table kernels cover
+bool table_two_run_supported(int w);
 void launch_pool_generic(const double* hi, int w, int h, const PoolListDev& px,
                          const PoolListDev& py, double* low, int wl, cudaStream_t stream);
 void launch_expand(const Geometry& g, const TableSlot* slots, const TableMeta* metas, int t,

@@ -698,6 +698,361 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
 }
 
 // ---------------------------------------------------------------------------
+// K2b'  two-run y-pass for matching tables (store_log, cropped or not, windows that
+// tile the axis).  The one-run form above writes the blurred values, and the normalise
+// pass then reads them back and writes their logs: 8 + 8 + 8 B per cell on top of the
+// y recursion's own reads.  The divisor of the normalisation is the maximum of the y-pass's
+// own output, so no single sweep can write final values; but a second RUN of the anti-causal
+// sweep can, and it costs less than the round trip:
+//   run 1 (YP2_MAX): causal sweep + anti-causal sweep as above, NOTHING stored but the
+//          causal checkpoints (global scratch, TableSlot::ck); tracks the table maximum
+//          and max-pools the raw values per low-res window (GetLookupTableLowRes,
+//          cc:32-48) with one atomicMax per (warp, window) on order-preserving keys -
+//          the maximum commutes with the monotone normalisation, as in
+//          normalize_pool_kernel.
+//   run 2 (YP2_LOG): rebuilds each chunk from run 1's checkpoints, repeats the
+//          anti-causal sweep (same operations, same operands: same bits) and stores
+//          lookup_log((v - m) / (M - m)) in place.
+// low_finalize_kernel then turns the pooled keys into low / lowlog.  Every stored value
+// is the one the one-run path + normalize_pool_kernel produce, bit for bit.
+// Measured (B200, 2 000 tables of the bench / 400 of the 0.01 m configuration): 9.05 ms
+// against 9.00 for the one-run path / 10.9 against 12.0, with 14.5 MB of DRAM traffic per
+// table instead of 19.1.  Not kept: the same two runs with every column streamed through
+// a cp.async ring in shared memory, 2 - 8 chunks deep (11.1 - 24.6 ms): the sweeps are
+// bound by instruction issue and the dependent fp64 chain at 4 - 5 warps per scheduler,
+// not by the latency of their loads, and the ring adds instructions while the shared
+// memory it takes removes warps.
+// ---------------------------------------------------------------------------
+
+// ck layout: [chunk][3][column], chunk nch = the causal sweep's final state
+__device__ __forceinline__ size_t ck_index(int chunk, int k, int col, int ckstride) {
+  return ((size_t)chunk * 3 + k) * (size_t)ckstride + col;
+}
+
+constexpr int YP2_MAX = 1, YP2_LOG = 2;
+constexpr int YP2_MAXWIN = 1024;  // pooling windows per axis the shared copies hold
+
+// Anti-causal steps over a[hi .. lo] (causal outputs in).  Run 1 folds the final values
+// into the maxima - the table's, and the pooling window's (rows <= hs; a window is
+// complete after its first row, bit u of wb, and moves to cap0, the one before to
+// cap1); run 2 leaves them in a[] for the normalising stores.
+template <int YC, int MODE, bool FULL, bool NEEDMIN>
+__device__ __forceinline__ void y2_anticausal(double (&a)[YC], int lo, int hi, int hs, int edge_u,
+                                              double w0, double sum, double& v1, double& v2,
+                                              double& v3, double a1, double a2, double a3,
+                                              double& vmax, double& vmin, double& dm, unsigned wb,
+                                              double& cap0, double& cap1) {
+#pragma unroll
+  for (int u = YC - 1; u >= 0; --u) {
+    if (FULL || (u >= lo && u <= hi)) {
+      double v0;
+      if (!FULL && u == edge_u) {
+        v0 = w0;
+      } else {
+        v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
+        v3 = v2; v2 = v1; v1 = v0;
+      }
+      if (MODE == YP2_MAX) {
+        vmax = v0 > vmax ? v0 : vmax;
+        if (NEEDMIN) vmin = v0 < vmin ? v0 : vmin;
+        if (FULL || u <= hs) {
+          dm = v0 > dm ? v0 : dm;
+          if ((wb >> u) & 1u) { cap1 = cap0; cap0 = dm; dm = -INFINITY; }
+        }
+      } else {
+        a[u] = v0;
+      }
+    }
+  }
+}
+
+template <int YC, int MINB, int MAXCH, int MODE>
+__global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
+    Geometry g, VanVliet f, const TableSlot* __restrict__ slots, TableMeta* __restrict__ metas,
+    const int* __restrict__ pool_s, const int* __restrict__ pool_dst,
+    const unsigned char* __restrict__ pool_win) {
+  const int t = blockIdx.y;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const int aw = m.ax1 - m.ax0 + 1;
+  if ((int)(blockIdx.x * YP_THREADS) >= aw) return;
+  const int col_raw = blockIdx.x * YP_THREADS + threadIdx.x;
+  const bool live = col_raw < aw;
+  // run 1 shuffles across the warp: a lane past the rectangle recomputes the last column
+  // (reads only) instead of leaving the loop
+  const int col = live ? col_raw : aw - 1;
+  const TableSlot slot = slots[t];
+  const double a1 = f.a1, a2 = f.a2, a3 = f.a3;
+  const double sum = __dmul_rn(f.B, f.B);
+  double* colp = slot.values + col;
+  double* ckp = slot.ck;
+  const int ckstride = m.stride;
+  const unsigned char* flag = slot.rowflag;
+  const size_t stride = (size_t)m.stride;
+  const int lane = threadIdx.x & 31;
+
+  __shared__ unsigned s_rows[MAXCH + 1];
+  __shared__ int s_ps[MODE == YP2_MAX ? YP2_MAXWIN : 1];
+  __shared__ int s_pd[MODE == YP2_MAX ? YP2_MAXWIN : 1];  // destination row, -1: window not pooled
+  __shared__ double s_out[MODE == YP2_LOG ? YC : 1][YP_THREADS];
+  {
+    const int rows = m.cy1 - m.cy0 + 1;
+    for (int w = threadIdx.x >> 5; w <= MAXCH; w += YP_THREADS / 32) {
+      const int r = w * 32 + lane;
+      const unsigned b = __ballot_sync(0xffffffffu, r < rows && flag[r] != 0);
+      if (lane == 0) s_rows[w] = b;
+    }
+    if (MODE == YP2_MAX)
+      for (int k = threadIdx.x; k < g.n_pool; k += YP_THREADS) {
+        s_ps[k] = pool_s[k];
+        s_pd[k] = pool_win[k] ? pool_dst[k] : -1;
+      }
+  }
+  __syncthreads();
+  if ((int)(blockIdx.x * YP_THREADS + (threadIdx.x & ~31)) >= aw) return;  // whole warp past the rectangle
+  constexpr unsigned CMASK = YC == 32 ? 0xffffffffu : ((1u << (YC & 31)) - 1u);
+
+  const int n_fwd = m.by1 - m.cy0 + 1;
+  const int rel_st = m.ay1 - m.cy0;  // last stored row
+  const int nch = (n_fwd + YC - 1) / YC;
+  const bool at_edge = (m.by1 == g.w - 1);
+  const int rel_lo = m.ay0 - m.cy0;  // <= 0
+  const int ch_lo = -((-rel_lo + YC - 1) / YC);
+
+  double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+  if (MODE == YP2_MAX) {
+    if (m.cy0 == 0 && flag[0]) {  // Neumann seed from grid row 0
+      const double x0 = ld_gbl(colp + (size_t)(0 - m.ay0) * stride);
+      v1 = v2 = v3 = __ddiv_rn(x0, f.B);
+    }
+    const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
+    for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
+      if (live) {
+        ckp[ck_index(ci, 0, col, ckstride)] = v1;
+        ckp[ck_index(ci, 1, col, ckstride)] = v2;
+        ckp[ck_index(ci, 2, col, ckstride)] = v3;
+      }
+      const int b0 = ci * YC;
+      const unsigned bits = (s_rows[b0 >> 5] >> (b0 & 31)) & CMASK;
+      double a[YC];
+      y_load<YC>(a, p, stride, bits);
+      const int nrow = n_fwd - b0;
+      if (nrow >= YC) y_causal<YC, true, false>(a, YC, v1, v2, v3, a1, a2, a3);
+      else y_causal<YC, false, false>(a, nrow, v1, v2, v3, a1, a2, a3);
+    }
+    if (live) {
+      ckp[ck_index(nch, 0, col, ckstride)] = v1;
+      ckp[ck_index(nch, 1, col, ckstride)] = v2;
+      ckp[ck_index(nch, 2, col, ckstride)] = v3;
+    }
+  } else {
+    v1 = ckp[ck_index(nch, 0, col, ckstride)];
+    v2 = ckp[ck_index(nch, 1, col, ckstride)];
+    v3 = ckp[ck_index(nch, 2, col, ckstride)];
+  }
+  double w0 = 0.0;
+  if (at_edge) {  // Triggs boundary at the grid edge
+    double iplus = 0.0;  // x-pass output on the grid's last row
+    if (m.cy1 == g.w - 1 && flag[m.cy1 - m.cy0])
+      iplus = ld_gbl(colp + (size_t)(g.w - 1 - m.ay0) * stride);
+    double w1, w2;
+    vv_triggs(f, iplus, v1, v2, v3, w0, w1, w2);
+    v1 = w0; v2 = w1; v3 = w2;
+  } else {
+    v1 = v2 = v3 = 0.0;
+  }
+
+  // ---- run 1: pooling state.  Columns: the window of this thread's column and which
+  // neighbours share it (segmented warp maximum); rows: the window of the row being
+  // walked, a window is flushed after its first row (rows descend).
+  int kx_dst = -1;
+  unsigned same = 0;  // bit j: lane + (1 << j) holds a column of the same window
+  bool head = false;
+  int ky = 0;
+  if (MODE == YP2_MAX) {
+    int lo = 0, hi = g.n_pool - 1;  // last window with pool_s <= column
+    const int cabs = m.ax0 + col;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_ps[mid] <= cabs) lo = mid; else hi = mid - 1;
+    }
+    const int kx = live ? lo : -1 - lane;  // lanes past the rectangle pool nothing
+    kx_dst = live ? s_pd[lo] : -1;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const int o = __shfl_down_sync(0xffffffffu, kx, 1 << j);
+      if (lane + (1 << j) < 32 && o == kx) same |= 1u << j;
+    }
+    const int prev = __shfl_up_sync(0xffffffffu, kx, 1);
+    head = lane == 0 || prev != kx;
+    lo = 0; hi = g.n_pool - 1;  // window of the last stored row
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_ps[mid] <= m.ay1) lo = mid; else hi = mid - 1;
+    }
+    ky = lo;
+  }
+  unsigned long long* lowkeys = reinterpret_cast<unsigned long long*>(slot.low);
+  auto flush = [&](double val, int kyw) {
+    const int dy = s_pd[kyw];
+    if (dy < 0) return;  // uniform
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const double o = __shfl_down_sync(0xffffffffu, val, 1 << j);
+      if ((same >> j) & 1u) val = o > val ? o : val;
+    }
+    if (head && kx_dst >= 0 && val > -INFINITY)
+      atomicMax(&lowkeys[(size_t)dy * g.wl + kx_dst], order_key(val));
+  };
+
+  // ---- run 2: normalisation constants
+  double mn = 0.0, range = 1.0, sub_floor = 0.0, rinv = 1.0;
+  bool constant = false;
+  if (MODE == YP2_LOG) {
+    const double M = key_to_double(m.max_key);
+    mn = m.cropped ? 0.0 : key_to_double(m.min_key);
+    constant = (M == mn);
+    range = __dsub_rn(M, mn);
+    sub_floor = __dmul_rn(range, CSM_MIN_VALUE_FOR_LOOKUP * (1.0 - 1e-9));
+    rinv = __ddiv_rn(1.0, range);
+  }
+
+  const bool needmin = !m.cropped;
+  double vmax = -INFINITY, vmin = INFINITY, dm = -INFINITY;
+  double* p = colp + (size_t)(m.cy0 + (nch - 1) * YC - m.ay0) * stride;
+  for (int ch = nch - 1; ch >= ch_lo; --ch, p -= (size_t)YC * stride) {
+    const int b0 = ch * YC;  // row of a[0] relative to cy0
+    double a[YC];
+    if (ch >= 0) {  // rebuild the chunk's causal outputs from its checkpoint
+      const unsigned bits = (s_rows[b0 >> 5] >> (b0 & 31)) & CMASK;
+      y_load<YC>(a, p, stride, bits);
+      double f1 = ckp[ck_index(ch, 0, col, ckstride)], f2 = ckp[ck_index(ch, 1, col, ckstride)],
+             f3 = ckp[ck_index(ch, 2, col, ckstride)];
+      const int nrow = n_fwd - b0;
+      if (nrow >= YC) y_causal<YC, true, true>(a, YC, f1, f2, f3, a1, a2, a3);
+      else y_causal<YC, false, true>(a, nrow, f1, f2, f3, a1, a2, a3);
+    } else {
+#pragma unroll
+      for (int u = 0; u < YC; ++u) a[u] = 0.0;  // exact zeros above the box
+    }
+    const int lo = max(0, rel_lo - b0), hi = min(YC - 1, n_fwd - 1 - b0);
+    const int hs = min(hi, rel_st - b0);  // rows of this chunk that are stored: lo .. hs
+    const int edge_u = (at_edge && ch == nch - 1) ? hi : -1;
+    // window starts among this chunk's rows (run 1): bit u = grid row cy0 + b0 + u starts a window
+    unsigned wb = 0;
+    if (MODE == YP2_MAX) {
+      const int r0 = m.cy0 + b0;
+      for (int k = ky; k >= 0 && s_ps[k] >= r0 + lo; --k)
+        if (s_ps[k] <= r0 + hs) wb |= 1u << (s_ps[k] - r0);
+    }
+    double cap0 = -INFINITY, cap1 = -INFINITY;
+    if (lo == 0 && hs == YC - 1 && edge_u < 0) {
+      if (needmin)
+        y2_anticausal<YC, MODE, true, true>(a, 0, YC - 1, YC - 1, -1, w0, sum, v1, v2, v3, a1, a2, a3,
+                                            vmax, vmin, dm, wb, cap0, cap1);
+      else
+        y2_anticausal<YC, MODE, true, false>(a, 0, YC - 1, YC - 1, -1, w0, sum, v1, v2, v3, a1, a2, a3,
+                                             vmax, vmin, dm, wb, cap0, cap1);
+    } else {
+      y2_anticausal<YC, MODE, false, true>(a, lo, hi, hs, edge_u, w0, sum, v1, v2, v3, a1, a2, a3, vmax,
+                                           vmin, dm, wb, cap0, cap1);
+    }
+    if (MODE == YP2_MAX) {
+      const int nb = __popc(wb);  // at most 2: windows are at least YC / 2 rows (host check)
+      if (nb == 2) { flush(cap1, ky); flush(cap0, ky - 1); }
+      else if (nb == 1) flush(cap0, ky);
+      ky -= nb;
+    } else {
+      // the divisions and logs run in a ROLLED loop over a shared copy of the chunk (a
+      // thread reads back its own words only): unrolled, the 16 inlined logs of the
+      // three sweep variants outgrow the instruction cache (ncu: no_instruction stalls)
+#pragma unroll
+      for (int u = 0; u < YC; ++u) s_out[u][threadIdx.x] = a[u];
+      if (live) {
+#pragma unroll 1
+        for (int u = lo; u <= hs; ++u) {
+          const double d = __dsub_rn(s_out[u][threadIdx.x], mn);
+          double out = CSM_FLOOR_LOG;
+          if (!(constant || d < sub_floor)) out = lookup_log(div_by(d, range, rinv));
+          st_gbl(p + (size_t)u * stride, out);
+        }
+      }
+    }
+  }
+  if (MODE == YP2_MAX) {
+    // the window cut by the rectangle's first row (nothing pending right after a flush)
+    if (ky >= 0 && __any_sync(0xffffffffu, dm > -INFINITY)) flush(dm, ky);
+    for (int o = 16; o > 0; o >>= 1) {
+      vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+      vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+    }
+    if (lane == 0 && vmax > -INFINITY) {
+      atomicMax(&metas[t].max_key, order_key(vmax));
+      if (needmin) atomicMin(&metas[t].min_key, order_key(vmin));
+    }
+  }
+}
+
+// Pooled keys -> low / lowlog (the tail of normalize_pool_kernel): one block per table,
+// over the windows that meet the stored rectangle.  A cell no column reached keeps its
+// 0.0 (bit pattern 0, below every key).
+__global__ void __launch_bounds__(256) low_finalize_kernel(
+    Geometry g, const TableSlot* __restrict__ slots, TableMeta* __restrict__ metas,
+    const int* __restrict__ pool_s, const int* __restrict__ pool_e,
+    const int* __restrict__ pool_dst, const unsigned char* __restrict__ pool_win) {
+  const int t = blockIdx.x;
+  const TableMeta m = metas[t];
+  if (m.cx1 < m.cx0) return;
+  const TableSlot slot = slots[t];
+  const double M = key_to_double(m.max_key);
+  const double mn = m.cropped ? 0.0 : key_to_double(m.min_key);
+  const bool constant = (M == mn);
+  const double range = __dsub_rn(M, mn);
+  // windows that meet the rectangle: [kx0, kx1] x [ky0, ky1] (the windows tile the axis)
+  __shared__ int s_k[4];
+  if (threadIdx.x < 4) {
+    const int target = threadIdx.x == 0 ? m.ax0 : threadIdx.x == 1 ? m.ax1 : threadIdx.x == 2 ? m.ay0 : m.ay1;
+    int lo = 0, hi = g.n_pool - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (pool_s[mid] <= target) lo = mid; else hi = mid - 1;
+    }
+    s_k[threadIdx.x] = lo;
+  }
+  __syncthreads();
+  const int kx0 = s_k[0], nx = s_k[1] - kx0 + 1, ky0 = s_k[2], ny = s_k[3] - ky0 + 1;
+  const unsigned long long* lowkeys = reinterpret_cast<const unsigned long long*>(slot.low);
+  int bx0 = INT_MAX, bx1 = INT_MIN, by0 = INT_MAX, by1 = INT_MIN;
+  for (int i = threadIdx.x; i < nx * ny; i += blockDim.x) {
+    const int kx = kx0 + i % nx, ky = ky0 + i / nx;
+    const int dx = pool_dst[kx], dy = pool_dst[ky];
+    if (!pool_win[kx] || !pool_win[ky] || dx < 0 || dy < 0) continue;
+    if (max(pool_s[kx], m.ax0) > min(pool_e[kx], m.ax1)) continue;
+    if (max(pool_s[ky], m.ay0) > min(pool_e[ky], m.ay1)) continue;
+    const size_t at = (size_t)dy * g.wl + dx;
+    const unsigned long long key = lowkeys[at];
+    double mx = 0.0;  // cells outside the grid (Dirichlet) / outside the rectangle
+    if (key != 0ULL && !constant) mx = fmax(mx, __ddiv_rn(__dsub_rn(key_to_double(key), mn), range));
+    slot.low[at] = mx;
+    slot.lowlog[lowlog_index(g.wl, dx, dy)] = lookup_log(mx);
+    if (mx > CSM_MIN_VALUE_FOR_LOOKUP) {
+      bx0 = min(bx0, dx); bx1 = max(bx1, dx);
+      by0 = min(by0, dy); by1 = max(by1, dy);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    bx0 = min(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+    bx1 = max(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+    by0 = min(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+    by1 = max(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+  }
+  if ((threadIdx.x & 31) == 0 && bx0 <= bx1) {
+    atomicMin(&metas[t].lx0, bx0); atomicMax(&metas[t].lx1, bx1);
+    atomicMin(&metas[t].ly0, by0); atomicMax(&metas[t].ly1, by1);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // K3+K4  normalise (CImg::normalize(0,1), CImg.h:39499-39517) fused with
 // GetLookupTableLowRes (CorrelativeScanMatcher.cc:32-48).
 //
@@ -739,6 +1094,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
   // below range * 1e-10 reads as the lookup floor without the division and the
   // log: d < range * 1e-10 * (1 - 1e-9) => d / range rounds to <= 1e-10.
   const double sub_floor = __dmul_rn(range, CSM_MIN_VALUE_FOR_LOOKUP * (1.0 - 1e-9));
+  const double rinv = constant ? 1.0 : __ddiv_rn(1.0, range);
   for (int c = threadIdx.x; c < aw; c += blockDim.x) {
     double dm = -INFINITY;
     double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
@@ -754,7 +1110,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
           // matching only ever needs log(GetPointValue): take it once per cell here
           // instead of once per (candidate, point) in the search
           double out;
-          if (store_log) out = (constant || d < sub_floor) ? CSM_FLOOR_LOG : lookup_log(__ddiv_rn(d, range));
+          if (store_log) out = (constant || d < sub_floor) ? CSM_FLOOR_LOG : lookup_log(div_by(d, range, rinv));
           else out = constant ? 0.0 : __ddiv_rn(d, range);
           st_gbl(p + (size_t)u * m.stride, out);
         }
@@ -853,10 +1209,12 @@ static int tuning_int(const char* name, int dflt) {
 }
 #endif
 
+bool table_two_run_supported(int w) { return w <= 32 * RC_MAXCH_LARGE; }
+
 void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* points,
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
                        TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
-                       cudaStream_t stream, int* launches) {
+                       cudaStream_t stream, int* launches, bool has_ck) {
   if (n_tables <= 0) return;
   bool stored = false;
 #ifdef NAUTILUS_CSM_TUNING
@@ -875,6 +1233,30 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
 #ifdef NAUTILUS_CSM_TUNING
   np_threads = tuning_int("NAUTILUS_CSM_NP_THREADS", np_threads);
 #endif
+  // matching tables: two-run y-pass instead of y-pass + normalise pass (see ypass2_kernel)
+  bool two_run = store_log && checkpointed && pool.two_run_ok && has_ck;
+#ifdef NAUTILUS_CSM_TUNING
+  if (tuning_int("NAUTILUS_CSM_TWO_RUN", 1) == 0) two_run = false;
+#endif
+  if (two_run) {
+    if (g.w <= 32 * RC_MAXCH_SMALL) {
+      xpass_kernel<RC_MAXCH_SMALL><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+      ypass2_kernel<16, 5, RC_MAXCH_SMALL, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
+          g, f, slots, metas, pool.s, pool.dst, pool.win);
+      ypass2_kernel<16, 5, RC_MAXCH_SMALL, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
+          g, f, slots, metas, pool.s, pool.dst, pool.win);
+    } else {
+      xpass_kernel<RC_MAXCH_LARGE><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
+      ypass2_kernel<16, 5, RC_MAXCH_LARGE, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
+          g, f, slots, metas, pool.s, pool.dst, pool.win);
+      ypass2_kernel<16, 5, RC_MAXCH_LARGE, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
+          g, f, slots, metas, pool.s, pool.dst, pool.win);
+    }
+    low_finalize_kernel<<<n_tables, 256, 0, stream>>>(g, slots, metas, pool.s, pool.e, pool.dst,
+                                                      pool.win);
+    if (launches) *launches += 5;
+    return;
+  }
   if (g.w <= 32 * RC_MAXCH_SMALL && !stored) {
     xpass_kernel<RC_MAXCH_SMALL><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
     ypass_kernel<16, 5, RC_MAXCH_SMALL><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
