@@ -17,7 +17,7 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libnautilus_csm_b200.so")
 SOURCES = ["csm_tables.cu", "csm_search.cu", "csm_capi.cu", "csm_comm.cu", "csm_image_ops.cu", "nn_kernels.cu", "nn_capi.cu", "csm_uncertainty.cu", "frontend.cu", "residuals.cu"]
-HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h")]
+HEADERS = ["csm_common.cuh", "csm_kernels.h", "csm_handle.h", "nn_kernels.h", os.path.join("..", "..", "include", "nautilus_csm.h"), "log_table.inc"]
 
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "--fmad=false", "-Xcompiler", "-fPIC", "-shared"]

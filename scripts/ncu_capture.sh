@@ -10,6 +10,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1
 # one launch of each kernel from the second (timed) step: skip the warm-up step's launches
 ncu --set full --clock-control none --import-source on \
-    -k regex:"raster_kernel|xpass_kernel|ypass_kernel|normalize_pool_kernel|low_score_kernel|refine_first_kernel|refine_spec_kernel|refine_finish_kernel" \
-    --launch-skip 8 --launch-count 8 -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
+    -k regex:"raster_kernel|xpass_kernel|ypass2_kernel|low_finalize_kernel|low_score_kernel|refine_first_kernel|refine_spec_kernel|refine_finish_kernel" \
+    --launch-skip 9 --launch-count 9 -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 ls -la gpurun_out/${TAG}_*

@@ -107,8 +107,12 @@ def main():
     # traffic.json is rewritten from THIS capture only (no stale kernels of older builds)
     n_tables = 400  # bench.py --scans 400: one table wave of 400 tables per launch
     tab = [k for k in traffic if any(t in k for t in ("raster_kernel", "xpass_kernel", "ypass_kernel",
+                                                      "ypass2_kernel", "low_finalize_kernel",
                                                       "normalize_pool_kernel"))]
-    norm = [k for k in traffic if "normalize_pool_kernel" in k]
+    # the kernel that writes every cell of every stored rectangle exactly once: the
+    # normalise pass (one-run path) or run 2 of the two-run y-pass (template MODE 2)
+    norm = [k for k in traffic if "normalize_pool_kernel" in k] or \
+           [k for k in traffic if "ypass2_kernel" in k and k.rstrip().endswith(", 2>")]
     low = [k for k in traffic if "low_score_kernel" in k]
     out = {"_source": f"{tag}: ncu --set full --clock-control none, one launch per kernel of "
                       f"`python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline` "
@@ -116,8 +120,7 @@ def main():
            "tables_per_launch": n_tables,
            "kernels_bytes_per_launch": {k: v["total"] for k, v in traffic.items()},
            "table_bytes_per_table": sum(traffic[k]["total"] for k in tab) / n_tables,
-           # every cell of every active rectangle is written exactly once by the normalise
-           # pass: its write bytes are the write-once minimum of this layout
+           # its write bytes are the write-once minimum of this layout
            "table_min_bytes_per_table": (traffic[norm[0]]["write"] / n_tables) if norm else None,
            "low_score_kernel_bytes_per_launch": traffic[low[0]]["total"] if low else None,
            "low_score_kernel_fp64_pipe_pct": traffic[low[0]]["fp64_pipe_pct"] if low else None}
