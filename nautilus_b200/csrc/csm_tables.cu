@@ -1234,9 +1234,17 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   np_threads = tuning_int("NAUTILUS_CSM_NP_THREADS", np_threads);
 #endif
   // matching tables: two-run y-pass instead of y-pass + normalise pass (see ypass2_kernel)
-  bool two_run = store_log && checkpointed && pool.two_run_ok && has_ck;
+  // It trades a longer dependent chain per column (five sweeps instead of three) for a
+  // quarter less DRAM traffic, which only pays when the wave fills the GPU several times
+  // over: measured equal at 1 000 tables of the 0.03 m grid, ahead beyond (2 000: 8.8
+  // against 9.0 ms; 400 tables of the 0.01 m grid, 9x the cells each: 10.7 against 12.0),
+  // behind below (250: 1.50 against 1.33 ms; a single table 0.67 against 0.50 ms per pair).
+  const double grid_cells = (double)n_tables * g.w * g.w;
+  bool two_run = store_log && checkpointed && pool.two_run_ok && has_ck && grid_cells >= 4.8e9;
 #ifdef NAUTILUS_CSM_TUNING
-  if (tuning_int("NAUTILUS_CSM_TWO_RUN", 1) == 0) two_run = false;
+  if (tuning_int("NAUTILUS_CSM_TWO_RUN", -1) == 0) two_run = false;
+  if (tuning_int("NAUTILUS_CSM_TWO_RUN", -1) == 1)
+    two_run = store_log && checkpointed && pool.two_run_ok && has_ck;
 #endif
   if (two_run) {
     if (g.w <= 32 * RC_MAXCH_SMALL) {

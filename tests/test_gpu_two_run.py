@@ -1,0 +1,106 @@
+"""The two-run table build (csm_tables.cu ypass2_kernel + low_finalize_kernel), which the
+library picks for waves that fill the GPU several times over (>= 1 200 tables of the
+0.03 m grid, >= 134 of the node's 0.01 m grid), against
+
+  * the reference's golden results (tests/golden/csm_golden.npz std pairs,
+    tests/golden/solver_golden.npz) for pairs placed inside such a wave, and
+  * the one-run path (small waves of the same scans): the two paths store the same
+    table bits, so scores, poses and search counters must be IDENTICAL, not just close.
+
+Fillers are rigid motions of the fixture clouds (cheap to make, distinct tables)."""
+import os
+
+import numpy as np
+import pytest
+
+from nautilus_b200 import CorrelativeScanMatcher
+
+pytestmark = pytest.mark.gpu
+REL = 1e-5
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def moved(cloud, ang, dx, dy):
+    c, s = np.cos(ang), np.sin(ang)
+    out = np.stack([c * cloud[:, 0] - s * cloud[:, 1] + dx, s * cloud[:, 0] + c * cloud[:, 1] + dy], 1)
+    return np.ascontiguousarray(out, np.float32)
+
+
+def scan_set(clouds):
+    offs = np.zeros(len(clouds) + 1, np.int64)
+    offs[1:] = np.cumsum([len(c) for c in clouds])
+    return np.ascontiguousarray(np.concatenate(clouds), np.float32), offs
+
+
+def run(params, clouds, pa, pb, rmin, rmax, chunk):
+    """match_batch over the pair list in slices of `chunk` pairs (one table wave each)"""
+    m = CorrelativeScanMatcher(*params)
+    xy, offs = scan_set(clouds)
+    m.upload_scans(xy, offs)
+    outs = []
+    for k0 in range(0, len(pa), chunk):
+        sl = slice(k0, k0 + chunk)
+        outs.append(m.match_batch(pa[sl], pb[sl], rmin[sl], rmax[sl], with_stats=True))
+    tm = m.last_timings()
+    m.close()
+    res = [np.concatenate([o[i] for o in outs]) for i in range(4)]
+    stats = np.concatenate([o[4] for o in outs])
+    return res, stats, tm
+
+
+def test_two_run_wave_vs_golden_and_one_run(golden):
+    params = tuple(golden["std_params"])
+    rows = golden["std_match"]
+    base = []
+    for k in range(len(rows)):
+        base += [golden[f"std_a_{k}"], golden[f"std_b_{k}"]]
+    rng = np.random.default_rng(77)
+    clouds = list(base)
+    n_fill = 1300
+    for i in range(n_fill):
+        src = base[int(rng.integers(0, len(base)))]
+        clouds.append(moved(src, rng.uniform(-0.3, 0.3), rng.uniform(-1.0, 1.0), rng.uniform(-1.0, 1.0)))
+    n_gold = len(rows)
+    pa = np.asarray([2 * k for k in range(n_gold)] + [int(rng.integers(0, len(clouds))) for _ in range(n_fill)], np.int32)
+    pb = np.asarray([2 * k + 1 for k in range(n_gold)] + list(range(len(base), len(base) + n_fill)), np.int32)
+    rmin, rmax = np.full(len(pa), -0.5), np.full(len(pa), 0.5)
+    big, big_stats, tm = run(params, clouds, pa, pb, rmin, rmax, chunk=len(pa))   # one wave of > 1 200 tables
+    for k, row in enumerate(rows):
+        assert (big[1][k], big[2][k], big[3][k]) == (row[1], row[2], row[3]), (k, row)
+        assert abs(big[0][k] - row[0]) <= REL * abs(row[0])
+    small, small_stats, tm_small = run(params, clouds, pa, pb, rmin, rmax, chunk=200)    # one-run waves
+    assert tm["launches"] == tm_small["launches"] + 1  # five table kernels instead of four
+    for i in range(4):
+        assert np.array_equal(big[i], small[i]), i
+    assert np.array_equal(big_stats, small_stats)
+
+
+def test_two_run_wave_on_the_solver_grid():
+    g = np.load(os.path.join(HERE, "golden", "solver_golden.npz"))
+    params = tuple(g["params"])
+    rows = g["match"]
+    base = []
+    for k in range(len(rows)):
+        base += [g[f"a_{k}"], g[f"b_{k}"]]
+    rng = np.random.default_rng(78)
+    clouds = list(base)
+    n_fill = 150  # >= 134 tables of the 6000-cell grid
+    for i in range(n_fill):
+        src = base[int(rng.integers(0, len(base)))]
+        clouds.append(moved(src, rng.uniform(-0.2, 0.2), rng.uniform(-0.5, 0.5), rng.uniform(-0.5, 0.5)))
+    n_gold = len(rows)
+    pa = np.asarray([2 * k for k in range(n_gold)] + [int(rng.integers(0, len(base))) for _ in range(n_fill)], np.int32)
+    pb = np.asarray([2 * k + 1 for k in range(n_gold)] + list(range(len(base), len(base) + n_fill)), np.int32)
+    m = CorrelativeScanMatcher(*params)
+    win = [m.rotation_window(r[0], r[1], float(g["restriction"])) for r in rows]
+    m.close()
+    rmin = np.asarray([w[0] for w in win] + [-0.3] * n_fill)
+    rmax = np.asarray([w[1] for w in win] + [0.3] * n_fill)
+    big, big_stats, _ = run(params, clouds, pa, pb, rmin, rmax, chunk=len(pa))
+    for k, row in enumerate(rows):
+        assert (big[1][k], big[2][k], big[3][k]) == (row[3], row[4], row[5]), (k, row)
+        assert abs(big[0][k] - row[2]) <= REL * abs(row[2])
+    small, small_stats, _ = run(params, clouds, pa, pb, rmin, rmax, chunk=40)
+    for i in range(4):
+        assert np.array_equal(big[i], small[i]), i
+    assert np.array_equal(big_stats, small_stats)
