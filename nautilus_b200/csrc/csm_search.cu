@@ -186,7 +186,7 @@ template <bool SMEM, bool ROWCLAMP>
 __device__ __forceinline__ void low_score_rounds(
     const SearchGrid& sg, const CellMap& cm, const float* s_tlow, const LowTab lt,
     const float2* __restrict__ a, int n_pts, const Rotation* __restrict__ rots, int rot0,
-    int rot1, double* s_best, int* s_best_rot, bool packable) {
+    int rot1, double* s_best, int* s_best_rot, int* s_next, bool packable) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = sg.n_t;
   const int tiles_x = (n_t + LS_TI - 1) / LS_TI, tiles_y = (n_t + LS_TJ - 1) / LS_TJ;
@@ -208,13 +208,22 @@ __device__ __forceinline__ void low_score_rounds(
     const int i0 = ti * LS_TI + half * LS_IU;   // this lane's first x translation
     const int jj = tj * LS_TJ + lj;             // this lane's y translation
     const float ty0 = s_tlow[tj * LS_TJ], tx0 = s_tlow[ti * LS_TI];
+    if (threadIdx.x == 0) *s_next = rot0;  // (the merge loop below ends on a barrier)
+    __syncthreads();
     double rbest[LS_IU];  // best of this warp's rotations, which ascend: '>' keeps the earliest
     int rbest_rot[LS_IU];
 #pragma unroll
     for (int u = 0; u < LS_IU; ++u) { rbest[u] = -INFINITY; rbest_rot[u] = 0; }
 
+    // Rotations are handed out by a shared counter instead of round-robin: a warp that
+    // falls behind (its scheduler's other warps sit in their add loops) takes fewer, and
+    // each warp's rotations still ascend, which is all the '>' below relies on.
 #pragma unroll 1
-    for (int r = rot0 + warp; r < rot1; r += LS_WARPS) {
+    for (;;) {
+      int r = 0;
+      if (lane == 0) r = atomicAdd(s_next, 1);
+      r = __shfl_sync(0xffffffffu, r, 0);
+      if (r >= rot1) break;
       const Rotation rot = rots[r];
       double acc[LS_IU];
 #pragma unroll
@@ -327,6 +336,7 @@ __global__ void __launch_bounds__(LS_THREADS, LS_MINB_N) low_score_kernel(
   const int n_t = sg.n_t, n_tr = n_t * n_t;
 
   extern __shared__ __align__(16) unsigned char s_raw[];
+  __shared__ int s_next;  // next rotation of the chunk to hand out
   double* s_tab = reinterpret_cast<double*>(s_raw);                  // [table_cells]
   double* s_best = s_tab + table_cells;                              // [n_tr]
   int* s_best_rot = reinterpret_cast<int*>(s_best + ((n_tr + 1) & ~1));  // [n_tr]
@@ -371,10 +381,10 @@ __global__ void __launch_bounds__(LS_THREADS, LS_MINB_N) low_score_kernel(
     __syncthreads();
     if (full_pad)
       low_score_rounds<true, false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
-                                    s_best, s_best_rot, (long long)ts * rows <= (long long)LS_CELL_MASK);
+                                    s_best, s_best_rot, &s_next, (long long)ts * rows <= (long long)LS_CELL_MASK);
     else  // one floor row above and below: rows packed in 10 bits, columns in 11
       low_score_rounds<true, true>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
-                                   s_best, s_best_rot,
+                                   s_best, s_best_rot, &s_next,
                                    lt.th + 2 * CSM_LOW_PADY < 1024 && lt.tw + 2 * CSM_LOW_PADX < 2048);
   } else {
     // whole table from global memory: lowlog has the fully padded layout
@@ -382,7 +392,7 @@ __global__ void __launch_bounds__(LS_THREADS, LS_MINB_N) low_score_kernel(
     lt.ts = lowlog_stride(g.wl); lt.pady = CSM_LOW_PADY;
     __syncthreads();
     low_score_rounds<false, false>(sg, cm, s_tlow, lt, a, n_pts, rots + pw.rot_begin, rot0, rot1,
-                                   s_best, s_best_rot, lowlog_cells(g.wl) <= (size_t)LS_CELL_MASK);
+                                   s_best, s_best_rot, &s_next, lowlog_cells(g.wl) <= (size_t)LS_CELL_MASK);
   }
   const size_t base = ((size_t)blockIdx.y * sb.chunks_per_pair + blockIdx.x) * n_tr;
   for (int tr = threadIdx.x; tr < n_tr; tr += LS_THREADS) {
