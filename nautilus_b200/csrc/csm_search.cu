@@ -79,8 +79,11 @@ __device__ __forceinline__ bool cell_clear(const CellMap& m, float v, float eps,
 // kernel is bound by the fp64 add pipe instead of shared-memory bandwidth.
 // A warp owns a rotation; the warps of a block take rotations round-robin.
 // ---------------------------------------------------------------------------
+// 16 warps x 2 blocks per SM = 64 registers per thread, which the kernel just fits without
+// spilling (18 warps: 56 registers, 200 B of spills).  With the rotations handed out by a
+// counter: 12 warps 11.87 ms, 16 warps 11.60 ms on the bench batch; wide search 899 / 790 ms.
 #ifndef LS_WARPS_N
-#define LS_WARPS_N 12
+#define LS_WARPS_N 16
 #endif
 #ifndef LS_MINB_N      // resident blocks per SM the register budget is set for
 #define LS_MINB_N 2
