@@ -730,6 +730,20 @@ __device__ __forceinline__ size_t ck_index(int chunk, int k, int col, int ckstri
 }
 
 constexpr int YP2_MAX = 1, YP2_LOG = 2;
+// Resident blocks per SM the two runs are compiled for.  Both fit 80 registers without
+// spilling (run 1 even 66); measured table stage of the bench, run 1 / run 2 at
+// 5/5, 6/5, 6/6, 7/6, 8/6 blocks: 8.65 / 8.49 / 8.27 / 8.26 / 8.24 ms.
+#ifndef YP2_MINB1_N
+#define YP2_MINB1_N 6
+#endif
+#ifndef YP2_MINB2_N
+#define YP2_MINB2_N 6
+#endif
+constexpr int YP2_MINB1 = YP2_MINB1_N, YP2_MINB2 = YP2_MINB2_N;
+#ifndef YP1_MINB_N    // the one-run y-pass (6 and 7 blocks measured: no gain)
+#define YP1_MINB_N 5
+#endif
+constexpr int YP1_MINB = YP1_MINB_N;
 constexpr int YP2_MAXWIN = 1024;  // pooling windows per axis the shared copies hold
 
 // Anti-causal steps over a[hi .. lo] (causal outputs in).  Run 1 folds the final values
@@ -753,7 +767,8 @@ __device__ __forceinline__ void y2_anticausal(double (&a)[YC], int lo, int hi, i
         v3 = v2; v2 = v1; v1 = v0;
       }
       if (MODE == YP2_MAX) {
-        vmax = v0 > vmax ? v0 : vmax;
+        // (the table maximum is folded from the window maxima at their flush: the rows
+        // past hs that take no part in them are below the lookup floor by construction)
         if (NEEDMIN) vmin = v0 < vmin ? v0 : vmin;
         if (FULL || u <= hs) {
           dm = v0 > dm ? v0 : dm;
@@ -893,7 +908,9 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
     ky = lo;
   }
   unsigned long long* lowkeys = reinterpret_cast<unsigned long long*>(slot.low);
+  double vmax = -INFINITY;
   auto flush = [&](double val, int kyw) {
+    vmax = val > vmax ? val : vmax;
     const int dy = s_pd[kyw];
     if (dy < 0) return;  // uniform
 #pragma unroll
@@ -918,7 +935,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
   }
 
   const bool needmin = !m.cropped;
-  double vmax = -INFINITY, vmin = INFINITY, dm = -INFINITY;
+  double vmin = INFINITY, dm = -INFINITY;
   double* p = colp + (size_t)(m.cy0 + (nch - 1) * YC - m.ay0) * stride;
   for (int ch = nch - 1; ch >= ch_lo; --ch, p -= (size_t)YC * stride) {
     const int b0 = ch * YC;  // row of a[0] relative to cy0
@@ -1249,15 +1266,15 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   if (two_run) {
     if (g.w <= 32 * RC_MAXCH_SMALL) {
       xpass_kernel<RC_MAXCH_SMALL><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
-      ypass2_kernel<16, 5, RC_MAXCH_SMALL, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
+      ypass2_kernel<16, YP2_MINB1, RC_MAXCH_SMALL, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
           g, f, slots, metas, pool.s, pool.dst, pool.win);
-      ypass2_kernel<16, 5, RC_MAXCH_SMALL, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
+      ypass2_kernel<16, YP2_MINB2, RC_MAXCH_SMALL, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
           g, f, slots, metas, pool.s, pool.dst, pool.win);
     } else {
       xpass_kernel<RC_MAXCH_LARGE><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
-      ypass2_kernel<16, 5, RC_MAXCH_LARGE, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
+      ypass2_kernel<16, YP2_MINB1, RC_MAXCH_LARGE, YP2_MAX><<<gy, YP_THREADS, 0, stream>>>(
           g, f, slots, metas, pool.s, pool.dst, pool.win);
-      ypass2_kernel<16, 5, RC_MAXCH_LARGE, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
+      ypass2_kernel<16, YP2_MINB2, RC_MAXCH_LARGE, YP2_LOG><<<gy, YP_THREADS, 0, stream>>>(
           g, f, slots, metas, pool.s, pool.dst, pool.win);
     }
     low_finalize_kernel<<<n_tables, 256, 0, stream>>>(g, slots, metas, pool.s, pool.e, pool.dst,
@@ -1267,10 +1284,10 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
   }
   if (g.w <= 32 * RC_MAXCH_SMALL && !stored) {
     xpass_kernel<RC_MAXCH_SMALL><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
-    ypass_kernel<16, 5, RC_MAXCH_SMALL><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+    ypass_kernel<16, YP1_MINB, RC_MAXCH_SMALL><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   } else if (g.w <= 32 * RC_MAXCH_LARGE && !stored) {
     xpass_kernel<RC_MAXCH_LARGE><<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
-    ypass_kernel<16, 5, RC_MAXCH_LARGE><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
+    ypass_kernel<16, YP1_MINB, RC_MAXCH_LARGE><<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
   } else {
     xpass_stored_kernel<<<gx, XP_WARPS * 32, 0, stream>>>(g, f, slots, metas);
     ypass_stored_kernel<<<gy, YP_THREADS, 0, stream>>>(g, f, slots, metas);
