@@ -192,6 +192,8 @@ int ensure_slots(NautilusCsm* h, int want) {
   if (rc) return rc;
   CU_TRY(cudaMemcpy(h->slots_dev.p, h->slots_host.data(), sizeof(TableSlot) * want,
                     cudaMemcpyHostToDevice));
+  launch_slot_init(g, h->slots_dev.p, h->metas_dev.p, want, nullptr);
+  CU_TRY(cudaDeviceSynchronize());  // (allocation path only) before any stream of the handle uses the slots
   h->n_slots = want;
   return NAUTILUS_OK;
 }

@@ -22,6 +22,10 @@ void launch_table_wave(const Geometry& g, const VanVliet& f, const float2* point
                        const long long* offsets, const int* scan_ids, TableSlot* slots,
                        TableMeta* metas, const PoolListDev& pool, int n_tables, bool store_log,
                        cudaStream_t stream, int* launches, bool has_ck = false);
+// Must run once over freshly allocated slots: the raster kernel only clears what the
+// slot's previous table wrote into the low-res arrays.
+void launch_slot_init(const Geometry& g, const TableSlot* slots, TableMeta* metas, int n_slots,
+                      cudaStream_t stream);
 // grids the checkpointed (and therefore the two-run) table kernels cover
 bool table_two_run_supported(int w);
 void launch_pool_generic(const double* hi, int w, int h, const PoolListDev& px,

@@ -445,6 +445,26 @@ void launch_low_score(const Geometry& g, const SearchGrid& sg, const CellMap& cm
 // one-kernel form.
 // ---------------------------------------------------------------------------
 constexpr int RF_THREADS = 128;
+// Resident blocks per SM the refine kernels are compiled for (0: left to the compiler:
+// 77 / 80 registers, 6 blocks).  Measured refine stage, bench batch / 0.01 m configuration:
+// first 8: 3.85 / 11.65 ms; spec 8: 3.80 / 11.98; both 8: 3.70 / 11.96; neither: 3.95 / 11.69.
+// The 30 x 30 windows of the 0.01 m grid want the registers, the 10 x 10 ones the warps.
+#ifndef RF_MINB_FIRST
+#define RF_MINB_FIRST 8
+#endif
+#ifndef RF_MINB_SPEC
+#define RF_MINB_SPEC 0
+#endif
+#if RF_MINB_FIRST > 0
+#define RF_BOUNDS_FIRST __launch_bounds__(RF_THREADS, RF_MINB_FIRST)
+#else
+#define RF_BOUNDS_FIRST __launch_bounds__(RF_THREADS)
+#endif
+#if RF_MINB_SPEC > 0
+#define RF_BOUNDS_SPEC __launch_bounds__(RF_THREADS, RF_MINB_SPEC)
+#else
+#define RF_BOUNDS_SPEC __launch_bounds__(RF_THREADS)
+#endif
 constexpr int RF_POINT_CHUNK = 1024;  // points whose window words are staged at a time
 #ifndef RF_DEPTH_N
 #define RF_DEPTH_N 2
@@ -743,7 +763,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(
 
 // --- speculative form --------------------------------------------------------
 
-__global__ void __launch_bounds__(RF_THREADS) refine_first_kernel(
+__global__ void RF_BOUNDS_FIRST refine_first_kernel(
     Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
@@ -821,7 +841,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_first_kernel(
   }
 }
 
-__global__ void __launch_bounds__(RF_THREADS) refine_spec_kernel(
+__global__ void RF_BOUNDS_SPEC refine_spec_kernel(
     Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,

@@ -38,6 +38,13 @@ __global__ void __launch_bounds__(256) raster_kernel(
   const TableSlot slot = slots[t];
   __shared__ int s_red[4][8];
   __shared__ int s_box[5];
+  __shared__ int s_oldrect[4];  // stored rectangle of the table this slot held before
+  if (threadIdx.x == 0) {
+    const TableMeta old = metas[t];  // (slot_init_kernel made it "empty" at allocation)
+    const bool had = old.cx1 >= old.cx0;
+    s_oldrect[0] = had ? old.ax0 : 0; s_oldrect[1] = had ? old.ax1 : -1;
+    s_oldrect[2] = had ? old.ay0 : 0; s_oldrect[3] = had ? old.ay1 : -1;
+  }
 
   int lo_x = INT_MAX, hi_x = INT_MIN, lo_y = INT_MAX, hi_y = INT_MIN, cnt = 0;
   for (long long i = p0 + threadIdx.x; i < p1; i += blockDim.x) {
@@ -113,12 +120,28 @@ __global__ void __launch_bounds__(256) raster_kernel(
   __syncthreads();
   const int cx0 = s_box[0], cx1 = s_box[1], cy0 = s_box[2], cy1 = s_box[3];
 
-  // low-res tables start as "all zero" / "all floor"; the pool kernel fills
-  // the cells its windows reach.
-  const double floor_log = CSM_FLOOR_LOG;
-  for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
-  for (int i = threadIdx.x; i < (int)lowlog_cells(g.wl); i += blockDim.x)
-    slot.lowlog[i] = floor_log;
+  // Low-res tables start as "all zero" / "all floor"; the pool kernels fill the cells
+  // whose windows meet the stored rectangle.  The slot was all zero / all floor when it
+  // was allocated (slot_init_kernel), so only what the PREVIOUS table of this slot wrote
+  // has to be cleared: the low-res cells of the windows that met its rectangle.  A window
+  // that holds hi-res cell c lands within two low-res cells of c's own (its first
+  // coordinate lies less than low_res + high_res before c's); three are cleared.
+  if (s_oldrect[1] >= s_oldrect[0] && s_oldrect[3] >= s_oldrect[2]) {
+    const double ratio = g.res_h / g.res_l;
+    auto low_of = [&](int c, int pad) {
+      const int v = (int)floor(((double)c - 0.5 * g.w) * ratio) + g.wl / 2 + pad;
+      return max(0, min(g.wl - 1, v));
+    };
+    const int x0 = low_of(s_oldrect[0] - 1, -3), x1 = low_of(s_oldrect[1] + 1, 3);
+    const int y0 = low_of(s_oldrect[2] - 1, -3), y1 = low_of(s_oldrect[3] + 1, 3);
+    const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
+    const double floor_log = CSM_FLOOR_LOG;
+    for (int i = threadIdx.x; i < nx * ny; i += blockDim.x) {
+      const int x = x0 + i % nx, y = y0 + i / nx;
+      slot.low[(size_t)y * g.wl + x] = 0.0;
+      slot.lowlog[lowlog_index(g.wl, x, y)] = floor_log;
+    }
+  }
   if (s_box[4] == 0) return;
 
   const int rows = cy1 - cy0 + 1, words = ((cx1 - cx0) >> 5) + 1;
@@ -1214,6 +1237,29 @@ __global__ void low_checksum_kernel(Geometry g, const TableSlot* __restrict__ sl
   for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) acc += slots[t].low[i];
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
+}
+
+// Fresh slots: low-res tables all zero / all floor (padding included), meta "no table".
+__global__ void __launch_bounds__(256) slot_init_kernel(Geometry g, const TableSlot* __restrict__ slots,
+                                                        TableMeta* __restrict__ metas) {
+  const TableSlot slot = slots[blockIdx.x];
+  const double floor_log = CSM_FLOOR_LOG;
+  for (int i = threadIdx.x; i < g.wl * g.wl; i += blockDim.x) slot.low[i] = 0.0;
+  for (int i = threadIdx.x; i < (int)lowlog_cells(g.wl); i += blockDim.x) slot.lowlog[i] = floor_log;
+  if (threadIdx.x == 0) {
+    TableMeta m = {};
+    m.cx0 = 0; m.cx1 = -1; m.cy0 = 0; m.cy1 = -1;
+    m.ax0 = 0; m.ax1 = -1; m.ay0 = 0; m.ay1 = -1;
+    m.bx1 = -1; m.by1 = -1; m.cropped = 1;
+    m.lx0 = INT_MAX; m.lx1 = INT_MIN; m.ly0 = INT_MAX; m.ly1 = INT_MIN;
+    m.min_key = ~0ULL;
+    metas[blockIdx.x] = m;
+  }
+}
+
+void launch_slot_init(const Geometry& g, const TableSlot* slots, TableMeta* metas, int n_slots,
+                      cudaStream_t stream) {
+  if (n_slots > 0) slot_init_kernel<<<n_slots, 256, 0, stream>>>(g, slots, metas);
 }
 
 // ---- launchers --------------------------------------------------------------

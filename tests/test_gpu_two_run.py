@@ -104,3 +104,40 @@ def test_two_run_wave_on_the_solver_grid():
     for i in range(4):
         assert np.array_equal(big[i], small[i]), i
     assert np.array_equal(big_stats, small_stats)
+
+
+def test_slot_reuse_leaves_no_stale_low_res_cells(golden):
+    """The raster kernel only clears what the slot's previous table wrote into the low-res
+    arrays: a handle that built large tables first must give, for small tables in another
+    place, exactly what a fresh handle gives (matches, counters and the low-res table)."""
+    params = tuple(golden["std_params"])
+    big = [golden["std_a_0"], golden["std_b_0"], golden["std_a_1"], golden["std_b_1"]]
+    rng = np.random.default_rng(5)
+    small = []
+    for k in range(4):  # a few metres of wall, far from the origin, different place per cloud
+        n = 200
+        t = np.linspace(0.0, 3.0, n)
+        pts = np.stack([t + 0.002 * rng.standard_normal(n), 0.3 * np.sin(2 * t)], 1)
+        small.append(moved(pts, 0.4 * k, 12.0 - 7.0 * k, -15.0 + 9.0 * k))
+    pa, pb = np.asarray([0, 2], np.int32), np.asarray([1, 3], np.int32)
+    rmin, rmax = np.full(2, -0.3), np.full(2, 0.3)
+
+    used = CorrelativeScanMatcher(*params)
+    xy, offs = scan_set(big)
+    used.upload_scans(xy, offs)
+    used.match_batch(pa, pb, rmin, rmax)
+    used.GetLookupTables(big[0])
+    xy, offs = scan_set(small)
+    used.upload_scans(xy, offs)
+    got = used.match_batch(pa, pb, rmin, rmax, with_stats=True)
+    got_hi, got_lo = used.GetLookupTables(small[1])
+
+    fresh = CorrelativeScanMatcher(*params)
+    fresh.upload_scans(xy, offs)
+    want = fresh.match_batch(pa, pb, rmin, rmax, with_stats=True)
+    want_hi, want_lo = fresh.GetLookupTables(small[1])
+    for g_, w_ in zip(got, want):
+        assert np.array_equal(g_, w_)
+    assert np.array_equal(got_lo.values, want_lo.values)
+    assert np.array_equal(got_hi.values, want_hi.values)
+    used.close(); fresh.close()
