@@ -1,10 +1,11 @@
 #!/bin/bash
 # ncu evidence for one build (run under gpurun, ONE GPU): launch list + one --set full
-# capture per step kernel of `python bench.py --scans 400` (400 tables, 2000 pairs per
-# step).  Reports land in gpurun_out/<tag>_*; summarise here with
-#   python scripts/ncu_summary.py <tag> gpurun_out/<tag>_launches.csv gpurun_out/<tag>_full.ncu-rep [bench.json]
+# capture per step kernel of `python bench.py --scans N` (N tables, 5 N pairs per
+# step; default N = 2000, the bench size).  Reports land in gpurun_out/<tag>_*; summarise here with
+#   python scripts/ncu_summary.py <tag> gpurun_out/<tag>_launches.csv gpurun_out/<tag>_full.ncu-rep [bench.json] [N]
 TAG=${1:-r2}
-CMD="python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline"
+SCANS=${2:-2000}   # full bench size: waves of >= 1200 tables take the two-run table path
+CMD="python bench.py --scans $SCANS --steps 1 --warmup 1 --no-cpu-baseline"
 $CMD > gpurun_out/${TAG}_ncu_plain.json 2> gpurun_out/${TAG}_ncu_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1

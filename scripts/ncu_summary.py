@@ -100,12 +100,12 @@ def full_table(rep):
 def main():
     tag, launches, rep = sys.argv[1], sys.argv[2], sys.argv[3]
     bench = sys.argv[4] if len(sys.argv) > 4 else None
+    n_tables = int(sys.argv[5]) if len(sys.argv) > 5 else 2000  # bench.py --scans N of the capture
     os.makedirs(PROF, exist_ok=True)
     shutil.copy(launches, os.path.join(PROF, f"{tag}_launches.csv"))
     lt, shares = launches_table(launches)
     ft, traffic = full_table(rep)
     # traffic.json is rewritten from THIS capture only (no stale kernels of older builds)
-    n_tables = 400  # bench.py --scans 400: one table wave of 400 tables per launch
     tab = [k for k in traffic if any(t in k for t in ("raster_kernel", "xpass_kernel", "ypass_kernel",
                                                       "ypass2_kernel", "low_finalize_kernel",
                                                       "normalize_pool_kernel"))]
@@ -115,7 +115,7 @@ def main():
            [k for k in traffic if "ypass2_kernel" in k and k.rstrip().endswith(", 2>")]
     low = [k for k in traffic if "low_score_kernel" in k]
     out = {"_source": f"{tag}: ncu --set full --clock-control none, one launch per kernel of "
-                      f"`python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline` "
+                      f"`python bench.py --scans {n_tables} --steps 1 --warmup 1 --no-cpu-baseline` "
                       f"({n_tables} tables, {5 * n_tables} pairs per launch)",
            "tables_per_launch": n_tables,
            "kernels_bytes_per_launch": {k: v["total"] for k, v in traffic.items()},
@@ -127,8 +127,8 @@ def main():
     json.dump(out, open(os.path.join(PROF, "traffic.json"), "w"), indent=1)
     md = [f"# ncu summary {tag}", "",
           "Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none` over "
-          "`python bench.py --scans 400 --steps 1 --warmup 1 --no-cpu-baseline` "
-          "(2000 pairs, 400 tables; cold-cache, serialised: compare SHARES).", "", lt, "",
+          f"`python bench.py --scans {n_tables} --steps 1 --warmup 1 --no-cpu-baseline` "
+          f"({5 * n_tables} pairs, {n_tables} tables; cold-cache, serialised: compare SHARES).", "", lt, "",
           "Full capture (`ncu --set full --clock-control none --import-source on`, one launch per "
           "kernel of the same command):", "", ft, ""]
     if bench and os.path.exists(bench):
