@@ -227,7 +227,22 @@ int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, dou
   cudaStream_t st = h->stream;
   const PairResult* src_dev = h->results_dev.p;
   if (world > 1) {
-    if ((rc = h->results_dev.reserve((size_t)max_count))) return rc;  // normally reserved at launch
+    // The all-gather sends max_count records from every rank.  A block matched through
+    // nautilus_csm_match_batch reserved only its own size: grow the buffer WITHOUT losing
+    // the records (DevBuf::reserve frees before it allocates).
+    if (h->results_dev.cap < (size_t)max_count) {
+      PairResult* bigger = nullptr;
+      const size_t want = std::max<size_t>((size_t)max_count, 16);
+      CU_TRY(cudaMalloc(&bigger, sizeof(PairResult) * want));
+      CU_TRY(cudaMemsetAsync(bigger, 0, sizeof(PairResult) * want, st));
+      if (n_local > 0)
+        CU_TRY(cudaMemcpyAsync(bigger, h->results_dev.p, sizeof(PairResult) * (size_t)n_local,
+                               cudaMemcpyDeviceToDevice, st));
+      CU_TRY(cudaStreamSynchronize(st));  // (growth path only) before the old buffer goes
+      cudaFree(h->results_dev.p);
+      h->results_dev.p = bigger;
+      h->results_dev.cap = want;
+    }
     if ((rc = h->gather_dev.reserve((size_t)max_count * world))) return rc;
     NcclApi* api = nccl_api();
     cudaEvent_t e0, e1;

@@ -43,6 +43,18 @@ else:
     uid = open(id_path, "rb").read()
 m.comm_init(uid)
 m.upload_scans(xy, offs)
+# first, on the fresh handle: blocks of very different size through the explicit form.  The
+# smaller block's result buffer has to grow to the all-gather's send size (the largest
+# block) without losing its records.
+# (the pair list repeated 200 times: record buffers of 0.1 - 0.5 MB, which the allocator does
+# not hand back in place the way it does a few KB)
+REP = 200
+pa_t, pb_t, rmin_t, rmax_t = (np.tile(v, REP) for v in (pa, pb, rmin, rmax))
+order_u = np.argsort(pb_t, kind="stable").astype(np.int32)
+bounds_u = np.asarray([0, len(pa_t) // 4, len(pa_t)], np.int64)
+mine_u = order_u[bounds_u[rank]:bounds_u[rank + 1]]
+m.match_batch(pa_t[mine_u], pb_t[mine_u], rmin_t[mine_u], rmax_t[mine_u], with_stats=True)
+got_u = m.gather(order_u, bounds_u, with_stats=True)
 got = m.match_batch_sharded(pa, pb, rmin, rmax, with_stats=True)
 t = m.last_timings()
 # the explicit form
@@ -57,8 +69,9 @@ m1 = CorrelativeScanMatcher(30, 2, 0.3, 0.03, device=rank)
 m1.upload_scans(xy, offs)
 want = m1.match_batch(pa, pb, rmin, rmax, with_stats=True)
 m1.close()
-for u, v, z in zip(got, want, got2):
+for u, v, z, zu in zip(got, want, got2, got_u):
     assert np.array_equal(u, v) and np.array_equal(z, v)
+    assert np.array_equal(zu, np.tile(v, (REP,) + (1,) * (v.ndim - 1))), "unequal blocks: gathered records differ"
 for u, v in zip(local, want):
     assert np.array_equal(u, v[mine])
 assert 0 < len(mine) < len(pa)
