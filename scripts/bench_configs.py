@@ -59,6 +59,14 @@ def bench_tables(cpu):
     return line
 
 
+def low_fp64_frac(st, offs, pa, ms_low, sm_mhz=1965.0):
+    """K5's fraction of the fp64 add pipe, as bench.py states it: one add per (low-res
+    candidate, point) over 148 SMs x 64 adds per clock."""
+    pts = (offs[1:] - offs[:-1])[pa].astype(np.float64)
+    adds = float((st[:, 0].astype(np.float64) * pts).sum())
+    return adds / (ms_low * 1e-3) / (148 * 64 * sm_mhz * 1e6)
+
+
 def bench_wide(cpu):
     n_scans, group = 40, 5
     xy, offs = synth.make_scan_set(n_scans, group=group, seed=4, trans_range=10.0, max_rot=1.5)
@@ -77,7 +85,8 @@ def bench_wide(cpu):
             "metric": "candidate_transforms_scored_per_sec", "value": cand / (tm["ms_total"] * 1e-3),
             "pairs_per_sec": len(pa) / (tm["ms_total"] * 1e-3), "ms": tm["ms_total"],
             "ms_wall": wall * 1e3, "kernels_ms": {k: tm[k] for k in ("ms_tables", "ms_low", "ms_refine")},
-            "low_candidates_per_pair": int(st[0, 0]), "mean_pops": float(st[:, 2].mean())}
+            "low_candidates_per_pair": int(st[0, 0]), "mean_pops": float(st[:, 2].mean()),
+            "low_score_kernel_fp64_add_frac": low_fp64_frac(st, offs, pa, tm["ms_low"])}
     if cpu:
         from oracle import ref
         k = min(cores(), 8)
@@ -128,11 +137,12 @@ def bench_solver(cpu):
             "kernels_ms": {k: tm[k] for k in ("ms_tables", "ms_low", "ms_refine")},
             "waves": tm["waves"], "w_high": m.w_high, "hi_candidates_per_window": int(st[0, 1] // max(1, st[0, 2])),
             "mean_pops": float(st[:, 2].mean()), "spec_windows": tm["spec_windows"],
+            "low_score_kernel_fp64_add_frac": low_fp64_frac(st, offs, pa, tm["ms_low"]),
             "tables": {"dense_layout_GBps": dense / (tm["ms_tables"] * 1e-3) / 1e9,
                        "dense_layout_frac_of_hbm": dense / (tm["ms_tables"] * 1e-3) / 1e9 / PEAK,
                        "note": "dense-layout bytes are the reference's 8 (W^2 + Wl^2) per table; the "
                                "kernels move the cropped rectangle only - actual traffic: "
-                               "profiles/r2_traffic.json"}}
+                               "profiles/traffic.json"}}
     if cpu:
         from oracle import ref
         k = cores()
