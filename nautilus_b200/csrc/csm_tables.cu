@@ -410,6 +410,15 @@ __device__ __forceinline__ double ld_gbl(const double* p) {
 __device__ __forceinline__ void st_gbl(double* p, double v) {
   asm volatile("st.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
+// Row u of a chunk: p + u * stride doubles with the product taken in 32 bits (a chunk
+// spans at most 32 rows of at most 30 000 cells), so that the address is one
+// IMAD.WIDE.U32 instead of a 64-bit multiply per access.
+__device__ __forceinline__ const double* row_at(const double* p, unsigned stride8, int u) {
+  return reinterpret_cast<const double*>(reinterpret_cast<const char*>(p) + stride8 * (unsigned)u);
+}
+__device__ __forceinline__ double* row_at(double* p, unsigned stride8, int u) {
+  return reinterpret_cast<double*>(reinterpret_cast<char*>(p) + stride8 * (unsigned)u);
+}
 
 constexpr int RC_MAXCH_SMALL = 64, RC_MAXCH_LARGE = 192;
 
@@ -547,7 +556,7 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
     if (lane >= k_lo && lane <= k_hi && r0 + lane <= rel_st) {
       double* dst = base + (m.cx0 + r0 + lane - m.ax0);
       for (int rr = 0; rr < 32; ++rr)
-        if ((mask >> rr) & 1u) st_gbl(dst + (size_t)rowidx[rr] * m.stride, tile[rr][lane]);
+        if ((mask >> rr) & 1u) st_gbl(dst + rowidx[rr] * m.stride, tile[rr][lane]);
     }
     __syncwarp();
   }
@@ -557,10 +566,10 @@ __global__ void __launch_bounds__(XP_WARPS * 32) xpass_kernel(
 // has bit u set when row r0+u holds a point (rows without one are exact zeros and
 // are not read).
 template <int YC>
-__device__ __forceinline__ void y_load(double (&a)[YC], const double* p, size_t stride,
+__device__ __forceinline__ void y_load(double (&a)[YC], const double* p, int stride,
                                        unsigned bits) {
 #pragma unroll
-  for (int u = 0; u < YC; ++u) a[u] = ((bits >> u) & 1u) ? ld_gbl(p + (size_t)u * stride) : 0.0;
+  for (int u = 0; u < YC; ++u) a[u] = ((bits >> u) & 1u) ? ld_gbl(row_at(p, 8u * (unsigned)stride, u)) : 0.0;
 }
 
 // nrow causal steps over a[0 .. nrow-1]; KEEP: the outputs replace the inputs.
@@ -582,7 +591,7 @@ __device__ __forceinline__ void y_causal(double (&a)[YC], int nrow, double& v1, 
 // already set), -1 when none.
 template <int YC, bool FULL, bool NEEDMIN>
 __device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int hi, int hs, int edge_u,
-                                             double w0, double* p, size_t stride, double sum,
+                                             double w0, double* p, int stride, double sum,
                                              double& v1, double& v2, double& v3, double a1,
                                              double a2, double a3, double& vmax, double& vmin) {
 #pragma unroll
@@ -595,7 +604,7 @@ __device__ __forceinline__ void y_anticausal(const double (&a)[YC], int lo, int 
         v0 = vv_step(__dmul_rn(a[u], sum), v1, v2, v3, a1, a2, a3);
         v3 = v2; v2 = v1; v1 = v0;
       }
-      if (FULL || u <= hs) st_gbl(p + (size_t)u * stride, v0);  // rows past ay1 are computed only
+      if (FULL || u <= hs) st_gbl(row_at(p, 8u * (unsigned)stride, u), v0);  // rows past ay1 are computed only
       vmax = v0 > vmax ? v0 : vmax;  // no NaNs here: a compare and a select instead of fmax
       if (NEEDMIN) vmin = v0 < vmin ? v0 : vmin;
     }
@@ -622,7 +631,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
   const double sum = __dmul_rn(f.B, f.B);
   double* colp = slot.values + (live ? col : 0);
   const unsigned char* flag = slot.rowflag;
-  const size_t stride = (size_t)m.stride;
+  const int stride = m.stride;  // element offsets within a chunk stay 32-bit: one IMAD.WIDE per access
 
   // rows of the occupied box that hold a point, one bit each (zeros past the box)
   __shared__ unsigned s_rows[MAXCH + 1];
@@ -656,7 +665,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     const int nch = (n_fwd + YC - 1) / YC;
     {
       const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
-      for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
+      for (int ci = 0; ci < nch; ++ci, p += YC * stride) {
         ck[3 * ci] = v1; ck[3 * ci + 1] = v2; ck[3 * ci + 2] = v3;
         const int b0 = ci * YC;
         const unsigned bits = (s_rows[b0 >> 5] >> (b0 & 31)) & CMASK;
@@ -680,7 +689,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass_kernel(
     const int rel_lo = m.ay0 - m.cy0;  // <= 0
     const int ch_lo = -((-rel_lo + YC - 1) / YC);
     double* p = colp + (size_t)(m.cy0 + (nch - 1) * YC - m.ay0) * stride;
-    for (int ch = nch - 1; ch >= ch_lo; --ch, p -= (size_t)YC * stride) {
+    for (int ch = nch - 1; ch >= ch_lo; --ch, p -= YC * stride) {
       const int b0 = ch * YC;  // row of a[0] relative to cy0
       double a[YC];
       if (ch >= 0) {  // rebuild the chunk's causal outputs from its checkpoint
@@ -826,7 +835,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
   double* ckp = slot.ck;
   const int ckstride = m.stride;
   const unsigned char* flag = slot.rowflag;
-  const size_t stride = (size_t)m.stride;
+  const int stride = m.stride;  // element offsets within a chunk stay 32-bit: one IMAD.WIDE per access
   const int lane = threadIdx.x & 31;
 
   __shared__ unsigned s_rows[MAXCH + 1];
@@ -864,7 +873,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
       v1 = v2 = v3 = __ddiv_rn(x0, f.B);
     }
     const double* p = colp + (size_t)(m.cy0 - m.ay0) * stride;
-    for (int ci = 0; ci < nch; ++ci, p += (size_t)YC * stride) {
+    for (int ci = 0; ci < nch; ++ci, p += YC * stride) {
       if (live) {
         ckp[ck_index(ci, 0, col, ckstride)] = v1;
         ckp[ck_index(ci, 1, col, ckstride)] = v2;
@@ -960,7 +969,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
   const bool needmin = !m.cropped;
   double vmin = INFINITY, dm = -INFINITY;
   double* p = colp + (size_t)(m.cy0 + (nch - 1) * YC - m.ay0) * stride;
-  for (int ch = nch - 1; ch >= ch_lo; --ch, p -= (size_t)YC * stride) {
+  for (int ch = nch - 1; ch >= ch_lo; --ch, p -= YC * stride) {
     const int b0 = ch * YC;  // row of a[0] relative to cy0
     double a[YC];
     if (ch >= 0) {  // rebuild the chunk's causal outputs from its checkpoint
@@ -1014,7 +1023,7 @@ __global__ void __launch_bounds__(YP_THREADS, MINB) ypass2_kernel(
           const double d = __dsub_rn(s_out[u][threadIdx.x], mn);
           double out = CSM_FLOOR_LOG;
           if (!(constant || d < sub_floor)) out = lookup_log(div_by(d, range, rinv));
-          st_gbl(p + (size_t)u * stride, out);
+          st_gbl(row_at(p, 8u * (unsigned)stride, u), out);
         }
       }
     }
@@ -1138,10 +1147,10 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
   for (int c = threadIdx.x; c < aw; c += blockDim.x) {
     double dm = -INFINITY;
     double* p = slot.values + (size_t)(rs - m.ay0) * m.stride + c;
-    for (int r0 = rs; r0 <= re; r0 += NP_B, p += (size_t)NP_B * m.stride) {
+    for (int r0 = rs; r0 <= re; r0 += NP_B, p += NP_B * m.stride) {
       double v[NP_B];  // the rows of a window are independent: all loads first
 #pragma unroll
-      for (int u = 0; u < NP_B; ++u) v[u] = (r0 + u <= re) ? ld_gbl(p + (size_t)u * m.stride) : 0.0;
+      for (int u = 0; u < NP_B; ++u) v[u] = (r0 + u <= re) ? ld_gbl(p + u * m.stride) : 0.0;
 #pragma unroll
       for (int u = 0; u < NP_B; ++u) {
         if (r0 + u <= re) {
@@ -1152,7 +1161,7 @@ __global__ void __launch_bounds__(256) normalize_pool_kernel(
           double out;
           if (store_log) out = (constant || d < sub_floor) ? CSM_FLOOR_LOG : lookup_log(div_by(d, range, rinv));
           else out = constant ? 0.0 : __ddiv_rn(d, range);
-          st_gbl(p + (size_t)u * m.stride, out);
+          st_gbl(p + u * m.stride, out);
         }
       }
     }
