@@ -19,6 +19,8 @@
 #include <string>
 #include <vector>
 
+#include <thread>
+
 #include "csm_handle.h"
 
 namespace {
@@ -283,16 +285,34 @@ int gather_impl(NautilusCsm* h, const int32_t* order, const int64_t* bounds, dou
   const HostTimer collect_timer;
   h->timings.ms_host_plan += ms_plan_extra;
   h->timings.ms_host_wait = ms_wait;
-  int bad = 0;
-  for (int r = 0; r < world; ++r) {
-    const PairResult* blk = h->gather_pin.p + (size_t)r * max_count;
-    for (long long k = bounds[r]; k < bounds[r + 1]; ++k) {
-      const PairResult& v = blk[k - bounds[r]];
-      const int p = order ? order[k] : (int)k;
-      score[p] = v.score; x[p] = v.x; y[p] = v.y; theta[p] = v.theta;
-      if (stats) { stats[p].n_low = v.n_low; stats[p].n_high = v.n_high; stats[p].n_pops = v.n_pops; }
-      bad |= v.pad;
+  // records -> the caller's arrays, in caller order (a scatter: every record lands in a
+  // place of its own, so large gathers are split over a few host threads by rank block)
+  auto scatter_blocks = [&](int r0, int r1) -> int {
+    int bad_ = 0;
+    for (int r = r0; r < r1; ++r) {
+      const PairResult* blk = h->gather_pin.p + (size_t)r * max_count;
+      for (long long k = bounds[r]; k < bounds[r + 1]; ++k) {
+        const PairResult& v = blk[k - bounds[r]];
+        const int p = order ? order[k] : (int)k;
+        score[p] = v.score; x[p] = v.x; y[p] = v.y; theta[p] = v.theta;
+        if (stats) { stats[p].n_low = v.n_low; stats[p].n_high = v.n_high; stats[p].n_pops = v.n_pops; }
+        bad_ |= v.pad;
+      }
     }
+    return bad_;
+  };
+  int bad = 0;
+  const int n_thr = (world >= 2 && n_total >= 16384) ? std::min(world, 4) : 1;
+  if (n_thr == 1) {
+    bad = scatter_blocks(0, world);
+  } else {
+    int bads[4] = {0, 0, 0, 0};
+    std::thread th[3];
+    for (int t = 1; t < n_thr; ++t)
+      th[t - 1] = std::thread([&, t] { bads[t] = scatter_blocks(world * t / n_thr, world * (t + 1) / n_thr); });
+    bads[0] = scatter_blocks(0, world / n_thr);
+    for (int t = 1; t < n_thr; ++t) th[t - 1].join();
+    bad = bads[0] | bads[1] | bads[2] | bads[3];
   }
   h->timings.ms_host_collect = collect_timer.ms();
   if (bad) return fail(NAUTILUS_EEMPTY, "a pair had nothing to score");
