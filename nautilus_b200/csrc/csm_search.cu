@@ -452,18 +452,10 @@ constexpr int RF_THREADS = 128;
 #ifndef RF_MINB_FIRST
 #define RF_MINB_FIRST 8
 #endif
-#ifndef RF_MINB_SPEC
-#define RF_MINB_SPEC 0
-#endif
 #if RF_MINB_FIRST > 0
 #define RF_BOUNDS_FIRST __launch_bounds__(RF_THREADS, RF_MINB_FIRST)
 #else
 #define RF_BOUNDS_FIRST __launch_bounds__(RF_THREADS)
-#endif
-#if RF_MINB_SPEC > 0
-#define RF_BOUNDS_SPEC __launch_bounds__(RF_THREADS, RF_MINB_SPEC)
-#else
-#define RF_BOUNDS_SPEC __launch_bounds__(RF_THREADS)
 #endif
 constexpr int RF_POINT_CHUNK = 1024;  // points whose window words are staged at a time
 #ifndef RF_DEPTH_N
@@ -841,11 +833,16 @@ __global__ void RF_BOUNDS_FIRST refine_first_kernel(
   }
 }
 
-__global__ void RF_BOUNDS_SPEC refine_spec_kernel(
-    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+// SMALLWIN: windows of at most RF_THREADS candidates (the 10 x 10 ones of the 0.03 m grid)
+// are a single pass of the block, which wants warps more than registers: 8 blocks per SM
+// (64 registers).  Larger windows (30 x 30 at 0.01 m) keep the compiler's 80.
+// (two entry points over one body: any explicit bound on the large-window kernel measured
+// worse than none - 11.9 - 12.5 ms against 11.65 on the 0.01 m configuration)
+__device__ __forceinline__ void refine_spec_body(
+    const Geometry& g, const SearchGrid& sg, const CellMap& cm, const float2* __restrict__ points,
     const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
     const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
-    const Rotation* __restrict__ rots, SearchBuffers sb) {
+    const Rotation* __restrict__ rots, const SearchBuffers& sb) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   const RefineShared sh = carve_refine(s_raw, sg.n_h_max, 0);
   __shared__ ArgBest s_red[RF_THREADS / 32];
@@ -874,6 +871,30 @@ __global__ void RF_BOUNDS_SPEC refine_spec_kernel(
     }
     __syncthreads();  // s_item is rewritten next turn
   }
+}
+
+template <bool SMALLWIN>
+__global__ void refine_spec_kernel(Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+                                   const long long* __restrict__ offsets,
+                                   const TableSlot* __restrict__ slots,
+                                   const TableMeta* __restrict__ metas,
+                                   const PairWork* __restrict__ pairs,
+                                   const Rotation* __restrict__ rots, SearchBuffers sb);
+template <>
+__global__ void __launch_bounds__(RF_THREADS, 8) refine_spec_kernel<true>(
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb) {
+  refine_spec_body(g, sg, cm, points, offsets, slots, metas, pairs, rots, sb);
+}
+template <>
+__global__ void __launch_bounds__(RF_THREADS) refine_spec_kernel<false>(
+    Geometry g, SearchGrid sg, CellMap cm, const float2* __restrict__ points,
+    const long long* __restrict__ offsets, const TableSlot* __restrict__ slots,
+    const TableMeta* __restrict__ metas, const PairWork* __restrict__ pairs,
+    const Rotation* __restrict__ rots, SearchBuffers sb) {
+  refine_spec_body(g, sg, cm, points, offsets, slots, metas, pairs, rots, sb);
 }
 
 __global__ void __launch_bounds__(RF_THREADS) refine_finish_kernel(
@@ -939,7 +960,7 @@ int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hig
                   int sm_count, cudaStream_t stream) {
   if (n_pairs <= 0) return 0;
   const size_t smem = refine_smem_bytes(sg.n_t, sg.n_h_max, true);
-  static SmemOptIn opt_serial, opt_first, opt_spec, opt_finish;
+  static SmemOptIn opt_serial, opt_first, opt_spec, opt_spec_wide, opt_finish;
   if (serial) {
     opt_serial.allow(refine_kernel, smem);
     refine_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots, metas,
@@ -948,17 +969,24 @@ int launch_refine(const Geometry& g, const SearchGrid& sg, const CellMap& cm_hig
   }
   const size_t smem_spec = refine_smem_bytes(sg.n_t, sg.n_h_max, false);
   opt_first.allow(refine_first_kernel, smem);
-  opt_spec.allow(refine_spec_kernel, smem_spec);
+  const bool small_win = sg.n_h_max * sg.n_h_max <= RF_THREADS;
+  if (small_win) opt_spec.allow(refine_spec_kernel<true>, smem_spec);
+  else opt_spec_wide.allow(refine_spec_kernel<false>, smem_spec);
   opt_finish.allow(refine_finish_kernel, smem);
   cudaMemsetAsync(sb.spec_counters, 0, 2 * sizeof(int), stream);
   refine_first_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots,
                                                              metas, pairs, rots, sb);
   // persistent: as many blocks as stay resident, each fetching windows from the queue
-  const int per_sm = opt_spec.blocks_per_sm(refine_spec_kernel, RF_THREADS, smem_spec);
+  const int per_sm = small_win ? opt_spec.blocks_per_sm(refine_spec_kernel<true>, RF_THREADS, smem_spec)
+                               : opt_spec_wide.blocks_per_sm(refine_spec_kernel<false>, RF_THREADS, smem_spec);
   const long long max_items = (long long)n_pairs * sb.spec_cap;
   const int grid = (int)std::min<long long>((long long)sm_count * per_sm, std::max<long long>(max_items, 1));
-  refine_spec_kernel<<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets, slots,
-                                                              metas, pairs, rots, sb);
+  if (small_win)
+    refine_spec_kernel<true><<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets,
+                                                                      slots, metas, pairs, rots, sb);
+  else
+    refine_spec_kernel<false><<<grid, RF_THREADS, smem_spec, stream>>>(g, sg, cm_high, points, offsets,
+                                                                       slots, metas, pairs, rots, sb);
   refine_finish_kernel<<<n_pairs, RF_THREADS, smem, stream>>>(g, sg, cm_high, points, offsets, slots,
                                                               metas, pairs, rots, sb, results);
   return 3;
