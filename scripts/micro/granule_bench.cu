@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(128) column_walk(const double* __restrict__ ba
 // The same walk with the y-pass's work per chunk: after a chunk's 16 loads, 16 steps of the
 // dependent recursion v0 = ((x + v1 a1) + v2 a2) + v3 a3 (separately rounded, like vv_step).
 // Dynamic shared memory only limits the resident blocks per SM.
+template <int SWEEPS>
 __global__ void __launch_bounds__(128) column_walk_chain(const double* __restrict__ base, double* out,
                                                          double a1, double a2, double a3) {
   extern __shared__ double pad[];
@@ -54,12 +55,17 @@ __global__ void __launch_bounds__(128) column_walk_chain(const double* __restric
     double v[16];
 #pragma unroll
     for (int u = 0; u < 16; ++u) v[u] = __ldg(p + (size_t)(r0 + u) * PITCH);
+    // SWEEPS passes over the chunk, each feeding the next (like causal rebuild -> anti-causal)
 #pragma unroll
-    for (int u = 0; u < 16; ++u) {
-      double v0 = __dadd_rn(v[u], __dmul_rn(v1, a1));
-      v0 = __dadd_rn(v0, __dmul_rn(v2, a2));
-      v0 = __dadd_rn(v0, __dmul_rn(v3, a3));
-      v3 = v2; v2 = v1; v1 = v0;
+    for (int s = 0; s < SWEEPS; ++s) {
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        double v0 = __dadd_rn(v[u], __dmul_rn(v1, a1));
+        v0 = __dadd_rn(v0, __dmul_rn(v2, a2));
+        v0 = __dadd_rn(v0, __dmul_rn(v3, a3));
+        v3 = v2; v2 = v1; v1 = v0;
+        v[u] = v0;
+      }
     }
   }
   if (v1 == 12345.678) out[0] = v1 + pad[0];
@@ -102,22 +108,27 @@ int main() {
   printf("column walk, 256 B granules (1 double per lane): %.0f GB/s\n", gb / (time_walk<1>(d, out, n_tables) * 1e-3));
   printf("column walk, 512 B granules (2 doubles per lane): %.0f GB/s\n", gb / (time_walk<2>(d, out, n_tables) * 1e-3));
   printf("column walk, 1 KB granules (4 doubles per lane): %.0f GB/s\n", gb / (time_walk<4>(d, out, n_tables) * 1e-3));
-  cudaFuncSetAttribute(column_walk_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  for (int blocks : {3, 4, 5, 6, 8, 12, 16}) {
-    const size_t smem = (size_t)(227 * 1024 / blocks - 1024) & ~(size_t)255;
-    dim3 grid((COLS + 127) / 128, n_tables);
-    cudaEvent_t a, b;
-    cudaEventCreate(&a); cudaEventCreate(&b);
-    column_walk_chain<<<grid, 128, smem>>>(d, out, 0.5, 0.25, 0.125);
-    cudaEventRecord(a);
-    for (int i = 0; i < 3; ++i) column_walk_chain<<<grid, 128, smem>>>(d, out, 0.5, 0.25, 0.125);
-    cudaEventRecord(b);
-    cudaEventSynchronize(b);
-    float t = 0.f;
-    cudaEventElapsedTime(&t, a, b);
-    printf("column walk + 16-step fp64 recursion per chunk, %2d blocks of 128 per SM: %.0f GB/s (%.3f ms per pass)\n",
-           blocks, gb / (t / 3 * 1e-3), t / 3);
-  }
+  auto chain = [&](auto kernel, int sweeps) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    for (int blocks : {4, 6, 8, 12}) {
+      const size_t smem = (size_t)(227 * 1024 / blocks - 1024) & ~(size_t)255;
+      dim3 grid((COLS + 127) / 128, n_tables);
+      cudaEvent_t a, b;
+      cudaEventCreate(&a); cudaEventCreate(&b);
+      kernel<<<grid, 128, smem>>>(d, out, 0.5, 0.25, 0.125);
+      cudaEventRecord(a);
+      for (int i = 0; i < 3; ++i) kernel<<<grid, 128, smem>>>(d, out, 0.5, 0.25, 0.125);
+      cudaEventRecord(b);
+      cudaEventSynchronize(b);
+      float t = 0.f;
+      cudaEventElapsedTime(&t, a, b);
+      printf("column walk + %d x 16-step fp64 recursion per chunk, %2d blocks of 128 per SM: %.0f GB/s, %.3f ms per pass, %.2f G steps/ms\n",
+             sweeps, blocks, gb / (t / 3 * 1e-3), t / 3, gb / 8 * sweeps / (t / 3));
+    }
+  };
+  chain(column_walk_chain<1>, 1);
+  chain(column_walk_chain<2>, 2);
+  chain(column_walk_chain<3>, 3);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   stream_read<<<dim3(64, 148), 256>>>(d, out, n_tables);
